@@ -1,0 +1,143 @@
+"""ctypes mirror of include/adrp.h (struct layouts, enum values) and the config builder.
+
+Host-side glue only: no arithmetic of the path lives here.  The same structures are handed to the
+CUDA library (``_lib.py``) and, in tests, to the CPU oracle -- both take ``adrp_config`` by pointer.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+from .assets import DroneParams, drone_params
+from .utils.enums import ActionType, DroneModel, Physics, RaceMode
+
+ABI_VERSION = 3
+MAX_DRONES, MAX_GATES, MAX_OBSTACLES, STATE_DIM = 32, 8, 8, 20
+
+F32, F64 = 0, 1
+PHY_DYN, PHY_GND, PHY_DRAG, PHY_DW, PHY_GROUND = 1, 2, 4, 8, 16
+ACT_RPM_RAW, ACT_RPM, ACT_ONE_D_RPM, ACT_PID, ACT_ONE_D_PID, ACT_VEL, ACT_MEL, ACT_PID_FULL = range(8)
+ENV_CTRL, ENV_HOVER, ENV_MULTIHOVER, ENV_RACE = range(4)
+FLAG_ELIMINATED, FLAG_FINISHED, FLAG_CRASHED, FLAG_OUT_OF_BOUNDS, FLAG_UNSTABLE, FLAG_TUMBLE_STOP = 1, 2, 4, 8, 16, 32
+
+MODEL_ID = {DroneModel.CF2X: 0, DroneModel.CF2P: 1, DroneModel.RACE: 2}
+ACTION_DIM = {ACT_RPM_RAW: 4, ACT_RPM: 4, ACT_ONE_D_RPM: 1, ACT_PID: 3, ACT_ONE_D_PID: 1, ACT_VEL: 4, ACT_MEL: 4,
+              ACT_PID_FULL: 12}
+ACTION_ID = {ActionType.RPM: ACT_RPM, ActionType.ONE_D_RPM: ACT_ONE_D_RPM, ActionType.PID: ACT_PID,
+             ActionType.ONE_D_PID: ACT_ONE_D_PID, ActionType.VEL: ACT_VEL, ActionType.MEL: ACT_MEL}
+
+#: Physics enum -> ADRP_PHY_* mask.  PYB modes get the declared plane response.
+PHYSICS_MASK = {
+    Physics.PYB: PHY_GROUND,
+    Physics.DYN: PHY_DYN,
+    Physics.PYB_GND: PHY_GND | PHY_GROUND,
+    Physics.PYB_DRAG: PHY_DRAG | PHY_GROUND,
+    Physics.PYB_DW: PHY_DW | PHY_GROUND,
+    Physics.PYB_GND_DRAG_DW: PHY_GND | PHY_DRAG | PHY_DW | PHY_GROUND,
+    Physics.DYN_GND_DRAG_DW: PHY_DYN | PHY_GND | PHY_DRAG | PHY_DW,
+}
+
+d = C.c_double
+i32 = C.c_int32
+
+
+class DroneParamsC(C.Structure):
+    _fields_ = [(n, d) for n in (
+        "mass", "arm", "kf", "km", "thrust2weight", "max_speed_kmh", "gnd_eff_coeff", "prop_radius",
+        "drag_coeff_xy", "drag_coeff_z", "dw_coeff_1", "dw_coeff_2", "dw_coeff_3", "ixx", "iyy", "izz",
+        "collision_r", "collision_h", "collision_z_offset")] + [
+        ("prop_x", d * 4), ("prop_y", d * 4),
+        ("pyb_mass", d), ("pyb_ixx", d), ("pyb_iyy", d), ("pyb_izz", d), ("lin_damping", d), ("ang_damping", d)]
+
+
+class TrackC(C.Structure):
+    _fields_ = [("num_gates", i32), ("num_obstacles", i32), ("gates", (d * 4) * MAX_GATES),
+                ("gate_type", i32 * MAX_GATES), ("obstacles", (d * 3) * MAX_OBSTACLES), ("bounds_hi", d * 3),
+                ("contact_margin", d), ("visibility_range", d)]
+
+
+class RandomizationC(C.Structure):
+    _fields_ = [("random_gates_obstacles", i32), ("random_drone_state", i32), ("random_drone_inertia", i32),
+                ("disturbances", i32), ("gate_range", d * 2), ("obstacle_range", d * 2),
+                ("pos_range", (d * 2) * 3), ("rot_range", (d * 2) * 3), ("mass_range", d * 2),
+                ("ixx_range", d * 2), ("iyy_range", d * 2), ("izz_range", d * 2), ("action_noise_std", d),
+                ("wind_lo", d * 3), ("wind_hi", d * 3)]
+
+
+class ConfigC(C.Structure):
+    _fields_ = [("abi_version", i32), ("device", i32), ("precision", i32), ("num_envs", i32),
+                ("drones_per_env", i32), ("drone_model", i32), ("physics", i32), ("pyb_freq", i32),
+                ("ctrl_freq", i32), ("action_type", i32), ("env_kind", i32), ("race_mode", i32),
+                ("auto_reset", i32), ("dslpid_model", i32), ("bug_compat", C.c_uint32), ("reserved0", i32),
+                ("g", d), ("episode_len_sec", d), ("mel_mass", d), ("seed", C.c_uint64), ("env_offset", C.c_uint64),
+                ("init_xyz", (d * 3) * MAX_DRONES), ("init_rpy", (d * 3) * MAX_DRONES),
+                ("init_vel", (d * 3) * MAX_DRONES), ("init_pqr", (d * 3) * MAX_DRONES),
+                ("target_pos", (d * 3) * MAX_DRONES), ("drone", DroneParamsC), ("dslpid_drone", DroneParamsC),
+                ("track", TrackC), ("rnd", RandomizationC)]
+
+
+def drone_params_c(p: DroneParams, body: DroneParams | None = None) -> DroneParamsC:
+    """``body``: the model whose mass/inertia Bullet integrates (race: legacy cf2x)."""
+    body = body or p
+    out = DroneParamsC()
+    for name in ("mass", "arm", "kf", "km", "thrust2weight", "max_speed_kmh", "gnd_eff_coeff", "prop_radius",
+                 "drag_coeff_xy", "drag_coeff_z", "dw_coeff_1", "dw_coeff_2", "dw_coeff_3", "ixx", "iyy", "izz"):
+        setattr(out, name, getattr(p, name))
+    out.collision_r, out.collision_h, out.collision_z_offset = p.collision_r, p.collision_h, p.collision_z_offset
+    for k in range(4):
+        out.prop_x[k], out.prop_y[k] = p.prop_xy[k]
+    out.pyb_mass, out.pyb_ixx, out.pyb_iyy, out.pyb_izz = body.mass, body.ixx, body.iyy, body.izz
+    out.lin_damping = out.ang_damping = 0.04
+    return out
+
+
+def default_init_xyz(p: DroneParams, M: int):
+    """BaseAviary.py:193-197."""
+    z = p.collision_h / 2 - p.collision_z_offset + 0.1
+    return [[i * 4 * p.arm, i * 4 * p.arm, z] for i in range(M)]
+
+
+def make_config(*, num_envs, num_drones=1, drone_model=DroneModel.CF2X, physics=Physics.PYB, pyb_freq=240,
+                ctrl_freq=240, action_type=ACT_RPM_RAW, env_kind=ENV_CTRL, precision=F32, device=0,
+                initial_xyzs=None, initial_rpys=None, initial_vels=None, initial_pqrs=None, target_pos=None,
+                episode_len_sec=8.0, auto_reset=False, race_mode=RaceMode.COMPARE, seed=0, env_offset=0,
+                physics_mask=None, body_model=None, mel_mass=0.027) -> ConfigC:
+    if pyb_freq % ctrl_freq != 0:
+        # same check and message as BaseAviary.__init__ (:79-80)
+        raise ValueError('[ERROR] in BaseAviary.__init__(), pyb_freq is not divisible by env_freq.')
+    if not 1 <= num_drones <= MAX_DRONES:
+        raise ValueError(f"num_drones must be in 1..{MAX_DRONES} (one env lives inside one warp)")
+    p = drone_params(drone_model)
+    c = ConfigC()
+    c.abi_version, c.device, c.precision = ABI_VERSION, device, precision
+    c.num_envs, c.drones_per_env = int(num_envs), int(num_drones)
+    c.drone_model = MODEL_ID[drone_model]
+    c.physics = PHYSICS_MASK[physics] if physics_mask is None else int(physics_mask)
+    c.pyb_freq, c.ctrl_freq = int(pyb_freq), int(ctrl_freq)
+    c.action_type, c.env_kind = int(action_type), int(env_kind)
+    c.race_mode = race_mode.value if isinstance(race_mode, RaceMode) else int(race_mode)
+    c.auto_reset = int(bool(auto_reset))
+    c.dslpid_model = MODEL_ID[DroneModel.CF2X]           # BaseRLAviary.py:75-76 (E11)
+    c.bug_compat = 0xFFFFFFFF
+    c.g, c.episode_len_sec, c.mel_mass = 9.8, float(episode_len_sec), float(mel_mass)
+    c.seed, c.env_offset = int(seed), int(env_offset)
+    xyz = default_init_xyz(p, num_drones) if initial_xyzs is None else initial_xyzs
+    rpy = [[0.0] * 3] * num_drones if initial_rpys is None else initial_rpys
+    vel = [[0.0] * 3] * num_drones if initial_vels is None else initial_vels
+    pqr = [[0.0] * 3] * num_drones if initial_pqrs is None else initial_pqrs
+    for i in range(num_drones):
+        for k in range(3):
+            c.init_xyz[i][k], c.init_rpy[i][k] = float(xyz[i][k]), float(rpy[i][k])
+            c.init_vel[i][k], c.init_pqr[i][k] = float(vel[i][k]), float(pqr[i][k])
+    if target_pos is None:
+        if env_kind == ENV_MULTIHOVER:                    # MultiHoverAviary.py:71
+            target_pos = [[xyz[i][0], xyz[i][1], xyz[i][2] + 1.0 / (i + 1)] for i in range(num_drones)]
+        else:                                             # HoverAviary.py:51
+            target_pos = [[0.0, 0.0, 1.0]] * num_drones
+    for i in range(num_drones):
+        for k in range(3):
+            c.target_pos[i][k] = float(target_pos[i][k])
+    c.drone = drone_params_c(p, drone_params(body_model) if body_model else None)
+    c.dslpid_drone = drone_params_c(drone_params(DroneModel.CF2X))
+    c.track.contact_margin, c.track.visibility_range = 0.02, 0.45
+    return c

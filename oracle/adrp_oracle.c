@@ -1,0 +1,119 @@
+/* TEST INFRASTRUCTURE -- C entry points of the CPU oracle (see adrp_oracle_impl.h for the arithmetic).
+ *
+ * Mirrors the product's C ABI (include/adrp.h) with HOST buffers so that tests can drive the CUDA
+ * library and the oracle with the same inputs.  Build: oracle/Makefile  ->  oracle/liboracle.so
+ *   gcc -O2 -ffp-contract=off -fno-fast-math -fopenmp -fPIC -shared
+ * The product never links or loads this file.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "../include/adrp.h"
+
+#define REAL double
+#define SFX f64
+#define SIN sin
+#define COS cos
+#define SQRT sqrt
+#define FABS fabs
+#define ATAN2 atan2
+#define ASIN asin
+#define EXP exp
+#define TAN tan
+#include "adrp_oracle_impl.h"
+#include "adrp_oracle_race.h"
+#include "adrp_oracle_api.h"
+#undef REAL
+#undef SFX
+#undef SIN
+#undef COS
+#undef SQRT
+#undef FABS
+#undef ATAN2
+#undef ASIN
+#undef EXP
+#undef TAN
+#undef CAT2
+#undef CAT
+#undef FN
+
+#define REAL float
+#define SFX f32
+#define SIN sinf
+#define COS cosf
+#define SQRT sqrtf
+#define FABS fabsf
+#define ATAN2 atan2f
+#define ASIN asinf
+#define EXP expf
+#define TAN tanf
+#include "adrp_oracle_impl.h"
+#include "adrp_oracle_race.h"
+#include "adrp_oracle_api.h"
+
+typedef struct orc_any { int precision; void* impl; } orc_any;
+
+int orc_create(const adrp_config* cfg, void** out)
+{
+    if (!cfg || cfg->abi_version != ADRP_ABI_VERSION) return ADRP_EABI;
+    orc_any* a = (orc_any*)calloc(1, sizeof(orc_any));
+    a->precision = cfg->precision;
+    a->impl = cfg->precision == ADRP_F64 ? (void*)create_f64(cfg) : (void*)create_f32(cfg);
+    if (!a->impl) { free(a); return ADRP_EINVAL; }
+    *out = a;
+    return ADRP_OK;
+}
+
+#define DISPATCH(call64, call32) (((orc_any*)h)->precision == ADRP_F64 ? call64 : call32)
+#define H64 ((orc_f64*)((orc_any*)h)->impl)
+#define H32 ((orc_f32*)((orc_any*)h)->impl)
+
+int orc_destroy(void* h) { DISPATCH(destroy_f64(H64), destroy_f32(H32)); free(h); return ADRP_OK; }
+int orc_obs_dim(void* h) { return DISPATCH(H64->O, H32->O); }
+int orc_action_dim(void* h) { return DISPATCH(H64->A, H32->A); }
+int orc_substeps(void* h) { return DISPATCH(H64->S, H32->S); }
+int orc_reset_draws_dim(void* h) { return DISPATCH(reset_draws_dim_f64(H64), reset_draws_dim_f32(H32)); }
+
+int orc_reset(void* h, const uint8_t* env_mask, const void* draws, void* obs)
+{
+    DISPATCH(reset_f64(H64, env_mask, (const double*)draws, (double*)obs),
+             reset_f32(H32, env_mask, (const float*)draws, (float*)obs));
+    return ADRP_OK;
+}
+
+int orc_set_state(void* h, const void* state)
+{
+    DISPATCH((void)memcpy(H64->state, state, sizeof(double) * 20 * (size_t)H64->N * H64->M),
+             (void)memcpy(H32->state, state, sizeof(float) * 20 * (size_t)H32->N * H32->M));
+    return ADRP_OK;
+}
+
+int orc_get_state(void* h, void* state)
+{
+    DISPATCH((void)memcpy(state, H64->state, sizeof(double) * 20 * (size_t)H64->N * H64->M),
+             (void)memcpy(state, H32->state, sizeof(float) * 20 * (size_t)H32->N * H32->M));
+    return ADRP_OK;
+}
+
+/* nthreads <= 1: serial.  Otherwise envs are split over OpenMP threads (the timed CPU baseline). */
+int orc_step(void* h, const void* action, const void* noise, void* obs, void* reward,
+             uint8_t* terminated, uint8_t* truncated, uint8_t* drone_flags, int nthreads)
+{
+    DISPATCH(step_f64(H64, (const double*)action, (const double*)noise, (double*)obs, (double*)reward, terminated, truncated, drone_flags, nthreads),
+             step_f32(H32, (const float*)action, (const float*)noise, (float*)obs, (float*)reward, terminated, truncated, drone_flags, nthreads));
+    return ADRP_OK;
+}
+
+/* DSLPIDControl.computeControl on n rows (known-answer tests against tests/golden/dslpid_kat.npz). */
+int orc_dslpid_control(int precision, int drone_model, const adrp_drone_params* drone, double g, int n, double dt,
+                       const void* pos, const void* quat, const void* vel, const void* tpos, const void* trpy,
+                       const void* tvel, const void* trates, void* ctrl, void* rpm, void* pos_e, void* yaw_e)
+{
+    if (precision == ADRP_F64)
+        dslpid_rows_f64(drone_model, drone, g, n, dt, pos, quat, vel, tpos, trpy, tvel, trates, ctrl, rpm, pos_e, yaw_e);
+    else
+        dslpid_rows_f32(drone_model, drone, g, n, dt, pos, quat, vel, tpos, trpy, tvel, trates, ctrl, rpm, pos_e, yaw_e);
+    return ADRP_OK;
+}

@@ -1,0 +1,51 @@
+"""Shared helpers: load a golden .npz (tests/golden/, produced by the reference's own Python) and
+build the matching adrp_config.  Used by the oracle tests (CPU) and the CUDA parity tests (GPU)."""
+from __future__ import annotations
+
+import json
+import os
+
+import numpy as np
+
+from gym_pybullet_adrp_b200 import _abi
+from gym_pybullet_adrp_b200.utils.enums import DroneModel, Physics
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+CTRL_CASES = ["ctrl_dyn_cf2x_s1", "ctrl_dyn_cf2x_s8_m3", "ctrl_dyn_cf2p_s8", "ctrl_dyn_race_s8",
+              "ctrl_dyn_cf2x_tilted", "ctrl_pyb_cf2x_s1", "ctrl_pyb_cf2x_s8_m2", "ctrl_pyb_cf2p_s8",
+              "ctrl_pyb_race_s8", "ctrl_pyb_gnd_s8", "ctrl_pyb_drag_s8", "ctrl_pyb_dw_s5_m4",
+              "ctrl_pyb_all_s5_m8", "ctrl_pyb_ground_contact"]
+RL_CASES = ["hover_pyb_rpm", "hover_dyn_one_d_rpm", "hover_dyn_pid", "hover_pyb_one_d_pid",
+            "multihover_pyb_rpm_m2", "hover_pyb_rpm_long"]
+PID_CASES = ["pid_dyn_c1", "pid_pyb_c1"]
+
+ACT = {"RPM": _abi.ACT_RPM, "ONE_D_RPM": _abi.ACT_ONE_D_RPM, "PID": _abi.ACT_PID, "ONE_D_PID": _abi.ACT_ONE_D_PID}
+
+
+def load(name):
+    z = np.load(os.path.join(GOLDEN, name + ".npz"))
+    meta = json.loads(str(z["meta"]))
+    return meta, {k: z[k] for k in z.files if k != "meta"}
+
+
+def config_for(meta, precision=_abi.F64, num_envs=1, **over):
+    kind = meta["env"]
+    kw = dict(num_envs=num_envs, num_drones=meta["M"], drone_model=DroneModel[meta["model"]],
+              physics=Physics[meta["physics"]], pyb_freq=meta["pyb_freq"], ctrl_freq=meta["ctrl_freq"],
+              precision=precision, initial_xyzs=meta["init_xyz"], initial_rpys=meta.get("init_rpy"))
+    if kind == "ctrl":
+        kw.update(action_type=_abi.ACT_RPM_RAW, env_kind=_abi.ENV_CTRL)
+    elif kind == "ctrl+dslpid":
+        kw.update(action_type=_abi.ACT_PID_FULL, env_kind=_abi.ENV_CTRL)
+    else:
+        kw.update(action_type=ACT[meta["act"]], env_kind=_abi.ENV_HOVER if kind == "hover" else _abi.ENV_MULTIHOVER,
+                  target_pos=meta["target"] if kind == "multihover" else [meta["target"]])
+    kw.update(over)
+    return _abi.make_config(**kw)
+
+
+def rel_err(a, b, floor=1.0):
+    """max |a-b| / max(|b|, floor) -- relative where the value is large, absolute near zero."""
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), floor)))

@@ -1,0 +1,80 @@
+"""CPU: pin the oracle (oracle/liboracle.so) against the golden vectors produced by the reference's
+own Python code (tests/golden/make_golden.py).  fp64 tolerance 1e-9 relative (north_star)."""
+import numpy as np
+import pytest
+
+from gym_pybullet_adrp_b200 import _abi
+from gym_pybullet_adrp_b200.assets import drone_params
+from gym_pybullet_adrp_b200.utils.enums import DroneModel
+from tests import golden_cases as gc
+from tests.oracle_lib import OracleEnv, dslpid_rows
+
+TOL64 = 1e-9
+
+
+@pytest.mark.parametrize("name", gc.CTRL_CASES)
+def test_ctrl_open_loop_fp64(name):
+    meta, z = gc.load(name)
+    env = OracleEnv(gc.config_for(meta))
+    obs0 = env.reset()
+    assert gc.rel_err(obs0[0], z["obs0"]) < TOL64
+    worst = 0.0
+    for k in range(meta["steps"]):
+        obs, rew, te, tr, _ = env.step(z["actions"][k][None])
+        worst = max(worst, gc.rel_err(obs[0], z["obs"][k]))
+        assert rew[0] == -1 and not te[0] and not tr[0]
+    assert worst < TOL64, f"{name}: {worst:.3e}"
+
+
+@pytest.mark.parametrize("name", gc.RL_CASES)
+def test_rl_aviaries_fp64(name):
+    meta, z = gc.load(name)
+    env = OracleEnv(gc.config_for(meta))
+    obs0 = env.reset()
+    # the reference casts the 12 kinematic entries to float32 (BaseRLAviary.py:312)
+    assert gc.rel_err(obs0[0], z["obs0"]) < 1e-6
+    for k in range(meta["steps"]):
+        obs, rew, te, tr, _ = env.step(z["actions"][k][None].astype(np.float64))
+        assert gc.rel_err(obs[0, :, :12], z["obs"][k][:, :12]) < 1e-6, (name, k)
+        np.testing.assert_array_equal(obs[0, :, 12:], z["obs"][k][:, 12:])      # action buffer: exact
+        assert abs(rew[0] - z["reward"][k]) < 1e-9 * max(1.0, abs(z["reward"][k])), (name, k)
+        assert bool(te[0]) == bool(z["terminated"][k]) and bool(tr[0]) == bool(z["truncated"][k]), (name, k)
+
+
+@pytest.mark.parametrize("name", gc.PID_CASES)
+def test_closed_loop_dslpid_fp64(name):
+    """BASELINE config 1 (examples/pid.py driver loop), fused as ACT_PID_FULL."""
+    meta, z = gc.load(name)
+    env = OracleEnv(gc.config_for(meta))
+    env.reset()
+    st = np.zeros((1, 1, 20))
+    o = z["obs"][0]
+    st[0, 0, 0:7], st[0, 0, 7:10], st[0, 0, 10:13], st[0, 0, 16:20] = o[0:7], o[10:13], o[13:16], o[16:20]
+    env.set_state(st)
+    act = np.zeros((1, 1, 12))
+    act[0, 0, 0:3] = meta["target"]
+    worst = 0.0
+    for k in range(1, meta["steps"]):
+        obs, *_ = env.step(act)
+        worst = max(worst, gc.rel_err(obs[0, 0], z["obs"][k]))
+        assert gc.rel_err(obs[0, 0, 16:20], z["rpm"][k - 1]) < TOL64
+    assert worst < TOL64, f"{name}: {worst:.3e}"
+    assert abs(z["obs"][-1][2] - 1.0) < 0.1 or name != "pid_dyn_c1"    # it does reach the hover target
+
+
+def test_dslpid_known_answers_fp64():
+    _, z = gc.load("dslpid_kat")
+    rows = z["rows"]
+    for row in rows:
+        ctrl = np.zeros((1, 9))
+        for call in range(2):
+            r = row[call * 41:(call + 1) * 41]
+            cf2p, dt = int(r[0]), r[1]
+            pos, quat, vel, tpos, trpy, tvel, trates = r[2:5], r[5:9], r[9:12], r[12:15], r[15:18], r[18:21], r[21:24]
+            out = r[24:41]
+            model = DroneModel.CF2P if cf2p else DroneModel.CF2X
+            rpm, pos_e, yaw_e, ctrl = dslpid_rows(_abi.F64, _abi.MODEL_ID[model], _abi.drone_params_c(drone_params(model)),
+                                                  1, dt, pos[None], quat[None], vel[None], tpos[None], trpy[None],
+                                                  tvel[None], trates[None], ctrl)
+            got = np.r_[rpm[0], pos_e[0], yaw_e[0], ctrl[0]]
+            assert gc.rel_err(got, out) < TOL64, (cf2p, call, got - out)
