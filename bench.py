@@ -1,0 +1,290 @@
+#!/usr/bin/env python
+"""bench.py -- drone-steps/s of the fused control-step kernel (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c5|c2|c4] [--impl reference]
+
+One "step" = one control step (S fused physics substeps) of every drone of the workload.  Default
+workload C5 (BASELINE.json configs[4], the scaling sweep the metric is quoted on): 2^20 drones per GPU,
+131072 envs x 8 CF2X drones, DYN + ground effect + drag + downwash, 240/30 Hz (S = 8), random RPM
+actions, CtrlAviary observation.  Weak scaling: every rank owns its own env range, no collective on the
+step path.  See DESIGN.md section "Measurement" for the roofline byte count.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from gym_pybullet_adrp_b200 import _abi  # noqa: E402
+from gym_pybullet_adrp_b200.utils.enums import DroneModel, Physics  # noqa: E402
+
+HOVER_RPM = float(np.sqrt(9.8 * 0.03454 / (4 * 3.16e-10)))
+WORKLOADS = {
+    # name: (envs per GPU, drones per env, physics, pyb, ctrl, env kind, action type, description)
+    "c5": (131072, 8, Physics.DYN_GND_DRAG_DW, 240, 30, _abi.ENV_CTRL, _abi.ACT_RPM_RAW,
+           "C5: 2^20 CF2X drones/GPU (131072 envs x 8), DYN+GND+DRAG+DW, 240/30 Hz, random RPM, obs (N,8,20)"),
+    "c4": (32768, 8, Physics.PYB_GND_DRAG_DW, 240, 48, _abi.ENV_CTRL, _abi.ACT_RPM_RAW,
+           "C4: 32768 envs x 8 CF2X, PYB_GND_DRAG_DW, 240/48 Hz, open-loop RPM, obs (N,8,20)"),
+    "c2": (65536, 1, Physics.PYB, 240, 30, _abi.ENV_HOVER, _abi.ACT_RPM,
+           "C2: HoverAviary 65536 envs x 1 CF2X, PYB, 240/30 Hz, RPM actions in [-1,1], obs (N,1,72), auto-reset"),
+}
+
+
+def make_cfg(wl, n_envs, device=0, env_offset=0):
+    N, M, phy, pyb, ctrl, kind, act, _ = WORKLOADS[wl]
+    xyz = [[0.3 * (k % 3), 0.3 * (k // 3), 0.5 + 0.25 * (k % 4)] for k in range(M)] if M > 1 else None
+    return _abi.make_config(num_envs=n_envs, num_drones=M, drone_model=DroneModel.CF2X, physics=phy, pyb_freq=pyb,
+                            ctrl_freq=ctrl, action_type=act, env_kind=kind, precision=_abi.F32, device=device,
+                            initial_xyzs=xyz, auto_reset=(kind != _abi.ENV_CTRL), seed=5, env_offset=env_offset)
+
+
+def make_actions(wl, n_envs, M, A, seed, count):
+    rng = np.random.default_rng(seed)
+    u = rng.uniform(-1, 1, (count, n_envs, M, A)).astype(np.float32)
+    if WORKLOADS[wl][6] == _abi.ACT_RPM_RAW:
+        return (HOVER_RPM * (1 + 0.05 * u)).astype(np.float32)      # rpm = HOVER_RPM (1 + 0.05 a), BaseRLAviary.py:192
+    return u
+
+
+def initial_state(wl, n_envs, M, seed):
+    """C5: start heights U(0.2, 1.5), xy on a 0.3 m grid per env."""
+    rng = np.random.default_rng(seed)
+    st = np.zeros((n_envs, M, 20), np.float32)
+    k = np.arange(M)
+    st[:, :, 0] = 0.3 * (k % 3)
+    st[:, :, 1] = 0.3 * (k // 3)
+    st[:, :, 2] = rng.uniform(0.2, 1.5, (n_envs, M))
+    st[:, :, 6] = 1.0
+    return st
+
+
+def algorithmic_bytes_per_drone_step(wl, O, A, M):
+    """fp32 bytes that MUST cross HBM per drone per control step (DESIGN.md 'Measurement')."""
+    phy = _abi.PHYSICS_MASK[WORKLOADS[wl][2]]
+    state_rd = 17                                        # pos3 quat4 vel3 (rates3 | ang_v3) last_rpm4
+    state_wr = 20 if phy & _abi.PHY_DYN else 17          # DYN also stores world ang_v next to the body rates
+    ring = 0
+    if WORKLOADS[wl][5] != _abi.ENV_CTRL:
+        ring = (O - 12) + A                               # read the action buffer once, write the newest slot
+    per_drone = 4 * (state_rd + A + state_wr + O + ring) + 1
+    per_env = 4 + 2 + 4 + 4                               # reward, two flag bytes, step counter read+write
+    return per_drone + per_env / M
+
+
+class ClockSampler(threading.Thread):
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.samples, self.reasons, self.max_mhz = index, False, [], set(), None
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                     nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                     nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                     nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+            while not self.stop_flag:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+                time.sleep(0.02)
+        except Exception as e:  # noqa: BLE001
+            self.reasons.add(f"nvml_unavailable:{type(e).__name__}")
+
+    def result(self):
+        return {"sm_mhz": float(np.median(self.samples)) if self.samples else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons)}
+
+
+def cpu_port_rate(wl, n_envs_sample, steps, threads):
+    """Oracle (CPU port of the reference arithmetic) on a bounded sample of the same workload."""
+    from tests.oracle_lib import OracleEnv
+    N, M = n_envs_sample, WORKLOADS[wl][1]
+    cfg = make_cfg(wl, N)
+    env = OracleEnv(cfg)
+    if WORKLOADS[wl][5] == _abi.ENV_CTRL:
+        env.set_state(initial_state(wl, N, M, 5))
+    acts = make_actions(wl, N, M, env.A, 5, 2)
+    env.step(acts[0], nthreads=threads)
+    t0 = time.perf_counter()
+    for k in range(steps):
+        env.step(acts[k % 2], nthreads=threads)
+    dt = time.perf_counter() - t0
+    env.close()
+    return N * M * steps / dt, dt
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU arithmetic (oracle port; the reference itself needs
+    PyBullet, which is not installable here or on the GPU box) on all host cores, bounded sample."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = len(os.sched_getaffinity(0))
+    wl = args.workload
+    M, S = WORKLOADS[wl][1], WORKLOADS[wl][3] // WORKLOADS[wl][4]
+    n_sample = 8192 if M > 1 else 65536
+    for _ in range(max(args.warmup, 1)):
+        cpu_port_rate(wl, n_sample, 1, threads)
+    rate, dt = cpu_port_rate(wl, n_sample, args.steps, threads)
+    sample = f"{n_sample} envs x {M} drones x {args.steps} control steps of the workload, OpenMP over envs"
+    print(json.dumps({
+        "impl": "reference", "metric": "drone_steps_per_s", "value": rate, "unit": "drone-steps/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOADS[wl][7], "sample": sample},
+        "cpu_baseline": {"value": rate, "unit": "drone-steps/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": rate, "unit": "drone-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "substep_updates_per_s": rate * S}))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--workload", default="c5", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--envs-per-gpu", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    from gym_pybullet_adrp_b200 import _lib
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    wl = args.workload
+    N = args.envs_per_gpu or WORKLOADS[wl][0]
+    M = WORKLOADS[wl][1]
+    S = WORKLOADS[wl][3] // WORKLOADS[wl][4]
+    h = _lib.Handle(make_cfg(wl, N, device=local, env_offset=rank * N))
+    if WORKLOADS[wl][5] == _abi.ENV_CTRL:
+        h.set_state(initial_state(wl, N, M, 5 + rank))
+    pool = 4
+    acts_np = make_actions(wl, N, M, h.A, 5 + rank, pool)
+    acts_dev = [torch.as_tensor(a, device=h.device) for a in acts_np]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---------------- device-resident throughput ("value")
+    for k in range(max(args.warmup, 3)):
+        h.step(acts_dev[k % pool])
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = h.launch_count
+    e0.record()
+    for k in range(args.steps):
+        h.step(acts_dev[k % pool])
+    e1.record()
+    barrier()
+    sampler.stop_flag = True
+    launches = h.launch_count - l0
+    ms = torch.tensor([e0.elapsed_time(e1)], device=h.device, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    value = world * N * M * args.steps / (ms_total * 1e-3)
+
+    # ---------------- kernel-only time for the roofline (CUDA events on the launching stream)
+    h.set_profiling(True)
+    for k in range(min(args.steps, 50)):
+        h.step(acts_dev[k % pool])
+    torch.cuda.synchronize()
+    kernel_ms = h.step_kernel_ms()
+    h.set_profiling(False)
+
+    # ---------------- end to end through the host-buffer call (H2D + kernel + D2H every step)
+    e2e_steps = max(3, min(args.steps, 20))
+    for k in range(3):
+        h.step_host(acts_np[k % pool])
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(e2e_steps):
+        out = h.step_host(acts_np[k % pool])
+    barrier()
+    t_e2e = torch.tensor([time.perf_counter() - t0], device=h.device, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
+    e2e_value = world * N * M * e2e_steps / float(t_e2e.item())
+    isz = 4
+    h2d = N * M * h.A * isz
+    d2h = N * M * h.O * isz + N * isz + 2 * N + N * M
+
+    # ---------------- optional episode statistics reduce (the only collective; off the step path)
+    stats = torch.stack([h.obs[:, :, 2].double().mean(), h.reward.double().mean()])
+    if world > 1:
+        dist.all_reduce(stats)
+        stats /= world
+
+    if rank == 0:
+        peaks = {}
+        try:
+            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+                peaks = json.load(f)
+        except OSError:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        bpd = algorithmic_bytes_per_drone_step(wl, h.O, h.A, M)
+        achieved = bpd * N * M / (kernel_ms * 1e-3) / 1e9 if kernel_ms > 0 else None
+        line = {
+            "metric": "drone_steps_per_s", "value": value, "unit": "drone-steps/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOADS[wl][7], "envs_per_gpu": N, "drones_per_env": M, "substeps_per_step": S,
+                       "l2": "working set per step (state+action+obs) exceeds the 126 MB L2" if N * M * bpd > 126e6
+                       else "working set fits L2 (small workload)", "action_pool": pool},
+            "substep_updates_per_s": value * S,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak if achieved else None, "traffic": None,
+                         "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback",
+                         "kernel_ms": kernel_ms, "algorithmic_bytes_per_drone_step": bpd},
+            "e2e": {"value": e2e_value, "unit": "drone-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "steps": e2e_steps},
+            "gpu_launches": launches,
+            "clocks": sampler.result(),
+            "episode_stats": {"mean_z": float(stats[0]), "mean_reward": float(stats[1])},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            threads = len(os.sched_getaffinity(0))
+            n_sample = 8192 if M > 1 else 65536
+            cpu_port_rate(wl, n_sample, 1, threads)
+            # size the sample for ~10-20 s of CPU work
+            r1, d1 = cpu_port_rate(wl, n_sample, 4, threads)
+            steps_cpu = int(max(4, min(400, 12.0 / (d1 / 4))))
+            rate, dt = cpu_port_rate(wl, n_sample, steps_cpu, threads)
+            line["cpu_baseline"] = {"value": rate, "unit": "drone-steps/s", "cores": threads, "kind": "port",
+                                    "sample": f"{n_sample} envs x {M} drones x {steps_cpu} control steps ({dt:.1f} s), fp64, OpenMP over envs"}
+        print(json.dumps(line))
+    h.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

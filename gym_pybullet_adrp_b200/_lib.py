@@ -1,0 +1,193 @@
+"""Loader of the CUDA library (libadrp_b200.so, built in-tree by build.py) and a thin handle class.
+
+There is NO CPU fallback: if the library is missing or a call fails, this raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import _abi
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG_DIR, "libadrp_b200.so")
+
+EXPORTS = ["adrp_create", "adrp_destroy", "adrp_obs_dim", "adrp_action_dim", "adrp_noise_dim",
+           "adrp_reset_draws_dim", "adrp_substeps", "adrp_reset", "adrp_set_state", "adrp_get_state",
+           "adrp_step", "adrp_step_host", "adrp_dslpid_control", "adrp_launch_count", "adrp_set_profiling",
+           "adrp_step_kernel_ms", "adrp_last_error", "adrp_abi_version", "adrp_config_size"]
+
+_lib = None
+
+
+class AdrpError(RuntimeError):
+    pass
+
+
+def load():
+    """dlopen the CUDA library and declare the C signatures of include/adrp.h."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise AdrpError(f"{LIB_PATH} not found: build it with `python -m gym_pybullet_adrp_b200.build` "
+                        "(nvcc, sm_100a). There is no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    vp, u8p = C.c_void_p, C.c_void_p
+    lib.adrp_create.argtypes = [C.POINTER(_abi.ConfigC), C.POINTER(vp)]
+    lib.adrp_destroy.argtypes = [vp]
+    for f in ("adrp_obs_dim", "adrp_action_dim", "adrp_noise_dim", "adrp_reset_draws_dim", "adrp_substeps"):
+        getattr(lib, f).argtypes = [vp]
+    lib.adrp_reset.argtypes = [vp, u8p, vp, vp, vp]
+    lib.adrp_set_state.argtypes = [vp, vp, vp]
+    lib.adrp_get_state.argtypes = [vp, vp, vp]
+    lib.adrp_step.argtypes = [vp, vp, vp, vp, vp, u8p, u8p, u8p, vp]
+    lib.adrp_step_host.argtypes = [vp, vp, vp, vp, u8p, u8p, u8p]
+    lib.adrp_dslpid_control.argtypes = [C.c_int, C.c_int, C.POINTER(_abi.DroneParamsC), C.c_double, C.c_int,
+                                        C.c_double] + [vp] * 12
+    lib.adrp_launch_count.argtypes = [vp]
+    lib.adrp_launch_count.restype = C.c_int64
+    lib.adrp_set_profiling.argtypes = [vp, C.c_int]
+    lib.adrp_step_kernel_ms.argtypes = [vp, C.c_int]
+    lib.adrp_step_kernel_ms.restype = C.c_double
+    lib.adrp_last_error.argtypes = [vp]
+    lib.adrp_last_error.restype = C.c_char_p
+    if lib.adrp_abi_version() != _abi.ABI_VERSION or lib.adrp_config_size() != C.sizeof(_abi.ConfigC):
+        raise AdrpError("libadrp_b200.so does not match include/adrp.h as mirrored in _abi.py (rebuild)")
+    _lib = lib
+    return lib
+
+
+def _torch():
+    import torch
+    return torch
+
+
+class Handle:
+    """Owns one adrp_handle; all tensors are torch CUDA tensors on the handle's device."""
+
+    def __init__(self, cfg: _abi.ConfigC):
+        self.lib = load()
+        self.cfg = cfg
+        self._h = C.c_void_p()
+        rc = self.lib.adrp_create(C.byref(cfg), C.byref(self._h))
+        if rc != 0:
+            msg = self.lib.adrp_last_error(None).decode()
+            if rc == _abi_EINVAL and "divisible" in msg:
+                raise ValueError(msg)
+            raise AdrpError(f"adrp_create failed ({rc}): {msg}")
+        torch = _torch()
+        self.device = torch.device("cuda", cfg.device)
+        self.dtype = torch.float64 if cfg.precision == _abi.F64 else torch.float32
+        self.np_dtype = np.float64 if cfg.precision == _abi.F64 else np.float32
+        self.N, self.M = cfg.num_envs, cfg.drones_per_env
+        self.O = self.lib.adrp_obs_dim(self._h)
+        self.A = self.lib.adrp_action_dim(self._h)
+        self.S = self.lib.adrp_substeps(self._h)
+        self.R = self.lib.adrp_reset_draws_dim(self._h)
+        self.obs = torch.zeros((self.N, self.M, self.O), dtype=self.dtype, device=self.device)
+        self.reward = torch.zeros(self.N, dtype=self.dtype, device=self.device)
+        self.terminated = torch.zeros(self.N, dtype=torch.uint8, device=self.device)
+        self.truncated = torch.zeros(self.N, dtype=torch.uint8, device=self.device)
+        self.flags = torch.zeros((self.N, self.M), dtype=torch.uint8, device=self.device)
+
+    # ------------------------------------------------------------------ helpers
+    def _check(self, rc, what):
+        if rc != 0:
+            raise AdrpError(f"{what} failed ({rc}): {self.lib.adrp_last_error(self._h).decode()}")
+
+    def _stream(self):
+        return C.c_void_p(_torch().cuda.current_stream(self.device).cuda_stream)
+
+    def _dev(self, x, shape):
+        torch = _torch()
+        t = torch.as_tensor(x, dtype=self.dtype, device=self.device).contiguous()
+        if tuple(t.shape) != tuple(shape):
+            t = t.reshape(shape)
+        return t
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.lib.adrp_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ API
+    def reset(self, env_mask=None, draws=None):
+        torch = _torch()
+        m = None if env_mask is None else torch.as_tensor(env_mask, dtype=torch.uint8, device=self.device).contiguous()
+        dr = None if draws is None else self._dev(draws, (self.N, self.R))
+        self._check(self.lib.adrp_reset(self._h, None if m is None else m.data_ptr(),
+                                        None if dr is None else dr.data_ptr(), self.obs.data_ptr(), self._stream()),
+                    "adrp_reset")
+        return self.obs
+
+    def set_state(self, state):
+        s = self._dev(state, (self.N, self.M, _abi.STATE_DIM))
+        self._check(self.lib.adrp_set_state(self._h, s.data_ptr(), self._stream()), "adrp_set_state")
+
+    def get_state(self):
+        torch = _torch()
+        s = torch.empty((self.N, self.M, _abi.STATE_DIM), dtype=self.dtype, device=self.device)
+        self._check(self.lib.adrp_get_state(self._h, s.data_ptr(), self._stream()), "adrp_get_state")
+        return s
+
+    def step(self, action, noise=None):
+        """Device path: ``action`` is (or is copied to) a CUDA tensor; outputs are the handle's tensors."""
+        a = self._dev(action, (self.N, self.M, self.A))
+        nz = None if noise is None else self._dev(noise, (self.N, self.M, self.S, 7))
+        self._check(self.lib.adrp_step(self._h, a.data_ptr(), None if nz is None else nz.data_ptr(),
+                                       self.obs.data_ptr(), self.reward.data_ptr(), self.terminated.data_ptr(),
+                                       self.truncated.data_ptr(), self.flags.data_ptr(), self._stream()), "adrp_step")
+        return self.obs, self.reward, self.terminated, self.truncated, self.flags
+
+    def step_host(self, action: np.ndarray):
+        """Host path (NumPy in, NumPy out): H2D, launch, D2H inside the C call."""
+        a = np.ascontiguousarray(action, self.np_dtype).reshape(self.N, self.M, self.A)
+        if not hasattr(self, "_hbuf"):
+            self._hbuf = (np.empty((self.N, self.M, self.O), self.np_dtype), np.empty(self.N, self.np_dtype),
+                          np.empty(self.N, np.uint8), np.empty(self.N, np.uint8), np.empty((self.N, self.M), np.uint8))
+        o, r, te, tr, fl = self._hbuf
+        self._check(self.lib.adrp_step_host(self._h, a.ctypes.data, o.ctypes.data, r.ctypes.data, te.ctypes.data,
+                                            tr.ctypes.data, fl.ctypes.data), "adrp_step_host")
+        return o, r, te, tr, fl
+
+    def set_profiling(self, on=True):
+        self._check(self.lib.adrp_set_profiling(self._h, int(on)), "adrp_set_profiling")
+
+    def step_kernel_ms(self, reset=True):
+        return self.lib.adrp_step_kernel_ms(self._h, int(reset))
+
+    @property
+    def launch_count(self):
+        return int(self.lib.adrp_launch_count(self._h))
+
+
+_abi_EINVAL = -1
+
+
+def dslpid_control(precision, drone_model, n, dt, pos, quat, vel, tpos, trpy, tvel, trates, ctrl, device=0):
+    """Batched DSLPIDControl.computeControl on the GPU (torch tensors in / out; ``ctrl`` updated in place)."""
+    from .assets import drone_params
+    torch = _torch()
+    lib = load()
+    dtype = torch.float64 if precision == _abi.F64 else torch.float32
+    dev = torch.device("cuda", device)
+    ts = [torch.as_tensor(x, dtype=dtype, device=dev).contiguous() for x in (pos, quat, vel, tpos, trpy, tvel, trates)]
+    rpm = torch.empty((n, 4), dtype=dtype, device=dev)
+    pos_e = torch.empty((n, 3), dtype=dtype, device=dev)
+    yaw_e = torch.empty(n, dtype=dtype, device=dev)
+    dp = _abi.drone_params_c(drone_params(drone_model))
+    rc = lib.adrp_dslpid_control(precision, _abi.MODEL_ID[drone_model], C.byref(dp), 9.8, n, float(dt),
+                                 *[t.data_ptr() for t in ts], ctrl.data_ptr(), rpm.data_ptr(), pos_e.data_ptr(),
+                                 yaw_e.data_ptr(), C.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
+    if rc != 0:
+        raise AdrpError(f"adrp_dslpid_control failed ({rc})")
+    return rpm, pos_e, yaw_e

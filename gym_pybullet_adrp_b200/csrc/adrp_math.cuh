@@ -1,0 +1,129 @@
+// adrp_math.cuh -- scalar helpers of the fused step kernel (float and double instantiations).
+//
+// Quaternion order is xyzw (PyBullet).  The closed forms follow the call sites of the reference:
+//   rotmat       p.getMatrixFromQuaternion  (envs/BaseAviary.py:778,843; control/DSLPIDControl.py:187,240)
+//   euler_rpy    p.getEulerFromQuaternion   (envs/BaseAviary.py:522; control/DSLPIDControl.py:144,241)
+//   quat_from_rpy p.getQuaternionFromEuler  (envs/BaseAviary.py:492)
+//   canon_quat   the reset->get pose round trip of a Bullet body (envs/BaseAviary.py:869-873 then :521)
+#pragma once
+#include <cuda_runtime.h>
+#include <math.h>
+
+namespace adrp {
+
+template <typename T> struct M;
+template <> struct M<float> {
+    static __device__ __forceinline__ float sqrt(float x) { return sqrtf(x); }
+    static __device__ __forceinline__ float rsqrt(float x) { return rsqrtf(x); }
+    static __device__ __forceinline__ float sin(float x) { return sinf(x); }
+    static __device__ __forceinline__ float cos(float x) { return cosf(x); }
+    static __device__ __forceinline__ void sincos(float x, float* s, float* c) { sincosf(x, s, c); }
+    static __device__ __forceinline__ float atan2(float y, float x) { return atan2f(y, x); }
+    static __device__ __forceinline__ float asin(float x) { return asinf(x); }
+    static __device__ __forceinline__ float exp(float x) { return expf(x); }
+    static __device__ __forceinline__ float abs(float x) { return fabsf(x); }
+    static __device__ __forceinline__ float tan(float x) { return tanf(x); }
+    static __device__ __forceinline__ float fmax(float a, float b) { return fmaxf(a, b); }
+    static __device__ __forceinline__ float fmin(float a, float b) { return fminf(a, b); }
+};
+template <> struct M<double> {
+    static __device__ __forceinline__ double sqrt(double x) { return ::sqrt(x); }
+    static __device__ __forceinline__ double rsqrt(double x) { return 1.0 / ::sqrt(x); }
+    static __device__ __forceinline__ double sin(double x) { return ::sin(x); }
+    static __device__ __forceinline__ double cos(double x) { return ::cos(x); }
+    static __device__ __forceinline__ void sincos(double x, double* s, double* c) { ::sincos(x, s, c); }
+    static __device__ __forceinline__ double atan2(double y, double x) { return ::atan2(y, x); }
+    static __device__ __forceinline__ double asin(double x) { return ::asin(x); }
+    static __device__ __forceinline__ double exp(double x) { return ::exp(x); }
+    static __device__ __forceinline__ double abs(double x) { return ::fabs(x); }
+    static __device__ __forceinline__ double tan(double x) { return ::tan(x); }
+    static __device__ __forceinline__ double fmax(double a, double b) { return ::fmax(a, b); }
+    static __device__ __forceinline__ double fmin(double a, double b) { return ::fmin(a, b); }
+};
+
+template <typename T> __device__ __forceinline__ T clampT(T v, T lo, T hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+template <typename T> struct V3 { T x, y, z; };
+template <typename T> struct Q4 { T x, y, z, w; };
+template <typename T> struct Mat3 { T m00, m01, m02, m10, m11, m12, m20, m21, m22; };
+
+template <typename T> __device__ __forceinline__ V3<T> cross(const V3<T>& a, const V3<T>& b)
+{
+    return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x};
+}
+template <typename T> __device__ __forceinline__ T dot(const V3<T>& a, const V3<T>& b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+template <typename T> __device__ __forceinline__ V3<T> mul(const Mat3<T>& R, const V3<T>& v)
+{
+    return {R.m00 * v.x + R.m01 * v.y + R.m02 * v.z, R.m10 * v.x + R.m11 * v.y + R.m12 * v.z,
+            R.m20 * v.x + R.m21 * v.y + R.m22 * v.z};
+}
+template <typename T> __device__ __forceinline__ V3<T> mulT(const Mat3<T>& R, const V3<T>& v)
+{
+    return {R.m00 * v.x + R.m10 * v.y + R.m20 * v.z, R.m01 * v.x + R.m11 * v.y + R.m21 * v.z,
+            R.m02 * v.x + R.m12 * v.y + R.m22 * v.z};
+}
+
+// btMatrix3x3::setRotation: normalises by 2/|q|^2.
+template <typename T> __device__ __forceinline__ Mat3<T> rotmat(const Q4<T>& q)
+{
+    const T d = q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w;
+    const T s = T(2) / d;
+    const T xs = q.x * s, ys = q.y * s, zs = q.z * s;
+    const T wx = q.w * xs, wy = q.w * ys, wz = q.w * zs;
+    const T xx = q.x * xs, xy = q.x * ys, xz = q.x * zs;
+    const T yy = q.y * ys, yz = q.y * zs, zz = q.z * zs;
+    return {T(1) - (yy + zz), xy - wz, xz + wy, xy + wz, T(1) - (xx + zz), yz - wx, xz - wy, yz + wx, T(1) - (xx + yy)};
+}
+
+// pybullet.getEulerFromQuaternion, including its gimbal-lock branches.
+template <typename T> __device__ __forceinline__ V3<T> euler_rpy(const Q4<T>& q)
+{
+    const T sqx = q.x * q.x, sqy = q.y * q.y, sqz = q.z * q.z, squ = q.w * q.w;
+    const T sarg = T(-2) * (q.x * q.z - q.w * q.y);
+    const T HALF_PI = T(1.5707963267948966);
+    if (sarg <= T(-0.99999)) return {T(0), -HALF_PI, T(2) * M<T>::atan2(q.x, -q.y)};
+    if (sarg >= T(0.99999)) return {T(0), HALF_PI, T(2) * M<T>::atan2(-q.x, q.y)};
+    return {M<T>::atan2(T(2) * (q.y * q.z + q.w * q.x), squ - sqx - sqy + sqz), M<T>::asin(sarg),
+            M<T>::atan2(T(2) * (q.x * q.y + q.w * q.z), squ + sqx - sqy - sqz)};
+}
+
+// |roll| < pi/2 and |pitch| < pi/2 (the _groundEffect gate, envs/BaseAviary.py:749) without
+// evaluating atan2/asin: roll = atan2(s, c) lies in (-pi/2, pi/2) iff c > 0 or s == c == 0;
+// the gimbal branches return pitch = +-pi/2 exactly, which fails the strict inequality.
+template <typename T> __device__ __forceinline__ bool level_enough(const Q4<T>& q)
+{
+    const T sarg = T(-2) * (q.x * q.z - q.w * q.y);
+    if (sarg <= T(-0.99999) || sarg >= T(0.99999)) return false;
+    const T c = q.w * q.w - q.x * q.x - q.y * q.y + q.z * q.z;
+    const T s = T(2) * (q.y * q.z + q.w * q.x);
+    return c > T(0) || (c == T(0) && s == T(0));
+}
+
+template <typename T> __device__ __forceinline__ Q4<T> quat_from_rpy(const V3<T>& e)
+{
+    T sp, cp, st, ct, ss, cs;
+    M<T>::sincos(e.x / T(2), &sp, &cp);
+    M<T>::sincos(e.y / T(2), &st, &ct);
+    M<T>::sincos(e.z / T(2), &ss, &cs);
+    Q4<T> q = {sp * ct * cs - cp * st * ss, cp * st * cs + sp * ct * ss, cp * ct * ss - sp * st * cs,
+               cp * ct * cs + sp * st * ss};
+    const T len = M<T>::sqrt(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
+    return {q.x / len, q.y / len, q.z / len, q.w / len};
+}
+
+// Normalised, sign-canonical quaternion: equals btMatrix3x3(q).getRotation() up to rounding.
+// trace = 4w^2/|q|^2 - 1 > 0 keeps w positive; otherwise the component picked by Bullet's
+// diagonal comparison chain (m00 < m11 <=> x^2 < y^2 ...) is made positive.
+template <typename T> __device__ __forceinline__ Q4<T> canon_quat(const Q4<T>& q)
+{
+    const T xx = q.x * q.x, yy = q.y * q.y, zz = q.z * q.z, ww = q.w * q.w;
+    const T d = xx + yy + zz + ww;
+    T inv = T(1) / M<T>::sqrt(d);
+    T pivot;
+    if (T(4) * ww > d) pivot = q.w;                                   // trace > 0
+    else pivot = xx < yy ? (yy < zz ? q.z : q.y) : (xx < zz ? q.z : q.x);
+    if (pivot < T(0)) inv = -inv;
+    return {q.x * inv, q.y * inv, q.z * inv, q.w * inv};
+}
+
+}  // namespace adrp

@@ -1,0 +1,301 @@
+// adrp_step.cuh -- the fused control-step kernel: one thread per drone, S substeps in registers.
+//
+// Replaces BaseAviary.step (envs/BaseAviary.py:262-387) for the Ctrl / Hover / MultiHover aviaries:
+// action map (_preprocessAction), optional DSLPID, S x {force models, integrator}, then observation,
+// reward, terminated / truncated -- one launch, state read once and written once.
+#pragma once
+#include "adrp_dslpid.cuh"
+#include "adrp_physics.cuh"
+
+namespace adrp {
+
+constexpr int kBlock = 128;
+
+template <typename T> __device__ __forceinline__ T ld(const T* base, long long D, int field, long long t) { return base[(long long)field * D + t]; }
+template <typename T> __device__ __forceinline__ void st(T* base, long long D, int field, long long t, T v) { base[(long long)field * D + t] = v; }
+
+template <typename T>
+__device__ __forceinline__ void load_drone(const KBuffers<T>& b, long long D, long long t, Drone<T>& d)
+{
+    const T* s = b.state;
+    d.p = {ld(s, D, F_PX, t), ld(s, D, F_PY, t), ld(s, D, F_PZ, t)};
+    d.q = {ld(s, D, F_QX, t), ld(s, D, F_QY, t), ld(s, D, F_QZ, t), ld(s, D, F_QW, t)};
+    d.v = {ld(s, D, F_VX, t), ld(s, D, F_VY, t), ld(s, D, F_VZ, t)};
+    d.w = {ld(s, D, F_WX, t), ld(s, D, F_WY, t), ld(s, D, F_WZ, t)};
+    d.rt = {ld(s, D, F_RX, t), ld(s, D, F_RY, t), ld(s, D, F_RZ, t)};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) d.last_rpm[k] = ld(s, D, F_RPM0 + k, t);
+}
+
+template <typename T>
+__device__ __forceinline__ void store_drone(const KBuffers<T>& b, long long D, long long t, const Drone<T>& d)
+{
+    T* s = b.state;
+    st(s, D, F_PX, t, d.p.x); st(s, D, F_PY, t, d.p.y); st(s, D, F_PZ, t, d.p.z);
+    st(s, D, F_QX, t, d.q.x); st(s, D, F_QY, t, d.q.y); st(s, D, F_QZ, t, d.q.z); st(s, D, F_QW, t, d.q.w);
+    st(s, D, F_VX, t, d.v.x); st(s, D, F_VY, t, d.v.y); st(s, D, F_VZ, t, d.v.z);
+    st(s, D, F_WX, t, d.w.x); st(s, D, F_WY, t, d.w.y); st(s, D, F_WZ, t, d.w.z);
+    st(s, D, F_RX, t, d.rt.x); st(s, D, F_RY, t, d.rt.y); st(s, D, F_RZ, t, d.rt.z);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) st(s, D, F_RPM0 + k, t, d.last_rpm[k]);
+}
+
+template <typename T>
+__device__ __forceinline__ void init_drone(const KParams<T>& P, int i, Drone<T>& d)
+{
+    d.p = {P.init_xyz[i][0], P.init_xyz[i][1], P.init_xyz[i][2]};
+    d.q = {P.init_quat[i][0], P.init_quat[i][1], P.init_quat[i][2], P.init_quat[i][3]};
+    d.v = {P.init_vel[i][0], P.init_vel[i][1], P.init_vel[i][2]};
+    d.w = {P.init_pqr[i][0], P.init_pqr[i][1], P.init_pqr[i][2]};
+    d.rt = {T(0), T(0), T(0)};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) d.last_rpm[k] = T(0);
+}
+
+// sum over the Mpad lanes of one env (Mpad is a power of two <= 32)
+template <typename T> __device__ __forceinline__ T group_sum(T v, int Mpad)
+{
+    for (int o = Mpad >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ int group_or(int v, int Mpad)
+{
+    for (int o = Mpad >> 1; o > 0; o >>= 1) v |= __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// PHY_CT >= 0: physics mask known at compile time (specialised kernels); -1: read from the params.
+// ACTC: 0 = RPM-type actions, 1 = DSLPID-type actions.
+template <typename T, int PHY_CT, int ACTC>
+__global__ void __launch_bounds__(kBlock)
+step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* __restrict__ action,
+            T* __restrict__ obs, T* __restrict__ reward, uint8_t* __restrict__ terminated,
+            uint8_t* __restrict__ truncated, uint8_t* __restrict__ drone_flags)
+{
+    const long long t = (long long)blockIdx.x * kBlock + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int i = (int)(t & (P.Mpad - 1));
+    const long long env = t / P.Mpad;
+    const int lane_base = lane - i;
+    const bool valid = env < P.N && i < P.M;
+    const long long D = P.Dpad;
+    const int phy = PHY_CT >= 0 ? PHY_CT : P.physics;
+    const long long od = valid ? env * P.M + i : 0;      // row of this drone in (N, M, .) tensors
+
+    Drone<T> d;
+    if (valid) load_drone(b, D, t, d); else init_drone(P, 0, d);
+
+    // ---- action -> RPM (CtrlAviary.py:140; BaseRLAviary.py:160-239)
+    T rpm[4];
+    const T* a = action + od * P.A;
+    T act_in[12];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) act_in[k] = (valid && k < P.A) ? a[k] : T(0);
+    PidState<T> pc;
+    if (ACTC == 0) {
+        if (P.action_type == ADRP_ACT_RPM_RAW) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) rpm[k] = clampT(act_in[k], T(0), P.max_rpm);
+        } else {
+            // NumPy evaluates (1 + 0.05*a) on the float32 action before promoting (BaseRLAviary.py:192)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float av = (float)act_in[P.action_type == ADRP_ACT_ONE_D_RPM ? 0 : k];
+                rpm[k] = P.hover_rpm * (T)__fadd_rn(1.0f, __fmul_rn(0.05f, av));
+            }
+        }
+    } else {
+        const T* pb = b.pid;
+        pc.ipos = {ld(pb, D, 0, t), ld(pb, D, 1, t), ld(pb, D, 2, t)};
+        pc.irpy = {ld(pb, D, 3, t), ld(pb, D, 4, t), ld(pb, D, 5, t)};
+        pc.last_rpy = {ld(pb, D, 6, t), ld(pb, D, 7, t), ld(pb, D, 8, t)};
+        V3<T> tpos, trpy = {T(0), T(0), T(0)}, tvel = {T(0), T(0), T(0)}, trates = {T(0), T(0), T(0)};
+        if (P.action_type == ADRP_ACT_PID) {
+            // BaseAviary._calculateNextStep (:1112-1154), step_size = 1
+            const V3<T> dir = {act_in[0] - d.p.x, act_in[1] - d.p.y, act_in[2] - d.p.z};
+            const T dist = M<T>::sqrt(dot(dir, dir));
+            if (dist <= T(1)) tpos = {act_in[0], act_in[1], act_in[2]};
+            else tpos = {d.p.x + dir.x / dist * T(1), d.p.y + dir.y / dist * T(1), d.p.z + dir.z / dist * T(1)};
+        } else if (P.action_type == ADRP_ACT_ONE_D_PID) {
+            tpos = {d.p.x, d.p.y, d.p.z + T(0.1) * act_in[0]};                   // :233
+        } else if (P.action_type == ADRP_ACT_VEL) {
+            const T nrm = M<T>::sqrt(act_in[0] * act_in[0] + act_in[1] * act_in[1] + act_in[2] * act_in[2]);   // :208-223
+            const T sc = P.speed_limit * M<T>::abs(act_in[3]);
+            tpos = d.p;
+            trpy.z = euler_rpy(d.q).z;
+            if (nrm != T(0)) tvel = {sc * (act_in[0] / nrm), sc * (act_in[1] / nrm), sc * (act_in[2] / nrm)};
+        } else {                                                                 // ADRP_ACT_PID_FULL
+            tpos = {act_in[0], act_in[1], act_in[2]}; trpy = {act_in[3], act_in[4], act_in[5]};
+            tvel = {act_in[6], act_in[7], act_in[8]}; trates = {act_in[9], act_in[10], act_in[11]};
+        }
+        V3<T> pos_e; T yaw_e;
+        dslpid_control(P.pid_gravity, P.pid_kf, P.pid_model, P.ctrl_dt, d.p, d.q, d.v, tpos, trpy, tvel, trates,
+                       pc, rpm, pos_e, yaw_e);
+    }
+
+    // ---- S fused substeps (BaseAviary.py:347-376)
+    T f0[4], tq[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { f0[k] = rpm[k] * rpm[k] * P.kf; tq[k] = rpm[k] * rpm[k] * P.km; }
+    const T two_pi_60 = T(6.283185307179586) / T(60);
+    for (int s = 0; s < P.S; ++s) {
+        const Mat3<T> R = rotmat(d.q);
+        T f[4] = {f0[0], f0[1], f0[2], f0[3]};
+        if (phy & ADRP_PHY_GND) {
+            T gnd[4];
+            ground_effect(P, d, R, f0, gnd);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) f[k] += gnd[k];
+        }
+        V3<T> fext = {T(0), T(0), T(0)};
+        if (phy & ADRP_PHY_DRAG) {
+            // _drag uses last_clipped_action: the previous step's RPM during the first substep (:363,:376)
+            const T sum = (T(2) * T(3.141592653589793) * d.last_rpm[0] / T(60) + T(2) * T(3.141592653589793) * d.last_rpm[1] / T(60)) +
+                          T(2) * T(3.141592653589793) * d.last_rpm[2] / T(60) + T(2) * T(3.141592653589793) * d.last_rpm[3] / T(60);
+            (void)two_pi_60;
+            fext = {-P.drag_xy * sum * d.v.x, -P.drag_xy * sum * d.v.y, -P.drag_z * sum * d.v.z};
+        }
+        T dw = T(0);
+        if (phy & ADRP_PHY_DW) dw = downwash(P, d.p, lane_base, valid);
+        if (phy & ADRP_PHY_DYN) {
+            dyn_substep(P, d, R, f, tq, dw, fext);
+        } else {
+            const T fz = (f[0] + f[1] + f[2] + f[3]) + dw;
+            const V3<T> tb = {P.prop_y[0] * f[0] + P.prop_y[1] * f[1] + P.prop_y[2] * f[2] + P.prop_y[3] * f[3],
+                              -(P.prop_x[0] * f[0] + P.prop_x[1] * f[1] + P.prop_x[2] * f[2] + P.prop_x[3] * f[3]),
+                              tq[0] - tq[1] + tq[2] - tq[3]};                   // :703
+            pyb_substep(P, phy, d, R, fz, tb, fext);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) d.last_rpm[k] = rpm[k];                      // :376
+    }
+
+    // ---- observation (CtrlAviary.py:106-117; BaseRLAviary.py:284-322)
+    const V3<T> rpy = euler_rpy(d.q);
+    T* o = obs + od * P.O;
+    int head = 0;
+    if (P.env_kind == ADRP_ENV_CTRL) {
+        if (valid) {
+            o[0] = d.p.x; o[1] = d.p.y; o[2] = d.p.z; o[3] = d.q.x; o[4] = d.q.y; o[5] = d.q.z; o[6] = d.q.w;
+            o[7] = rpy.x; o[8] = rpy.y; o[9] = rpy.z; o[10] = d.v.x; o[11] = d.v.y; o[12] = d.v.z;
+            o[13] = d.w.x; o[14] = d.w.y; o[15] = d.w.z;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) o[16 + k] = d.last_rpm[k];
+        }
+    } else if (valid) {
+        o[0] = d.p.x; o[1] = d.p.y; o[2] = d.p.z; o[3] = rpy.x; o[4] = rpy.y; o[5] = rpy.z;
+        o[6] = d.v.x; o[7] = d.v.y; o[8] = d.v.z; o[9] = d.w.x; o[10] = d.w.y; o[11] = d.w.z;
+        // action buffer (deque(maxlen=ctrl_freq//2), BaseRLAviary.py:66-67,187): the newest action
+        // overwrites the oldest ring slot; the observation lists the slots oldest -> newest
+        head = b.ring_head[env];
+        for (int k = 0; k < P.A; ++k) st(b.ring, D, head * P.A + k, t, act_in[k]);
+        const int nh = head + 1 == P.B ? 0 : head + 1;
+        for (int j = 0; j < P.B; ++j) {
+            int slot = nh + j;
+            if (slot >= P.B) slot -= P.B;
+            for (int k = 0; k < P.A; ++k) o[12 + j * P.A + k] = ld(b.ring, D, slot * P.A + k, t);
+        }
+        head = nh;
+    }
+
+    // ---- reward and flags (HoverAviary.py:68-117; MultiHoverAviary.py:75-130; CtrlAviary.py:144-200)
+    T rew = T(-1);
+    int term = 0, trunc = 0;
+    const int counter = (valid || env < P.N) ? b.step_counter[env < P.N ? env : 0] : 0;
+    if (P.env_kind != ADRP_ENV_CTRL) {
+        T r = T(0), dist = T(0);
+        int tr = 0;
+        if (valid) {
+            const V3<T> e = {P.target[i][0] - d.p.x, P.target[i][1] - d.p.y, P.target[i][2] - d.p.z};
+            dist = M<T>::sqrt(dot(e, e));
+            const T d2 = dist * dist;
+            r = M<T>::fmax(T(0), T(2) - d2 * d2);
+            tr = M<T>::abs(d.p.x) > P.hover_lim || M<T>::abs(d.p.y) > P.hover_lim || d.p.z > T(2) ||
+                 M<T>::abs(rpy.x) > T(.4) || M<T>::abs(rpy.y) > T(.4);
+        }
+        rew = group_sum(r, P.Mpad);
+        term = group_sum(dist, P.Mpad) < T(.0001);
+        trunc = group_or(tr, P.Mpad) | (counter >= P.trunc_steps);
+    }
+    const bool done = P.auto_reset && (term || trunc);
+    if (valid && i == 0) {
+        reward[env] = rew;
+        terminated[env] = (uint8_t)term;
+        truncated[env] = (uint8_t)trunc;
+        b.step_counter[env] = done ? 0 : counter + P.S;                          // BaseAviary.py:386
+        if (P.env_kind != ADRP_ENV_CTRL) b.ring_head[env] = done ? 0 : head;
+    }
+    if (valid && drone_flags) drone_flags[od] = 0;
+
+    // ---- write the state back (re-initialised when the episode ended and auto_reset is on)
+    if (valid) {
+        if (done) {
+            init_drone(P, i, d);
+            pc.ipos = pc.irpy = pc.last_rpy = {T(0), T(0), T(0)};
+            if (P.env_kind != ADRP_ENV_CTRL)
+                for (int k = 0; k < P.B * P.A; ++k) st(b.ring, D, k, t, T(0));
+        }
+        store_drone(b, D, t, d);
+        if (ACTC == 1) {
+            T* pb = b.pid;
+            st(pb, D, 0, t, pc.ipos.x); st(pb, D, 1, t, pc.ipos.y); st(pb, D, 2, t, pc.ipos.z);
+            st(pb, D, 3, t, pc.irpy.x); st(pb, D, 4, t, pc.irpy.y); st(pb, D, 5, t, pc.irpy.z);
+            st(pb, D, 6, t, pc.last_rpy.x); st(pb, D, 7, t, pc.last_rpy.y); st(pb, D, 8, t, pc.last_rpy.z);
+        }
+    }
+}
+
+// (N, M, 20) rows <-> SoA state
+template <typename T>
+__global__ void set_state_kernel(const KParams<T> P, KBuffers<T> b, const T* __restrict__ rows)
+{
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = (int)(t & (P.Mpad - 1));
+    const long long env = t / P.Mpad;
+    if (env >= P.N || i >= P.M) return;
+    const T* r = rows + (env * P.M + i) * ADRP_STATE_DIM;
+    for (int f = 0; f < F_COUNT; ++f) b.state[(long long)f * P.Dpad + t] = r[f];
+}
+
+template <typename T>
+__global__ void get_state_kernel(const KParams<T> P, KBuffers<T> b, T* __restrict__ rows)
+{
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = (int)(t & (P.Mpad - 1));
+    const long long env = t / P.Mpad;
+    if (env >= P.N || i >= P.M) return;
+    T* r = rows + (env * P.M + i) * ADRP_STATE_DIM;
+    for (int f = 0; f < F_COUNT; ++f) r[f] = b.state[(long long)f * P.Dpad + t];
+}
+
+// Env.reset (BaseAviary.py:223-258) for the masked envs; writes the initial observation if asked.
+template <typename T>
+__global__ void reset_kernel(const KParams<T> P, KBuffers<T> b, const uint8_t* __restrict__ mask, T* __restrict__ obs)
+{
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = (int)(t & (P.Mpad - 1));
+    const long long env = t / P.Mpad;
+    if (env >= P.N || i >= P.M) return;
+    if (mask && !mask[env]) return;
+    Drone<T> d;
+    init_drone(P, i, d);
+    store_drone(b, P.Dpad, t, d);
+    for (int k = 0; k < 9; ++k) b.pid[(long long)k * P.Dpad + t] = T(0);
+    for (int k = 0; k < P.B * P.A; ++k) b.ring[(long long)k * P.Dpad + t] = T(0);
+    if (i == 0) { b.step_counter[env] = 0; b.ring_head[env] = 0; }
+    if (obs) {
+        T* o = obs + (env * P.M + i) * P.O;
+        const V3<T> rpy = euler_rpy(d.q);
+        if (P.env_kind == ADRP_ENV_CTRL) {
+            o[0] = d.p.x; o[1] = d.p.y; o[2] = d.p.z; o[3] = d.q.x; o[4] = d.q.y; o[5] = d.q.z; o[6] = d.q.w;
+            o[7] = rpy.x; o[8] = rpy.y; o[9] = rpy.z; o[10] = d.v.x; o[11] = d.v.y; o[12] = d.v.z;
+            o[13] = d.w.x; o[14] = d.w.y; o[15] = d.w.z; o[16] = o[17] = o[18] = o[19] = T(0);
+        } else {
+            o[0] = d.p.x; o[1] = d.p.y; o[2] = d.p.z; o[3] = rpy.x; o[4] = rpy.y; o[5] = rpy.z;
+            o[6] = d.v.x; o[7] = d.v.y; o[8] = d.v.z; o[9] = d.w.x; o[10] = d.w.y; o[11] = d.w.z;
+            for (int k = 12; k < P.O; ++k) o[k] = T(0);
+        }
+    }
+}
+
+}  // namespace adrp
