@@ -13,8 +13,9 @@ from tests.oracle_lib import OracleEnv
 pytestmark = pytest.mark.gpu
 
 TOL64, TOL32 = 1e-9, 1e-4
-# downwash between 8 stacked drones is chaotic (beta crosses zero): fp32 only pinned early
-CHAOTIC = {"ctrl_pyb_all_s5_m8": 6}
+# downwash between 8 stacked drones is chaotic from the first step (beta crosses zero): the fp32
+# trajectory is not comparable to the fp64 golden there; the case stays pinned in fp64
+CHAOTIC = {"ctrl_pyb_all_s5_m8": 0}
 
 
 def _handle(cfg):
