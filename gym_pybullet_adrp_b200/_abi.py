@@ -141,3 +141,64 @@ def make_config(*, num_envs, num_drones=1, drone_model=DroneModel.CF2X, physics=
     c.dslpid_drone = drone_params_c(drone_params(DroneModel.CF2X))
     c.track.contact_margin, c.track.visibility_range = 0.02, 0.45
     return c
+
+
+def make_race_config(race_config, *, num_envs, num_drones=2, drone_model=DroneModel.CF2X, physics=Physics.PYB,
+                     pyb_freq=500, ctrl_freq=25, racemode=RaceMode.COMPARE, precision=F32, device=0, seed=None,
+                     env_offset=0, auto_reset=False, physics_mask=None, mel_mass=0.027) -> ConfigC:
+    """adrp_config for MultiRaceAviary(race_config, ...) (envs/MultiRaceAviary.py:31-123)."""
+    rc = race_config
+    drones = list(rc["init_states"].keys())[:num_drones]
+    if len(drones) < num_drones:
+        raise ValueError("race_config.init_states has fewer entries than num_drones")
+    st = [rc["init_states"][d] for d in drones]
+    c = make_config(num_envs=num_envs, num_drones=num_drones, drone_model=drone_model, physics=physics,
+                    pyb_freq=pyb_freq, ctrl_freq=ctrl_freq, action_type=ACT_MEL, env_kind=ENV_RACE, precision=precision,
+                    device=device, initial_xyzs=[s["pos"] for s in st],
+                    # _drone_init uses the config rpy WITHOUT deg->rad (MultiRaceAviary.py:459, SURVEY E16)
+                    initial_rpys=[s["rpy"] for s in st], initial_vels=[s["vel"] for s in st],
+                    initial_pqrs=[s["pqr"] for s in st], episode_len_sec=rc["episode_len_sec"],
+                    auto_reset=auto_reset, race_mode=racemode, seed=rc.get("seed", 0) if seed is None else seed,
+                    env_offset=env_offset, physics_mask=physics_mask,
+                    body_model="cf2x",            # Bullet mass / inertia from the legacy urdf (:409-416)
+                    mel_mass=mel_mass)
+    t = c.track
+    gates, obst = rc["gates"], rc["obstacles"]
+    if len(gates) > MAX_GATES or len(obst) > MAX_OBSTACLES:
+        raise ValueError("too many gates / obstacles")
+    t.num_gates, t.num_obstacles = len(gates), len(obst)
+    for g, row in enumerate(gates):
+        t.gates[g][0], t.gates[g][1], t.gates[g][2], t.gates[g][3] = row[0], row[1], row[2], row[5]
+        if row[6] not in (0, 1):
+            raise ValueError("Unknown gate type.")                      # MultiRaceAviary.py:483-484
+        t.gate_type[g] = int(row[6])
+    for o, row in enumerate(obst):
+        for k in range(3):
+            t.obstacles[o][k] = row[k]
+    for k in range(3):
+        t.bounds_hi[k] = rc["bounds"][1][k]
+    r = c.rnd
+    r.random_gates_obstacles = int(bool(rc.get("random_gates_obstacles")))
+    r.random_drone_state = int(bool(rc.get("random_drone_state")))
+    r.random_drone_inertia = int(bool(rc.get("random_drone_inertia")))
+    r.disturbances = int(bool(rc.get("disturbances")))
+    if r.random_gates_obstacles:
+        info = rc["random_gates_obstacles_info"]
+        r.gate_range[0], r.gate_range[1] = info["gates"]["range"]
+        r.obstacle_range[0], r.obstacle_range[1] = info["obstacles"]["range"]
+    if r.random_drone_state:
+        info = rc["random_drone_state_info"]
+        for k, ax in enumerate("xyz"):
+            r.pos_range[k][0], r.pos_range[k][1] = info["pos"][ax]
+        for k, ax in enumerate("rpy"):
+            r.rot_range[k][0], r.rot_range[k][1] = info["rot"][ax]
+    if r.random_drone_inertia:
+        info = rc["random_drone_inertia_info"]
+        for field, key in (("mass_range", "M"), ("ixx_range", "Ixx"), ("iyy_range", "Iyy"), ("izz_range", "Izz")):
+            getattr(r, field)[0], getattr(r, field)[1] = info[key]["range"]
+    if r.disturbances:
+        info = rc["disturbances_info"]
+        r.action_noise_std = info["action"]["std"]
+        for k in range(3):
+            r.wind_lo[k], r.wind_hi[k] = info["dynamics"]["low"][k], info["dynamics"]["high"][k]
+    return c

@@ -21,6 +21,7 @@
 #define ATAN2 atan2
 #define ASIN asin
 #define EXP exp
+#define LOG log
 #define TAN tan
 #include "adrp_oracle_impl.h"
 #include "adrp_oracle_race.h"
@@ -34,6 +35,7 @@
 #undef ATAN2
 #undef ASIN
 #undef EXP
+#undef LOG
 #undef TAN
 #undef CAT2
 #undef CAT
@@ -48,6 +50,7 @@
 #define ATAN2 atan2f
 #define ASIN asinf
 #define EXP expf
+#define LOG logf
 #define TAN tanf
 #include "adrp_oracle_impl.h"
 #include "adrp_oracle_race.h"
@@ -116,4 +119,40 @@ int orc_dslpid_control(int precision, int drone_model, const adrp_drone_params* 
     else
         dslpid_rows_f32(drone_model, drone, g, n, dt, pos, quat, vel, tpos, trpy, tvel, trates, ctrl, rpm, pos_e, yaw_e);
     return ADRP_OK;
+}
+
+/* ---- firmware entry points for oracle/refstub/firmware_stub.py (lets the reference's own
+ * MellingerControl wrapper run against the declared firmware restatement) ---- */
+void fw_lpf2p_init(float coef[5], float fs, float fc)
+{
+    lpf_coef_f32 c;
+    lpf2p_init_f32(&c, fs, fc);
+    coef[0] = c.b0; coef[1] = c.b1; coef[2] = c.b2; coef[3] = c.a1; coef[4] = c.a2;
+}
+
+float fw_lpf2p_apply(const float coef[5], float delay[2], float sample)
+{
+    lpf_coef_f32 c = {coef[0], coef[1], coef[2], coef[3], coef[4]};
+    return lpf2p_apply_f32(&c, &delay[0], &delay[1], sample);
+}
+
+/* statics[10] = i_error_x,y,z, i_error_m_x,y,z, prev_omega_roll,pitch, prev_setpoint_omega_roll,pitch
+ * sp[16] = pos3 vel3 acc3 rate_deg3 quat4 ; out[4] = roll pitch yaw thrust */
+void fw_controller_mellinger(float statics[10], const float sp[16], const float pos[3], const float vel[3],
+                             const float q[4], const float gyro_deg[3], float mass, float out[4])
+{
+    mel_state_f32 m;
+    memset(&m, 0, sizeof(m));
+    m.i_error_x = statics[0]; m.i_error_y = statics[1]; m.i_error_z = statics[2];
+    m.i_error_m_x = statics[3]; m.i_error_m_y = statics[4]; m.i_error_m_z = statics[5];
+    m.prev_omega_roll = statics[6]; m.prev_omega_pitch = statics[7];
+    m.prev_setpoint_omega_roll = statics[8]; m.prev_setpoint_omega_pitch = statics[9];
+    memcpy(m.sp_pos, sp, 12); memcpy(m.sp_vel, sp + 3, 12); memcpy(m.sp_acc, sp + 6, 12);
+    memcpy(m.sp_rate_deg, sp + 9, 12); memcpy(m.sp_quat, sp + 12, 16);
+    controller_mellinger_f32(&m, mass, pos, vel, q, gyro_deg);
+    statics[0] = m.i_error_x; statics[1] = m.i_error_y; statics[2] = m.i_error_z;
+    statics[3] = m.i_error_m_x; statics[4] = m.i_error_m_y; statics[5] = m.i_error_m_z;
+    statics[6] = m.prev_omega_roll; statics[7] = m.prev_omega_pitch;
+    statics[8] = m.prev_setpoint_omega_roll; statics[9] = m.prev_setpoint_omega_pitch;
+    out[0] = (float)m.ctl_roll; out[1] = (float)m.ctl_pitch; out[2] = (float)m.ctl_yaw; out[3] = m.ctl_thrust;
 }

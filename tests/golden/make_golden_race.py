@@ -1,0 +1,143 @@
+"""Golden vectors for the race env: runs the REFERENCE'S OWN ``MultiRaceAviary`` + ``MellingerControl``
+(one controller process per drone over mp.Pipe, exactly as envs/MultiRaceAviary.py:107-115 does) with
+the stand-ins of oracle/refstub for PyBullet and for the pycffirmware SWIG module.
+
+    python tests/golden/make_golden_race.py        (build container only; needs /root/reference)
+
+Pinned by these vectors: every reference-owned line of MultiRaceAviary.step / reset / _gate_progress /
+_computeObs / _computeTerminated and of the MellingerControl wrapper (sensor synthesis, sub-rate
+schedule, power distribution, battery curve, thrust->PWM->RPM, prop reorder).  NOT pinned (declared
+restatements): the firmware core, Bullet's integrator and collision / ray queries.
+The reference's RNG is unseeded; every draw it makes is recorded here and stored next to
+the outputs so that the oracle and the CUDA path can be fed the same numbers.
+"""
+from __future__ import annotations
+
+import json
+import os
+import sys
+import warnings
+
+warnings.filterwarnings("ignore")
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+REF = os.environ.get("ADRP_REFERENCE_ROOT", "/root/reference")
+sys.path.insert(0, os.path.join(ROOT, "oracle", "refstub"))
+sys.path.insert(0, REF)
+sys.path.insert(0, ROOT)
+os.chdir(REF)                      # the reference opens "gym_pybullet_adrp/assets/..." relative to its root
+
+import numpy as np  # noqa: E402
+
+import firmware_stub  # noqa: E402
+import gym_pybullet_adrp.control  # noqa: E402,F401
+from gym_pybullet_adrp.envs.MultiRaceAviary import MultiRaceAviary  # noqa: E402
+from gym_pybullet_adrp.utils.enums import DroneModel, Physics, RaceMode  # noqa: E402
+from munch import munchify  # noqa: E402
+
+from gym_pybullet_adrp_b200 import configs  # noqa: E402
+
+# pycffirmware is not installable here; the package re-exports the class under the submodule's name, hence sys.modules
+sys.modules["gym_pybullet_adrp.control.MellingerControl"].load_firmware = lambda path: firmware_stub.Firmware()
+
+
+class RecordingRNG:
+    """Stands in for np.random / env.np_random: same formulas (low + (high-low)*u, N(0, std)), every unit
+    draw logged in call order."""
+
+    def __init__(self, seed):
+        self.g = np.random.default_rng(seed)
+        self.uniforms, self.step_noise = [], []
+
+    def uniform(self, low=0.0, high=1.0, size=None):
+        low, high = np.asarray(low, float), np.asarray(high, float)
+        shape = size if size is not None else np.broadcast(low, high).shape
+        u = self.g.random(shape)
+        self.uniforms.extend(np.ravel(u).tolist())
+        return low + (high - low) * u
+
+    def normal(self, loc=0.0, scale=1.0, size=None):
+        v = loc + scale * self.g.standard_normal(size)
+        self.step_noise.append(("n", np.array(v)))
+        return v
+
+
+def gate_pass_setpoints(cfg, steps, M):
+    """Smooth full-state setpoints: climb, fly through gate 0 along its normal, carry on to gate 1."""
+    g0, g1 = cfg.gates[0], cfg.gates[1]
+    n0 = np.array([-np.sin(g0[5]), np.cos(g0[5])])
+    starts = [np.array(cfg.init_states[f"drone{i}"].pos) for i in range(M)]
+    out = np.zeros((steps, M, 4))
+    for i in range(M):
+        way = [np.r_[starts[i][:2], 0.35], np.r_[1.0, 0.0, 0.45], np.r_[np.array(g0[:2]) - 0.45 * n0, 0.525],
+               np.r_[np.array(g0[:2]) + 0.45 * n0, 0.525], np.r_[g1[0] - 0.3, g1[1] - 0.1, 0.9]]
+        seg_t = [1.2, 2.2, 2.0, 1.4, 1.8]
+        t0 = 1.6 * i                                   # the second drone follows later
+        for k in range(steps):
+            t = max(0.0, k / 25.0 - t0)
+            p, acc = np.r_[starts[i][:2], 0.05], 0.0
+            for w, dt in zip(way, seg_t):
+                if t <= acc + dt:
+                    s = (t - acc) / dt
+                    s = s * s * (3 - 2 * s)
+                    p = p + s * (w - p)
+                    break
+                acc += dt
+                p = w
+            out[k, i, :3] = p
+            out[k, i, 3] = 0.0
+    return out
+
+
+def race_case(name, level, physics, racemode, M, steps, seed, actions=None):
+    cfg = munchify(json.loads(json.dumps(configs.builtin_config(level))))
+    rec = RecordingRNG(seed)
+    orig_uniform = np.random.uniform
+    np.random.uniform = rec.uniform                              # _addObstacles uses the global np.random (:362,373)
+    env = MultiRaceAviary(cfg, drone_model=DroneModel.CF2X, num_drones=M, physics=physics, racemode=racemode)
+    env.np_random = rec
+    try:
+        obs0, _ = env.reset()
+        draws = np.array(rec.uniforms)
+        state0 = np.array([env._getDroneStateVector(i) for i in range(M)])
+        for i in range(M):                                       # pose AFTER _drone_init (initial_obs predates it, E17)
+            env._updateAndStoreKinematicInformation()
+        state0 = np.array([env._getDroneStateVector(i) for i in range(M)])
+        if actions is None:
+            actions = gate_pass_setpoints(cfg, steps, M)
+        S = env.PYB_STEPS_PER_CTRL
+        noise = np.zeros((steps, M, S, 7))
+        obs = np.zeros((steps,) + obs0.shape)
+        term, trunc = np.zeros(steps, bool), np.zeros(steps, bool)
+        gate, elim, fin = np.zeros((steps, M)), np.zeros((steps, M), bool), np.zeros((steps, M), bool)
+        for k in range(steps):
+            rec.uniforms, rec.step_noise = [], []
+            o, r, te, tr, _ = env.step(actions[k].copy())
+            obs[k], term[k], trunc[k] = o, te, tr
+            gate[k], elim[k], fin[k] = env.current_gate, env.drones_eliminated, env.drones_finished
+            if cfg.disturbances:
+                u = np.array(rec.uniforms).reshape(S, M, 3)
+                lo, hi = np.array(cfg.disturbances_info.dynamics.low), np.array(cfg.disturbances_info.dynamics.high)
+                noise[k, :, :, 0:3] = np.transpose(lo + (hi - lo) * u, (1, 0, 2))
+                nrm = np.array([v for _, v in rec.step_noise])   # (S, M, 4)
+                noise[k, :, :, 3:7] = np.transpose(nrm, (1, 0, 2))
+    finally:
+        np.random.uniform = orig_uniform
+        env.close()
+    meta = dict(env="race", level=level, physics=physics.name, racemode=racemode.name, M=M, steps=steps)
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), meta=json.dumps(meta), draws=draws, state0=state0,
+                        obs0=obs0, actions=actions, noise=noise, obs=obs, terminated=term, truncated=trunc,
+                        current_gate=gate, eliminated=elim, finished=fin)
+    print(name, "gates passed:", gate[-1].tolist(), "eliminated:", elim[-1].tolist(), "terminated at:",
+          int(np.argmax(term)) if term.any() else None)
+
+
+def main():
+    race_case("race_pyb_compete_gs", "getting_started", Physics.PYB, RaceMode.COMPETE, 2, 230, 1)
+    race_case("race_pyb_compare_level3", "level3", Physics.PYB, RaceMode.COMPARE, 2, 150, 2)
+    race_case("race_dyn_compete_level1", "level1", Physics.DYN, RaceMode.COMPETE, 2, 60, 3)
+    race_case("race_pyb_all_compete_level3", "level3", Physics.PYB_GND_DRAG_DW, RaceMode.COMPETE, 2, 100, 4)
+
+
+if __name__ == "__main__":
+    main()

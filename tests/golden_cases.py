@@ -49,3 +49,36 @@ def rel_err(a, b, floor=1.0):
     """max |a-b| / max(|b|, floor) -- relative where the value is large, absolute near zero."""
     a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
     return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), floor)))
+
+RACE_CASES = ["race_pyb_compete_gs", "race_pyb_compare_level3", "race_dyn_compete_level1", "race_pyb_all_compete_level3"]
+
+
+def race_config_for(meta, precision=_abi.F64, num_envs=1, **over):
+    from gym_pybullet_adrp_b200 import configs
+    from gym_pybullet_adrp_b200.utils.enums import RaceMode
+    rc = configs.load_config(meta["level"])
+    cfg = _abi.make_race_config(rc, num_envs=num_envs, num_drones=meta["M"], physics=Physics[meta["physics"]],
+                                racemode=RaceMode[meta["racemode"]], precision=precision, **over)
+    return rc, cfg
+
+
+def place_draws(rc, raw, M, G=4, O=4):
+    """The reference only draws for the randomisation blocks that are switched on; the C ABI's reset
+    draw vector always has the full layout [gates 3G | obstacles 2O | per drone: inertia 4, pos 3, rot 3]."""
+    out = np.zeros(3 * G + 2 * O + 10 * M)
+    raw = list(raw)
+    k = 0
+    if rc.get("random_gates_obstacles"):
+        n = 3 * G + 2 * O
+        out[:n] = raw[k:k + n]
+        k += n
+    for i in range(M):
+        base = 3 * G + 2 * O + 10 * i
+        if rc.get("random_drone_inertia"):
+            out[base:base + 4] = raw[k:k + 4]
+            k += 4
+        if rc.get("random_drone_state"):
+            out[base + 4:base + 10] = raw[k:k + 6]
+            k += 6
+    assert k == len(raw), (k, len(raw))
+    return out

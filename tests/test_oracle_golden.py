@@ -78,3 +78,51 @@ def test_dslpid_known_answers_fp64():
                                                   tvel[None], trates[None], ctrl)
             got = np.r_[rpm[0], pos_e[0], yaw_e[0], ctrl[0]]
             assert gc.rel_err(got, out) < TOL64, (cf2p, call, got - out)
+
+
+@pytest.mark.parametrize("name", gc.RACE_CASES)
+def test_race_env_fp64(name):
+    """MultiRaceAviary + MellingerControl wrapper as run by the reference itself (tests/golden/make_golden_race.py),
+    with the recorded random draws injected.  Flags, gate counters and latches must be identical."""
+    meta, z = gc.load(name)
+    rc, cfg = gc.race_config_for(meta)
+    env = OracleEnv(cfg)
+    env.reset(draws=gc.place_draws(rc, z["draws"], meta["M"])[None])
+    st = env.get_state()[0]
+    assert np.abs(st[:, 0:7] - z["state0"][:, 0:7]).max() < 1e-12
+    worst = 0.0
+    for k in range(meta["steps"]):
+        noise = z["noise"][k][None] if rc.get("disturbances") else None
+        obs, rew, te, tr, fl = env.step(z["actions"][k][None], noise=noise)
+        worst = max(worst, gc.rel_err(obs[0], z["obs"][k]))
+        assert worst < TOL64, (name, k, worst)
+        np.testing.assert_array_equal((fl[0] & _abi.FLAG_ELIMINATED) != 0, z["eliminated"][k])
+        np.testing.assert_array_equal((fl[0] & _abi.FLAG_FINISHED) != 0, z["finished"][k])
+        np.testing.assert_array_equal(obs[0][:, 48], z["current_gate"][k])
+        assert bool(te[0]) == bool(z["terminated"][k]) and bool(tr[0]) == bool(z["truncated"][k])
+        assert rew[0] == 0
+
+
+def test_mellinger_schedule_known_answer():
+    """the float64 sub-rate schedule of MellingerControl._step_controller (:395-411),
+    first 120 ticks, computed with the reference's own expressions; the oracle's integer-stamp form
+    ("run iff cur_time - last_att > 0.002") must fire on exactly the non-'1' ticks."""
+    want = ("112121012121012120122210221202122022122022212022220122220221220222202221202222022220221220222202222022122022220222202212")
+    last_att = last_pos = 0.0
+    got = ""
+    for tick in range(120):
+        t = tick / 500
+        if (t - last_att > 0.002) and (t - last_pos > 0.01):
+            got += "0"; last_pos = last_att = t
+        elif t - last_att > 0.002:
+            got += "2"; last_att = t
+        else:
+            got += "1"
+    assert got == want
+    last_tick, fired = 0, ""
+    for tick in range(120):
+        if tick / 500.0 - last_tick / 500.0 > 0.002:
+            fired += "x"; last_tick = tick
+        else:
+            fired += "1"
+    assert all((a == "1") == (b == "1") for a, b in zip(want, fired))
