@@ -14,9 +14,12 @@ import sys
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 OUT = os.path.join(PKG_DIR, "libadrp_b200.so")
-SOURCES = ["adrp_api.cu"]
+# translation unit -> extra flags.  The fp64 parity build contracts no multiply-add (the oracle is compiled
+# with -ffp-contract=off); the fp32 product build keeps nvcc's default FMA contraction.
+SOURCES = {"adrp_api.cu": [], "adrp_kernels_f32.cu": [], "adrp_kernels_f64.cu": ["-fmad=false"]}
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-              "-Xcompiler", "-fPIC", "-shared", "--cudart", "shared"]
+              "-Xcompiler", "-fPIC", "--cudart", "shared"]
+OBJ_DIR = os.path.join(PKG_DIR, "build")
 
 
 def _stale():
@@ -33,12 +36,23 @@ def build(force: bool = False, verbose: bool = False) -> str:
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     if not os.path.exists(nvcc):
         raise RuntimeError("nvcc not found: cannot build libadrp_b200.so")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT] + SOURCES
-    res = subprocess.run(cmd, cwd=CSRC, capture_output=True, text=True)
+    os.makedirs(OBJ_DIR, exist_ok=True)
+    procs = []
+    for src, extra in SOURCES.items():
+        obj = os.path.join(OBJ_DIR, src.replace(".cu", ".o"))
+        cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", obj, src]
+        procs.append((obj, subprocess.Popen(cmd, cwd=CSRC, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)))
+    objs = []
+    for obj, pr in procs:
+        out, err = pr.communicate()
+        if pr.returncode != 0:
+            raise RuntimeError("nvcc failed:\n" + out + err)
+        if verbose:
+            print(err)
+        objs.append(obj)
+    res = subprocess.run([nvcc, "-shared", "--cudart", "shared", "-o", OUT] + objs, cwd=CSRC, capture_output=True, text=True)
     if res.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
-    if verbose:
-        print(res.stderr)
+        raise RuntimeError("nvcc link failed:\n" + res.stdout + res.stderr)
     return OUT
 
 

@@ -8,7 +8,9 @@
 #include <new>
 #include <string>
 
-#include "adrp_step.cuh"
+#include <vector>
+
+#include "adrp_kernels.cuh"
 
 using namespace adrp;
 
@@ -39,7 +41,11 @@ template <typename T>
 struct Handle : HandleBase {
     KParams<T> P;
     KBuffers<T> B;
+    RaceParams<T> RP;
+    RaceBuffers<T> RB;
+    bool race = false;
 };
+
 
 int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
 
@@ -76,6 +82,8 @@ void derive_params(const adrp_config& c, KParams<T>& P)
     P.S = c.pyb_freq / c.ctrl_freq; P.A = action_dim(c.action_type);
     P.B = (c.env_kind == ADRP_ENV_HOVER || c.env_kind == ADRP_ENV_MULTIHOVER) ? c.ctrl_freq / 2 : 0;   // BaseRLAviary.py:66
     P.O = c.env_kind == ADRP_ENV_CTRL ? 20 : 12 + P.B * P.A;
+    if (c.env_kind == ADRP_ENV_RACE)      // MultiRaceAviary._observationSpace (:291-343)
+        P.O = 12 + 5 * c.track.num_gates + 4 * c.track.num_obstacles + 1 + (c.race_mode == ADRP_RACE_COMPETE ? 6 * (c.drones_per_env - 1) : 0);
     P.physics = c.physics; P.drone_model = c.drone_model; P.action_type = c.action_type; P.env_kind = c.env_kind;
     P.race_mode = c.race_mode; P.auto_reset = c.auto_reset; P.pid_model = c.dslpid_model;
     P.Dpad = (long long)P.N * P.Mpad;
@@ -111,7 +119,7 @@ void derive_params(const adrp_config& c, KParams<T>& P)
         host_init_quat(c.init_rpy[i], q);
         for (int k = 0; k < 4; ++k) P.init_quat[i][k] = (T)q[k];
         for (int k = 0; k < 3; ++k) {
-            P.init_xyz[i][k] = (T)c.init_xyz[i][k]; P.init_vel[i][k] = (T)c.init_vel[i][k];
+            P.init_xyz[i][k] = (T)c.init_xyz[i][k]; P.init_vel[i][k] = (T)c.init_vel[i][k]; P.init_rpy[i][k] = (T)c.init_rpy[i][k];
             P.init_pqr[i][k] = (T)c.init_pqr[i][k]; P.target[i][k] = (T)c.target_pos[i][k];
         }
     }
@@ -126,6 +134,61 @@ void derive_params(const adrp_config& c, KParams<T>& P)
         }                                                                                  \
     } while (0)
 
+// filter.c lpf2pSetCutoffFreq, evaluated once on the host in float like the firmware does.
+void host_lpf2p(float sample_freq, float cutoff_freq, float out[5])
+{
+    const float fr = sample_freq / cutoff_freq;
+    const float ohm = tanf(3.14159265358979323846f / fr);
+    const float cc = 1.0f + 2.0f * cosf(3.14159265358979323846f / 4.0f) * ohm + ohm * ohm;
+    out[0] = ohm * ohm / cc;
+    out[1] = 2.0f * out[0];
+    out[2] = out[0];
+    out[3] = 2.0f * (ohm * ohm - 1.0f) / cc;
+    out[4] = (1.0f - 2.0f * cosf(3.14159265358979323846f / 4.0f) * ohm + ohm * ohm) / cc;
+}
+
+template <typename T>
+void derive_race(const adrp_config& c, const KParams<T>& P, RaceParams<T>& R)
+{
+    memset(&R, 0, sizeof(R));
+    const adrp_track& t = c.track;
+    const adrp_randomization& r = c.rnd;
+    R.G = t.num_gates; R.NO = t.num_obstacles;
+    R.TF = kGateFields * R.G + kObstFields * R.NO;
+    R.R = 3 * R.G + 2 * R.NO + 10 * c.drones_per_env;
+    R.compete = c.race_mode == ADRP_RACE_COMPETE;
+    R.rnd_track = r.random_gates_obstacles; R.rnd_state = r.random_drone_state;
+    R.rnd_inertia = r.random_drone_inertia; R.disturbances = r.disturbances;
+    R.seed_lo = (unsigned)(c.seed & 0xffffffffu); R.seed_hi = (unsigned)(c.seed >> 32);
+    R.env_offset = c.env_offset;
+    for (int g = 0; g < R.G; ++g) {
+        for (int k = 0; k < 4; ++k) R.gate_nom[g][k] = (T)t.gates[g][k];
+        R.gate_type[g] = t.gate_type[g];
+    }
+    for (int o = 0; o < R.NO; ++o)
+        for (int k = 0; k < 3; ++k) R.obst_nom[o][k] = (T)t.obstacles[o][k];
+    for (int k = 0; k < 3; ++k) {
+        R.bounds_hi[k] = (T)t.bounds_hi[k];
+        R.pos_lo[k] = (T)r.pos_range[k][0]; R.pos_hi[k] = (T)r.pos_range[k][1];
+        R.rot_lo[k] = (T)r.rot_range[k][0]; R.rot_hi[k] = (T)r.rot_range[k][1];
+        R.wind_lo[k] = (T)r.wind_lo[k]; R.wind_hi[k] = (T)r.wind_hi[k];
+    }
+    R.contact_margin = (T)t.contact_margin; R.visibility = (T)t.visibility_range;
+    R.gate_lo = (T)r.gate_range[0]; R.gate_hi = (T)r.gate_range[1];
+    R.obst_lo = (T)r.obstacle_range[0]; R.obst_hi = (T)r.obstacle_range[1];
+    const double* ranges[4] = {r.mass_range, r.ixx_range, r.iyy_range, r.izz_range};
+    for (int k = 0; k < 4; ++k) { R.inertia_lo[k] = (T)ranges[k][0]; R.inertia_hi[k] = (T)ranges[k][1]; }
+    R.noise_std = (T)r.action_noise_std;
+    for (int i = 0; i < c.drones_per_env; ++i)
+        for (int k = 0; k < 3; ++k) R.mel_prev_rpy[i][k] = (T)(c.init_rpy[i][k] * (M_PI / 180.0));   // MellingerControl.py:103-107
+    R.mel_mass = (float)c.mel_mass;
+    float lp[5];
+    host_lpf2p(500.0f, 30.0f, lp);      // lpf2pInit(gyrolpf, FIRMWARE_FREQ, ACCEL_LPF_CUTOFF_FREQ): the swapped cutoffs of :116-117
+    R.lpf_b0 = lp[0]; R.lpf_b1 = lp[1]; R.lpf_b2 = lp[2]; R.lpf_a1 = lp[3]; R.lpf_a2 = lp[4];
+    // one firmware tick per physics substep while the episode lasts, plus the steps a caller may take after truncation
+    R.lut_ticks = ((P.trunc_steps + 64 * P.S + 1 + 31) / 32) * 32;
+}
+
 template <typename T>
 int alloc_buffers(Handle<T>* h)
 {
@@ -137,6 +200,33 @@ int alloc_buffers(Handle<T>* h)
     CUDA_TRY(h, cudaMalloc(&h->B.step_counter, sizeof(int32_t) * P.N));
     CUDA_TRY(h, cudaMalloc(&h->B.ring_head, sizeof(int32_t) * P.N));
     CUDA_TRY(h, cudaMemset(h->B.state, 0, sizeof(T) * F_COUNT * D));
+    if (h->race) {
+        RaceBuffers<T>& rb = h->RB;
+        const RaceParams<T>& R = h->RP;
+        CUDA_TRY(h, cudaMalloc(&rb.track, sizeof(T) * (size_t)(R.TF > 0 ? R.TF : 1) * P.N));
+        CUDA_TRY(h, cudaMalloc(&rb.body, sizeof(T) * 4 * D));
+        CUDA_TRY(h, cudaMalloc(&rb.mel_t, sizeof(T) * MT_COUNT * D));
+        CUDA_TRY(h, cudaMalloc(&rb.mel_f, sizeof(float) * MF_COUNT * D));
+        CUDA_TRY(h, cudaMalloc(&rb.mel_i, sizeof(int32_t) * MI_COUNT * D));
+        CUDA_TRY(h, cudaMalloc(&rb.gate_latch, sizeof(int32_t) * D));
+        CUDA_TRY(h, cudaMalloc(&rb.episode, sizeof(int32_t) * P.N));
+        CUDA_TRY(h, cudaMemset(rb.episode, 0, sizeof(int32_t) * P.N));
+        CUDA_TRY(h, cudaMemset(rb.mel_t, 0, sizeof(T) * MT_COUNT * D));
+        CUDA_TRY(h, cudaMemset(rb.mel_f, 0, sizeof(float) * MF_COUNT * D));
+        CUDA_TRY(h, cudaMemset(rb.mel_i, 0, sizeof(int32_t) * MI_COUNT * D));
+        CUDA_TRY(h, cudaMemset(rb.gate_latch, 0, sizeof(int32_t) * D));
+        // sub-rate schedule (MellingerControl.py:395-411): bit t <=> (t/500 - (t-1)/500 > 0.002) in float64
+        std::vector<uint32_t> lut((size_t)R.lut_ticks / 32, 0u);
+        for (int t = 1; t < R.lut_ticks; ++t) {
+            const volatile double a = (double)t / 500.0, b = (double)(t - 1) / 500.0;
+            if (a - b > 0.002) lut[(size_t)t >> 5] |= 1u << (t & 31);
+        }
+        uint32_t* dl = nullptr;
+        CUDA_TRY(h, cudaMalloc(&dl, sizeof(uint32_t) * lut.size()));
+        CUDA_TRY(h, cudaMemcpy(dl, lut.data(), sizeof(uint32_t) * lut.size(), cudaMemcpyHostToDevice));
+        rb.lut = dl;
+        CUDA_TRY(h, Launch<T>::race_prepare(R, P));
+    }
     return ADRP_OK;
 }
 
@@ -144,26 +234,25 @@ template <typename T>
 void free_buffers(Handle<T>* h)
 {
     cudaFree(h->B.state); cudaFree(h->B.pid); cudaFree(h->B.ring); cudaFree(h->B.step_counter); cudaFree(h->B.ring_head);
+    if (h->race) {
+        RaceBuffers<T>& rb = h->RB;
+        cudaFree(rb.track); cudaFree(rb.body); cudaFree(rb.mel_t); cudaFree(rb.mel_f); cudaFree(rb.mel_i);
+        cudaFree(rb.gate_latch); cudaFree(rb.episode); cudaFree(const_cast<uint32_t*>(rb.lut));
+    }
 }
 
-inline unsigned grid_for(long long D) { return (unsigned)((D + kBlock - 1) / kBlock); }
-
 template <typename T>
-int do_reset(Handle<T>* h, const uint8_t* mask, T* obs, cudaStream_t s)
+int do_reset(Handle<T>* h, const uint8_t* mask, const T* draws, T* obs, cudaStream_t s)
 {
-    reset_kernel<T><<<grid_for(h->P.Dpad), kBlock, 0, s>>>(h->P, h->B, mask, obs);
     h->launches++;
-    CUDA_TRY(h, cudaGetLastError());
+    if (h->race) CUDA_TRY(h, Launch<T>::race_reset(h->P, h->RP, h->B, h->RB, mask, draws, obs, s));
+    else CUDA_TRY(h, Launch<T>::reset(h->P, h->B, mask, obs, s));
     return ADRP_OK;
 }
 
 template <typename T>
-int do_step(Handle<T>* h, const T* action, T* obs, T* reward, uint8_t* te, uint8_t* tr, uint8_t* fl, cudaStream_t s)
+int do_step(Handle<T>* h, const T* action, const T* noise, T* obs, T* reward, uint8_t* te, uint8_t* tr, uint8_t* fl, cudaStream_t s)
 {
-    const KParams<T>& P = h->P;
-    const unsigned grid = grid_for(P.Dpad);
-    const bool pid = P.action_type == ADRP_ACT_PID || P.action_type == ADRP_ACT_ONE_D_PID ||
-                     P.action_type == ADRP_ACT_VEL || P.action_type == ADRP_ACT_PID_FULL;
     if (h->profiling) {
         if (h->ev_pending) {          // harvest the previous launch's time before re-recording the events
             float ms = 0;
@@ -173,11 +262,10 @@ int do_step(Handle<T>* h, const T* action, T* obs, T* reward, uint8_t* te, uint8
         }
         CUDA_TRY(h, cudaEventRecord(h->ev0, s));
     }
-    if (pid) step_kernel<T, -1, 1><<<grid, kBlock, 0, s>>>(P, h->B, action, obs, reward, te, tr, fl);
-    else step_kernel<T, -1, 0><<<grid, kBlock, 0, s>>>(P, h->B, action, obs, reward, te, tr, fl);
     h->launches++;
+    if (h->race) CUDA_TRY(h, Launch<T>::race_step(h->P, h->RP, h->B, h->RB, action, noise, obs, reward, te, tr, fl, s));
+    else CUDA_TRY(h, Launch<T>::step(h->P, h->B, action, obs, reward, te, tr, fl, s));
     if (h->profiling) { CUDA_TRY(h, cudaEventRecord(h->ev1, s)); h->ev_pending = true; }
-    CUDA_TRY(h, cudaGetLastError());
     return ADRP_OK;
 }
 
@@ -188,11 +276,13 @@ int create_typed(const adrp_config* cfg, adrp_handle** out)
     if (!h) { g_create_error = "out of host memory"; return ADRP_EINVAL; }
     h->cfg = *cfg;
     h->precision = cfg->precision;
+    h->race = cfg->env_kind == ADRP_ENV_RACE;
     derive_params<T>(*cfg, h->P);
+    if (h->race) derive_race<T>(*cfg, h->P, h->RP);
     cudaError_t e = cudaSetDevice(cfg->device);
     if (e != cudaSuccess) { g_create_error = std::string("cudaSetDevice: ") + cudaGetErrorString(e); delete h; return ADRP_ECUDA; }
     int rc = alloc_buffers(h);
-    if (rc == ADRP_OK) rc = do_reset<T>(h, nullptr, nullptr, 0);
+    if (rc == ADRP_OK) rc = do_reset<T>(h, nullptr, nullptr, nullptr, 0);
     if (rc == ADRP_OK && cudaDeviceSynchronize() != cudaSuccess) { h->err = "reset kernel failed"; rc = ADRP_ECUDA; }
     if (rc != ADRP_OK) { g_create_error = h->err; free_buffers(h); delete h; return rc; }
     *out = reinterpret_cast<adrp_handle*>(static_cast<HandleBase*>(h));
@@ -211,7 +301,8 @@ int validate(const adrp_config* c)
     if (c->ctrl_freq < 1 || c->pyb_freq % c->ctrl_freq != 0) { g_create_error = "[ERROR] in BaseAviary.__init__(), pyb_freq is not divisible by env_freq."; return ADRP_EINVAL; }
     if (c->precision != ADRP_F32 && c->precision != ADRP_F64) { g_create_error = "unknown precision"; return ADRP_EINVAL; }
     if (action_dim(c->action_type) == 0) { g_create_error = "unknown action_type"; return ADRP_EINVAL; }
-    if (c->env_kind == ADRP_ENV_RACE || c->action_type == ADRP_ACT_MEL) { g_create_error = "race env / Mellinger: not in this build"; return ADRP_EUNSUPPORTED; }
+    if ((c->env_kind == ADRP_ENV_RACE) != (c->action_type == ADRP_ACT_MEL)) { g_create_error = "ADRP_ACT_MEL (Mellinger full-state setpoints) is the race env's action type, and its only one"; return ADRP_EINVAL; }
+    if (c->env_kind == ADRP_ENV_RACE && (c->track.num_gates < 0 || c->track.num_gates > ADRP_MAX_GATES || c->track.num_obstacles < 0 || c->track.num_obstacles > ADRP_MAX_OBSTACLES)) { g_create_error = "too many gates / obstacles"; return ADRP_EINVAL; }
     if (c->env_kind == ADRP_ENV_HOVER && c->drones_per_env != 1) { g_create_error = "HoverAviary is single-drone"; return ADRP_EINVAL; }
     return ADRP_OK;
 }
@@ -253,30 +344,34 @@ int adrp_obs_dim(const adrp_handle* h) { return BY_PRECISION(h, typed<double>(co
 int adrp_action_dim(const adrp_handle* h) { return BY_PRECISION(h, typed<double>(const_cast<adrp_handle*>(h))->P.A, typed<float>(const_cast<adrp_handle*>(h))->P.A); }
 int adrp_substeps(const adrp_handle* h) { return BY_PRECISION(h, typed<double>(const_cast<adrp_handle*>(h))->P.S, typed<float>(const_cast<adrp_handle*>(h))->P.S); }
 int adrp_noise_dim(const adrp_handle*) { return 7; }
-int adrp_reset_draws_dim(const adrp_handle*) { return 0; }
+int adrp_reset_draws_dim(const adrp_handle* h)
+{
+    if (!h) return 0;
+    const HandleBase* b = base(h);
+    if (b->cfg.env_kind != ADRP_ENV_RACE) return 0;
+    return 3 * b->cfg.track.num_gates + 2 * b->cfg.track.num_obstacles + 10 * b->cfg.drones_per_env;
+}
 
 int adrp_reset(adrp_handle* h, const uint8_t* env_mask, const void* draws, void* obs, void* stream)
 {
-    (void)draws;
     if (!h) return ADRP_EINVAL;
     cudaStream_t s = (cudaStream_t)stream;
-    return BY_PRECISION(h, do_reset<double>(typed<double>(h), env_mask, (double*)obs, s),
-                        do_reset<float>(typed<float>(h), env_mask, (float*)obs, s));
+    return BY_PRECISION(h, do_reset<double>(typed<double>(h), env_mask, (const double*)draws, (double*)obs, s),
+                        do_reset<float>(typed<float>(h), env_mask, (const float*)draws, (float*)obs, s));
 }
 
 int adrp_set_state(adrp_handle* h, const void* state, void* stream)
 {
     if (!h || !state) return ADRP_EINVAL;
     cudaStream_t s = (cudaStream_t)stream;
+    base(h)->launches++;
     if (base(h)->precision == ADRP_F64) {
         auto* t = typed<double>(h);
-        set_state_kernel<double><<<grid_for(t->P.Dpad), kBlock, 0, s>>>(t->P, t->B, (const double*)state);
+        CUDA_TRY(t, Launch<double>::set_state(t->P, t->B, (const double*)state, s));
     } else {
         auto* t = typed<float>(h);
-        set_state_kernel<float><<<grid_for(t->P.Dpad), kBlock, 0, s>>>(t->P, t->B, (const float*)state);
+        CUDA_TRY(t, Launch<float>::set_state(t->P, t->B, (const float*)state, s));
     }
-    base(h)->launches++;
-    CUDA_TRY(base(h), cudaGetLastError());
     return ADRP_OK;
 }
 
@@ -284,29 +379,27 @@ int adrp_get_state(adrp_handle* h, void* state, void* stream)
 {
     if (!h || !state) return ADRP_EINVAL;
     cudaStream_t s = (cudaStream_t)stream;
+    base(h)->launches++;
     if (base(h)->precision == ADRP_F64) {
         auto* t = typed<double>(h);
-        get_state_kernel<double><<<grid_for(t->P.Dpad), kBlock, 0, s>>>(t->P, t->B, (double*)state);
+        CUDA_TRY(t, Launch<double>::get_state(t->P, t->B, (double*)state, s));
     } else {
         auto* t = typed<float>(h);
-        get_state_kernel<float><<<grid_for(t->P.Dpad), kBlock, 0, s>>>(t->P, t->B, (float*)state);
+        CUDA_TRY(t, Launch<float>::get_state(t->P, t->B, (float*)state, s));
     }
-    base(h)->launches++;
-    CUDA_TRY(base(h), cudaGetLastError());
     return ADRP_OK;
 }
 
 int adrp_step(adrp_handle* h, const void* action, const void* noise, void* obs, void* reward,
               uint8_t* terminated, uint8_t* truncated, uint8_t* drone_flags, void* stream)
 {
-    (void)noise;
     if (!h || !action || !obs || !reward || !terminated || !truncated) {
         if (h) base(h)->err = "adrp_step: NULL buffer";
         return ADRP_EINVAL;
     }
     cudaStream_t s = (cudaStream_t)stream;
-    return BY_PRECISION(h, do_step<double>(typed<double>(h), (const double*)action, (double*)obs, (double*)reward, terminated, truncated, drone_flags, s),
-                        do_step<float>(typed<float>(h), (const float*)action, (float*)obs, (float*)reward, terminated, truncated, drone_flags, s));
+    return BY_PRECISION(h, do_step<double>(typed<double>(h), (const double*)action, (const double*)noise, (double*)obs, (double*)reward, terminated, truncated, drone_flags, s),
+                        do_step<float>(typed<float>(h), (const float*)action, (const float*)noise, (float*)obs, (float*)reward, terminated, truncated, drone_flags, s));
 }
 
 }  // extern "C"
@@ -346,7 +439,7 @@ int do_step_host(Handle<T>* h, const void* action, void* obs, void* reward, uint
     cudaStream_t s = h->own_stream;
     memcpy(h->h_action, action, sizeof(T) * nd * P.A);
     CUDA_TRY(h, cudaMemcpyAsync(h->d_action, h->h_action, sizeof(T) * nd * P.A, cudaMemcpyHostToDevice, s));
-    rc = do_step<T>(h, (const T*)h->d_action, (T*)h->d_obs, (T*)h->d_reward, h->d_term, h->d_trunc, h->d_flags, s);
+    rc = do_step<T>(h, (const T*)h->d_action, (const T*)nullptr, (T*)h->d_obs, (T*)h->d_reward, h->d_term, h->d_trunc, h->d_flags, s);
     if (rc != ADRP_OK) return rc;
     CUDA_TRY(h, cudaMemcpyAsync(h->h_obs, h->d_obs, sizeof(T) * nd * P.O, cudaMemcpyDeviceToHost, s));
     CUDA_TRY(h, cudaMemcpyAsync(h->h_reward, h->d_reward, sizeof(T) * P.N, cudaMemcpyDeviceToHost, s));
@@ -360,30 +453,6 @@ int do_step_host(Handle<T>* h, const void* action, void* obs, void* reward, uint
     memcpy(tr, h->h_trunc, P.N);
     if (fl) memcpy(fl, h->h_flags, nd);
     return ADRP_OK;
-}
-
-// DSLPIDControl.computeControl for n independent rows (control/DSLPIDControl.py:82-145).
-template <typename T>
-__global__ void dslpid_rows_kernel(T pid_gravity, T pid_kf, int model, int n, T dt, const T* pos, const T* quat,
-                                   const T* vel, const T* tpos, const T* trpy, const T* tvel, const T* trates,
-                                   T* ctrl, T* rpm, T* pos_e, T* yaw_e)
-{
-    const int r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= n) return;
-    PidState<T> c;
-    T* cs = ctrl + 9 * r;
-    c.ipos = {cs[0], cs[1], cs[2]}; c.irpy = {cs[3], cs[4], cs[5]}; c.last_rpy = {cs[6], cs[7], cs[8]};
-    const V3<T> zero = {T(0), T(0), T(0)};
-    auto v3 = [&](const T* p) -> V3<T> { return p ? V3<T>{p[3 * r], p[3 * r + 1], p[3 * r + 2]} : zero; };
-    const Q4<T> q = {quat[4 * r], quat[4 * r + 1], quat[4 * r + 2], quat[4 * r + 3]};
-    T out[4], ye;
-    V3<T> pe;
-    dslpid_control(pid_gravity, pid_kf, model, dt, v3(pos), q, v3(vel), v3(tpos), v3(trpy), v3(tvel), v3(trates), c, out, pe, ye);
-    for (int k = 0; k < 4; ++k) rpm[4 * r + k] = out[k];
-    if (pos_e) { pos_e[3 * r] = pe.x; pos_e[3 * r + 1] = pe.y; pos_e[3 * r + 2] = pe.z; }
-    if (yaw_e) yaw_e[r] = ye;
-    cs[0] = c.ipos.x; cs[1] = c.ipos.y; cs[2] = c.ipos.z; cs[3] = c.irpy.x; cs[4] = c.irpy.y; cs[5] = c.irpy.z;
-    cs[6] = c.last_rpy.x; cs[7] = c.last_rpy.y; cs[8] = c.last_rpy.z;
 }
 
 }  // namespace
@@ -407,16 +476,16 @@ int adrp_dslpid_control(int precision, int drone_model, const adrp_drone_params*
     if (drone_model != ADRP_CF2X && drone_model != ADRP_CF2P) return ADRP_EUNSUPPORTED;   // DSLPIDControl.py:34-36
     if (n == 0) return ADRP_OK;
     cudaStream_t s = (cudaStream_t)stream;
-    const unsigned grid = (unsigned)((n + 127) / 128);
+    cudaError_t e;
     if (precision == ADRP_F64)
-        dslpid_rows_kernel<double><<<grid, 128, 0, s>>>(g * drone->mass, drone->kf, drone_model, n, control_timestep,
+        e = Launch<double>::dslpid_rows(g * drone->mass, drone->kf, drone_model, n, control_timestep,
             (const double*)pos, (const double*)quat, (const double*)vel, (const double*)target_pos, (const double*)target_rpy,
-            (const double*)target_vel, (const double*)target_rates, (double*)ctrl_state, (double*)rpm, (double*)pos_e, (double*)yaw_e);
+            (const double*)target_vel, (const double*)target_rates, (double*)ctrl_state, (double*)rpm, (double*)pos_e, (double*)yaw_e, s);
     else
-        dslpid_rows_kernel<float><<<grid, 128, 0, s>>>((float)(g * drone->mass), (float)drone->kf, drone_model, n, (float)control_timestep,
+        e = Launch<float>::dslpid_rows((float)(g * drone->mass), (float)drone->kf, drone_model, n, (float)control_timestep,
             (const float*)pos, (const float*)quat, (const float*)vel, (const float*)target_pos, (const float*)target_rpy,
-            (const float*)target_vel, (const float*)target_rates, (float*)ctrl_state, (float*)rpm, (float*)pos_e, (float*)yaw_e);
-    return cudaGetLastError() == cudaSuccess ? ADRP_OK : ADRP_ECUDA;
+            (const float*)target_vel, (const float*)target_rates, (float*)ctrl_state, (float*)rpm, (float*)pos_e, (float*)yaw_e, s);
+    return e == cudaSuccess ? ADRP_OK : ADRP_ECUDA;
 }
 
 int64_t adrp_launch_count(const adrp_handle* h) { return h ? base(h)->launches : 0; }

@@ -1,0 +1,29 @@
+// adrp_kernels.cuh -- launch interface between the host side of the C ABI (adrp_api.cu) and the two
+// kernel translation units: adrp_kernels_f32.cu (fp32 product build) and adrp_kernels_f64.cu (fp64
+// parity build, compiled with -fmad=false so that its arithmetic is statement-for-statement IEEE).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "adrp_params.cuh"
+
+namespace adrp {
+
+template <typename T>
+struct Launch {
+    static cudaError_t reset(const KParams<T>& P, const KBuffers<T>& b, const uint8_t* mask, T* obs, cudaStream_t s);
+    static cudaError_t step(const KParams<T>& P, const KBuffers<T>& b, const T* action, T* obs, T* reward,
+                            uint8_t* terminated, uint8_t* truncated, uint8_t* flags, cudaStream_t s);
+    static cudaError_t set_state(const KParams<T>& P, const KBuffers<T>& b, const T* rows, cudaStream_t s);
+    static cudaError_t get_state(const KParams<T>& P, const KBuffers<T>& b, T* rows, cudaStream_t s);
+    static cudaError_t race_prepare(const RaceParams<T>& RP, const KParams<T>& P);     // shared-memory opt-in
+    static cudaError_t race_reset(const KParams<T>& P, const RaceParams<T>& RP, const KBuffers<T>& b, const RaceBuffers<T>& rb,
+                                  const uint8_t* mask, const T* draws, T* obs, cudaStream_t s);
+    static cudaError_t race_step(const KParams<T>& P, const RaceParams<T>& RP, const KBuffers<T>& b, const RaceBuffers<T>& rb,
+                                 const T* action, const T* noise, T* obs, T* reward, uint8_t* terminated,
+                                 uint8_t* truncated, uint8_t* flags, cudaStream_t s);
+    static cudaError_t dslpid_rows(T pid_gravity, T pid_kf, int model, int n, T dt, const T* pos, const T* quat, const T* vel,
+                                   const T* tpos, const T* trpy, const T* tvel, const T* trates, T* ctrl, T* rpm, T* pos_e,
+                                   T* yaw_e, cudaStream_t s);
+};
+
+}  // namespace adrp

@@ -1,0 +1,106 @@
+// adrp_kernels_impl.cuh -- Launch<T> bodies; included by exactly one .cu per precision.
+#pragma once
+#include "adrp_kernels.cuh"
+#include "adrp_race.cuh"
+
+namespace adrp {
+
+inline unsigned grid_for(long long D) { return (unsigned)((D + kBlock - 1) / kBlock); }
+
+template <typename T>
+inline size_t race_smem_bytes(const KParams<T>& P, const RaceParams<T>& RP) { return sizeof(T) * (size_t)RP.TF * (kBlock / P.Mpad); }
+
+// DSLPIDControl.computeControl for n independent rows (control/DSLPIDControl.py:82-145).
+template <typename T>
+__global__ void dslpid_rows_kernel(T pid_gravity, T pid_kf, int model, int n, T dt, const T* pos, const T* quat,
+                                   const T* vel, const T* tpos, const T* trpy, const T* tvel, const T* trates,
+                                   T* ctrl, T* rpm, T* pos_e, T* yaw_e)
+{
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    PidState<T> c;
+    T* cs = ctrl + 9 * r;
+    c.ipos = {cs[0], cs[1], cs[2]}; c.irpy = {cs[3], cs[4], cs[5]}; c.last_rpy = {cs[6], cs[7], cs[8]};
+    const V3<T> zero = {T(0), T(0), T(0)};
+    auto v3 = [&](const T* p) -> V3<T> { return p ? V3<T>{p[3 * r], p[3 * r + 1], p[3 * r + 2]} : zero; };
+    const Q4<T> q = {quat[4 * r], quat[4 * r + 1], quat[4 * r + 2], quat[4 * r + 3]};
+    T out[4], ye;
+    V3<T> pe;
+    dslpid_control(pid_gravity, pid_kf, model, dt, v3(pos), q, v3(vel), v3(tpos), v3(trpy), v3(tvel), v3(trates), c, out, pe, ye);
+    for (int k = 0; k < 4; ++k) rpm[4 * r + k] = out[k];
+    if (pos_e) { pos_e[3 * r] = pe.x; pos_e[3 * r + 1] = pe.y; pos_e[3 * r + 2] = pe.z; }
+    if (yaw_e) yaw_e[r] = ye;
+    cs[0] = c.ipos.x; cs[1] = c.ipos.y; cs[2] = c.ipos.z; cs[3] = c.irpy.x; cs[4] = c.irpy.y; cs[5] = c.irpy.z;
+    cs[6] = c.last_rpy.x; cs[7] = c.last_rpy.y; cs[8] = c.last_rpy.z;
+}
+
+template <typename T>
+cudaError_t Launch<T>::reset(const KParams<T>& P, const KBuffers<T>& b, const uint8_t* mask, T* obs, cudaStream_t s)
+{
+    reset_kernel<T><<<grid_for(P.Dpad), kBlock, 0, s>>>(P, b, mask, obs);
+    return cudaGetLastError();
+}
+
+template <typename T>
+cudaError_t Launch<T>::step(const KParams<T>& P, const KBuffers<T>& b, const T* action, T* obs, T* reward,
+                            uint8_t* te, uint8_t* tr, uint8_t* fl, cudaStream_t s)
+{
+    const bool pid = P.action_type == ADRP_ACT_PID || P.action_type == ADRP_ACT_ONE_D_PID ||
+                     P.action_type == ADRP_ACT_VEL || P.action_type == ADRP_ACT_PID_FULL;
+    if (pid) step_kernel<T, -1, 1><<<grid_for(P.Dpad), kBlock, 0, s>>>(P, b, action, obs, reward, te, tr, fl);
+    else step_kernel<T, -1, 0><<<grid_for(P.Dpad), kBlock, 0, s>>>(P, b, action, obs, reward, te, tr, fl);
+    return cudaGetLastError();
+}
+
+template <typename T>
+cudaError_t Launch<T>::set_state(const KParams<T>& P, const KBuffers<T>& b, const T* rows, cudaStream_t s)
+{
+    set_state_kernel<T><<<grid_for(P.Dpad), kBlock, 0, s>>>(P, b, rows);
+    return cudaGetLastError();
+}
+
+template <typename T>
+cudaError_t Launch<T>::get_state(const KParams<T>& P, const KBuffers<T>& b, T* rows, cudaStream_t s)
+{
+    get_state_kernel<T><<<grid_for(P.Dpad), kBlock, 0, s>>>(P, b, rows);
+    return cudaGetLastError();
+}
+
+template <typename T>
+cudaError_t Launch<T>::race_prepare(const RaceParams<T>& RP, const KParams<T>& P)
+{
+    const size_t bytes = race_smem_bytes(P, RP);
+    if (bytes <= 48 * 1024) return cudaSuccess;
+    cudaError_t e = cudaFuncSetAttribute(race_step_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(race_reset_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+}
+
+template <typename T>
+cudaError_t Launch<T>::race_reset(const KParams<T>& P, const RaceParams<T>& RP, const KBuffers<T>& b, const RaceBuffers<T>& rb,
+                                  const uint8_t* mask, const T* draws, T* obs, cudaStream_t s)
+{
+    race_reset_kernel<T><<<grid_for(P.Dpad), kBlock, race_smem_bytes(P, RP), s>>>(P, RP, b, rb, mask, draws, obs);
+    return cudaGetLastError();
+}
+
+template <typename T>
+cudaError_t Launch<T>::race_step(const KParams<T>& P, const RaceParams<T>& RP, const KBuffers<T>& b, const RaceBuffers<T>& rb,
+                                 const T* action, const T* noise, T* obs, T* reward, uint8_t* te, uint8_t* tr,
+                                 uint8_t* fl, cudaStream_t s)
+{
+    race_step_kernel<T><<<grid_for(P.Dpad), kBlock, race_smem_bytes(P, RP), s>>>(P, RP, b, rb, action, noise, obs, reward, te, tr, fl);
+    return cudaGetLastError();
+}
+
+template <typename T>
+cudaError_t Launch<T>::dslpid_rows(T pid_gravity, T pid_kf, int model, int n, T dt, const T* pos, const T* quat, const T* vel,
+                                   const T* tpos, const T* trpy, const T* tvel, const T* trates, T* ctrl, T* rpm, T* pos_e,
+                                   T* yaw_e, cudaStream_t s)
+{
+    dslpid_rows_kernel<T><<<(unsigned)((n + 127) / 128), 128, 0, s>>>(pid_gravity, pid_kf, model, n, dt, pos, quat, vel, tpos, trpy,
+                                                                      tvel, trates, ctrl, rpm, pos_e, yaw_e);
+    return cudaGetLastError();
+}
+
+}  // namespace adrp

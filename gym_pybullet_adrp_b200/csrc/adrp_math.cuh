@@ -21,6 +21,7 @@ template <> struct M<float> {
     static __device__ __forceinline__ float atan2(float y, float x) { return atan2f(y, x); }
     static __device__ __forceinline__ float asin(float x) { return asinf(x); }
     static __device__ __forceinline__ float exp(float x) { return expf(x); }
+    static __device__ __forceinline__ float log(float x) { return logf(x); }
     static __device__ __forceinline__ float abs(float x) { return fabsf(x); }
     static __device__ __forceinline__ float tan(float x) { return tanf(x); }
     static __device__ __forceinline__ float fmax(float a, float b) { return fmaxf(a, b); }
@@ -35,6 +36,7 @@ template <> struct M<double> {
     static __device__ __forceinline__ double atan2(double y, double x) { return ::atan2(y, x); }
     static __device__ __forceinline__ double asin(double x) { return ::asin(x); }
     static __device__ __forceinline__ double exp(double x) { return ::exp(x); }
+    static __device__ __forceinline__ double log(double x) { return ::log(x); }
     static __device__ __forceinline__ double abs(double x) { return ::fabs(x); }
     static __device__ __forceinline__ double tan(double x) { return ::tan(x); }
     static __device__ __forceinline__ double fmax(double a, double b) { return ::fmax(a, b); }

@@ -1,0 +1,218 @@
+// adrp_mellinger.cuh -- the race env's low-level controller as device functions, one call per drone
+// per physics SUBSTEP (500 Hz), state in registers.
+//
+//   mellinger_tick   MellingerControl.computeControl (control/MellingerControl.py:154-262): sensor
+//                    synthesis by finite differences (:206-214), _update_state (:446-471),
+//                    _update_sensorData gyro low-pass (:347-365), _step_controller tumble check and
+//                    sub-rate schedule (:378-419), _compute_pwms power distribution + battery curve
+//                    (:423-442), PWM -> thrust -> prop reorder -> noise -> _thr2pwm -> RPM (:246-262,
+//                    :307-343).  Wrapper arithmetic in T (the reference: float64).
+//   fw_mellinger     firmware core controllerMellinger() (pycffirmware, un-vendored, float32 C):
+//                    DECLARED restatement, statement order fixed so that the CPU checker can match it.
+//                    float32 in both builds; the fp64 (parity) translation unit is compiled with
+//                    -fmad=false so that no multiply-add is contracted, like the C build of the firmware.
+#pragma once
+#include "adrp_math.cuh"
+#include "adrp_params.cuh"
+
+namespace adrp {
+
+// libm float functions of the firmware.  Parity build (T = double): correctly rounded via the
+// double-precision function; fp32 build: CUDA's float functions.
+template <typename T> struct FwMath;
+template <> struct FwMath<double> {
+    static __device__ __forceinline__ float atan2(float y, float x) { return (float)::atan2((double)y, (double)x); }
+    static __device__ __forceinline__ void sincos(float a, float* s, float* c) { *s = (float)::sin((double)a); *c = (float)::cos((double)a); }
+};
+template <> struct FwMath<float> {
+    static __device__ __forceinline__ float atan2(float y, float x) { return atan2f(y, x); }
+    static __device__ __forceinline__ void sincos(float a, float* s, float* c) { sincosf(a, s, c); }
+};
+
+struct MelFw {                       // controller_mellinger.c file-scope statics + control_t
+    float i_error_x, i_error_y, i_error_z, i_error_m_x, i_error_m_y, i_error_m_z;
+    float prev_omega_roll, prev_omega_pitch, prev_setpoint_omega_roll, prev_setpoint_omega_pitch;
+    float thrust;
+    int roll, pitch, yaw;            // int16 values
+};
+
+template <typename T>
+struct Mel {
+    V3<T> prev_rpy, prev_vel;        // wrapper state (MellingerControl.reset, :99-150)
+    T rpms[4];                       // MultiRaceAviary.rpms[i]: the command the physics applies next substep
+    float gd1[3], gd2[3];            // gyro lpf2p delay elements
+    MelFw fw;
+    float acc_z;                     // state_t.acc.z as stored (tumble check, :382)
+    int tick, tumble, last_att, error;
+};
+
+struct MelSetpoint { float pos[3], qz, qw; };   // full-state command: vel = acc = rates = 0, yaw-only quaternion (:510-543)
+
+__device__ __forceinline__ float fw_clamp(float v, float lo, float hi) { return v < lo ? lo : (v > hi ? hi : v); }
+__device__ __forceinline__ float fw_radians(float d) { return (3.14159265358979323846f / 180.0f) * d; }
+__device__ __forceinline__ float fw_degrees(float r) { return (180.0f / 3.14159265358979323846f) * r; }
+
+// filter.c lpf2pApply
+__device__ __forceinline__ float fw_lpf2p(float b0, float b1, float b2, float a1, float a2, float& d1, float& d2, float sample)
+{
+    float d0 = sample - d1 * a1 - d2 * a2;
+    if (!isfinite(d0)) d0 = sample;
+    const float out = d0 * b0 + d1 * b1 + d2 * b2;
+    d2 = d1;
+    d1 = d0;
+    return out;
+}
+
+// controllerMellinger() with mode.x/y/z/quat = modeAbs, roll/pitch/yaw = modeDisable.
+template <typename T>
+__device__ __forceinline__ void fw_mellinger(MelFw& m, const MelSetpoint& sp, float mass, const float pos[3],
+                                             const float vel[3], const float q[4], const float gyro_deg[3])
+{
+    const float massThrust = 132000.0f;
+    const float kp_xy = 0.4f, kd_xy = 0.2f, ki_xy = 0.05f, i_range_xy = 2.0f;
+    const float kp_z = 1.25f, kd_z = 0.4f, ki_z = 0.05f, i_range_z = 0.4f;
+    const float kR_xy = 70000.0f, kw_xy = 20000.0f, ki_m_xy = 0.0f, i_range_m_xy = 1.0f;
+    const float kR_z = 60000.0f, kw_z = 12000.0f, ki_m_z = 500.0f, i_range_m_z = 1500.0f;
+    const float kd_omega_rp = 200.0f, GRAVITY_MAGNITUDE = 9.81f;
+    const float dt = (float)(1.0f / 500.0f);
+    const float sp_vel = 0.0f, sp_acc = 0.0f, sp_rate_deg = 0.0f;
+    float r_error[3], v_error[3], tt[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { r_error[k] = sp.pos[k] - pos[k]; v_error[k] = sp_vel - vel[k]; }
+    m.i_error_z += r_error[2] * dt; m.i_error_z = fw_clamp(m.i_error_z, -i_range_z, i_range_z);
+    m.i_error_x += r_error[0] * dt; m.i_error_x = fw_clamp(m.i_error_x, -i_range_xy, i_range_xy);
+    m.i_error_y += r_error[1] * dt; m.i_error_y = fw_clamp(m.i_error_y, -i_range_xy, i_range_xy);
+    tt[0] = mass * sp_acc + kp_xy * r_error[0] + kd_xy * v_error[0] + ki_xy * m.i_error_x;
+    tt[1] = mass * sp_acc + kp_xy * r_error[1] + kd_xy * v_error[1] + ki_xy * m.i_error_y;
+    tt[2] = mass * (sp_acc + GRAVITY_MAGNITUDE) + kp_z * r_error[2] + kd_z * v_error[2] + ki_z * m.i_error_z;
+    // desired yaw from the setpoint quaternion (0, 0, qz, qw), in degrees
+    const float sx = 0.0f, sy = 0.0f, sz = sp.qz, sw = sp.qw;
+    const float desiredYaw = fw_degrees(FwMath<T>::atan2(2.0f * (sw * sz + sx * sy), 1 - 2 * (sy * sy + sz * sz)));
+    const float x = q[0], y = q[1], z = q[2], w = q[3];
+    const float R00 = 1 - 2 * y * y - 2 * z * z, R01 = 2 * x * y - 2 * z * w, R02 = 2 * x * z + 2 * y * w;
+    const float R10 = 2 * x * y + 2 * z * w, R11 = 1 - 2 * x * x - 2 * z * z, R12 = 2 * y * z - 2 * x * w;
+    const float R20 = 2 * x * z - 2 * y * w, R21 = 2 * y * z + 2 * x * w, R22 = 1 - 2 * x * x - 2 * y * y;
+    const float current_thrust = tt[0] * R02 + tt[1] * R12 + tt[2] * R22;
+    const float nt = sqrtf(tt[0] * tt[0] + tt[1] * tt[1] + tt[2] * tt[2]);
+    const float zd0 = tt[0] / nt, zd1 = tt[1] / nt, zd2 = tt[2] / nt;
+    float xc0, xc1;
+    FwMath<T>::sincos(fw_radians(desiredYaw), &xc1, &xc0);
+    const float xc2 = 0.0f;
+    float yd0 = zd1 * xc2 - zd2 * xc1, yd1 = zd2 * xc0 - zd0 * xc2, yd2 = zd0 * xc1 - zd1 * xc0;
+    const float ny = sqrtf(yd0 * yd0 + yd1 * yd1 + yd2 * yd2);
+    yd0 /= ny; yd1 /= ny; yd2 /= ny;
+    const float xd0 = yd1 * zd2 - yd2 * zd1, xd1 = yd2 * zd0 - yd0 * zd2, xd2 = yd0 * zd1 - yd1 * zd0;
+    // eRM = Rdes^T R - R^T Rdes with Rdes = [xd yd zd] (columns): Rd[k][0] = xd_k, Rd[k][1] = yd_k, Rd[k][2] = zd_k
+    float e21 = 0, e02 = 0, e10 = 0;
+    e21 += zd0 * R01 - R02 * yd0; e02 += xd0 * R02 - R00 * zd0; e10 += yd0 * R00 - R01 * xd0;
+    e21 += zd1 * R11 - R12 * yd1; e02 += xd1 * R12 - R10 * zd1; e10 += yd1 * R10 - R11 * xd1;
+    e21 += zd2 * R21 - R22 * yd2; e02 += xd2 * R22 - R20 * zd2; e10 += yd2 * R20 - R21 * xd2;
+    const float eR0 = e21, eR1 = -e02, eR2 = e10;
+    const float rate_roll = fw_radians(gyro_deg[0]), rate_pitch = -fw_radians(gyro_deg[1]), rate_yaw = fw_radians(gyro_deg[2]);
+    const float ew0 = fw_radians(sp_rate_deg) - rate_roll, ew1 = -fw_radians(sp_rate_deg) - rate_pitch,
+                ew2 = fw_radians(sp_rate_deg) - rate_yaw;
+    const float err_d_roll = ((fw_radians(sp_rate_deg) - m.prev_setpoint_omega_roll) - (rate_roll - m.prev_omega_roll)) / dt;
+    const float err_d_pitch = (-(fw_radians(sp_rate_deg) - m.prev_setpoint_omega_pitch) - (rate_pitch - m.prev_omega_pitch)) / dt;
+    m.prev_omega_roll = rate_roll; m.prev_omega_pitch = rate_pitch;
+    m.prev_setpoint_omega_roll = fw_radians(sp_rate_deg);
+    m.prev_setpoint_omega_pitch = fw_radians(sp_rate_deg);
+    m.i_error_m_x += (-eR0) * dt; m.i_error_m_x = fw_clamp(m.i_error_m_x, -i_range_m_xy, i_range_m_xy);
+    m.i_error_m_y += (-eR1) * dt; m.i_error_m_y = fw_clamp(m.i_error_m_y, -i_range_m_xy, i_range_m_xy);
+    m.i_error_m_z += (-eR2) * dt; m.i_error_m_z = fw_clamp(m.i_error_m_z, -i_range_m_z, i_range_m_z);
+    const float Mx = -kR_xy * eR0 + kw_xy * ew0 + ki_m_xy * m.i_error_m_x + kd_omega_rp * err_d_roll;
+    const float My = -kR_xy * eR1 + kw_xy * ew1 + ki_m_xy * m.i_error_m_y + kd_omega_rp * err_d_pitch;
+    const float Mz = -kR_z * eR2 + kw_z * ew2 + ki_m_z * m.i_error_m_z;
+    m.thrust = massThrust * current_thrust;
+    if (m.thrust > 0) {
+        m.roll = (int)(short)fw_clamp(Mx, -32000, 32000);
+        m.pitch = (int)(short)fw_clamp(My, -32000, 32000);
+        m.yaw = (int)(short)fw_clamp(-Mz, -32000, 32000);
+    } else {
+        m.roll = m.pitch = m.yaw = 0;
+        m.i_error_x = m.i_error_y = m.i_error_z = 0;          // controllerMellingerReset()
+        m.i_error_m_x = m.i_error_m_y = m.i_error_m_z = 0;
+    }
+}
+
+// (tick/500 - last/500 > 0.002) exactly as Python evaluates it in float64 (:395-411): always true for a gap
+// of two or more ticks, never for a gap of zero; for a gap of one it depends on the rounding of tick/500,
+// which the host tabulates once (bit `tick` of lut).
+template <typename T>
+__device__ __forceinline__ bool mel_schedule_fires(const RaceParams<T>& RP, const uint32_t* __restrict__ lut, int tick, int last)
+{
+    const int gap = tick - last;
+    if (gap != 1) return gap > 1;
+    if (tick < RP.lut_ticks) return (__ldg(lut + (tick >> 5)) >> (tick & 31)) & 1u;
+    return (double)tick / 500.0 - (double)last / 500.0 > 0.002;
+}
+
+// One 500 Hz tick.  p, q, v: the drone's state AFTER this substep's physics.  noise4: motor thrust noise (N).
+template <typename T>
+__device__ __forceinline__ void mellinger_tick(const RaceParams<T>& RP, const uint32_t* __restrict__ lut, Mel<T>& m,
+                                               const MelSetpoint& sp, const V3<T>& p, const Q4<T>& q, const V3<T>& v,
+                                               const T noise4[4])
+{
+    const T FIRMWARE_DT = (T)(1.0 / 500), RAD_TO_DEG = (T)(180.0 / 3.14159265358979323846), DEG_TO_RAD = (T)(3.14159265358979323846 / 180.0);
+    const V3<T> rpy = euler_rpy(q);                                              // obs[i, 3:6] (:242)
+    const T rates[3] = {(rpy.x - m.prev_rpy.x) / FIRMWARE_DT, (rpy.y - m.prev_rpy.y) / FIRMWARE_DT,
+                        (rpy.z - m.prev_rpy.z) / FIRMWARE_DT};                   // :209
+    m.prev_rpy = rpy;
+    const T acc_z = (v.z - m.prev_vel.z) / FIRMWARE_DT / T(9.8) + T(1);          // :213 (only acc.z is read downstream)
+    m.prev_vel = v;
+    // _update_state (:446-471): degrees and back, then utils.get_quaternion_from_euler (utils/utils.py:20-43)
+    const T rdx = rpy.x * RAD_TO_DEG * DEG_TO_RAD, rdy = rpy.y * RAD_TO_DEG * DEG_TO_RAD, rdz = rpy.z * RAD_TO_DEG * DEG_TO_RAD;
+    T sr, cr, sp_, cp, sy, cy;
+    M<T>::sincos(rdx / T(2), &sr, &cr);
+    M<T>::sincos(rdy / T(2), &sp_, &cp);
+    M<T>::sincos(rdz / T(2), &sy, &cy);
+    const float qf[4] = {(float)(sr * cp * cy - cr * sp_ * sy), (float)(cr * sp_ * cy + sr * cp * sy),
+                         (float)(cr * cp * sy - sr * sp_ * cy), (float)(cr * cp * cy + sr * sp_ * sy)};
+    const float pos[3] = {(float)p.x, (float)p.y, (float)p.z}, vel[3] = {(float)v.x, (float)v.y, (float)v.z};
+    m.acc_z = (float)acc_z;
+    // _update_sensorData (:347-365): gyro in deg/s through lpf2p
+    float gyro[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+        gyro[k] = fw_lpf2p(RP.lpf_b0, RP.lpf_b1, RP.lpf_b2, RP.lpf_a1, RP.lpf_a2, m.gd1[k], m.gd2[k], (float)(rates[k] * RAD_TO_DEG));
+    // _step_controller (:378-419)
+    T pwms[4] = {T(0), T(0), T(0), T(0)};
+    if (m.acc_z < -0.5f) m.tumble += 1; else m.tumble = 0;                       // :382-385
+    if (m.tumble >= 30) {
+        m.tick += 1; m.error = 1;                                                // :387-391: zero PWM
+    } else {
+        if (mel_schedule_fires(RP, lut, m.tick, m.last_att)) {
+            m.last_att = m.tick;
+            fw_mellinger<T>(m.fw, sp, RP.mel_mass, pos, vel, qf, gyro);
+        }
+        m.tick += 1;
+        // _compute_pwms (:423-442)
+        const T r = (T)m.fw.roll / T(2), pp = (T)m.fw.pitch / T(2), y = (T)m.fw.yaw, t = (T)m.fw.thrust;
+        const T th[4] = {t - r + pp + y, t - r - pp - y, t + r - pp + y, t + r + pp - y};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const T x = clampT(th[k], T(0), T(65535)) / T(65535) * T(60);
+            const T volts = T(-0.0006239) * (x * x) + T(0.088) * x;
+            const T pct = volts / T(3) < T(1) ? volts / T(3) : T(1);
+            pwms[k] = pct * T(65535);
+        }
+    }
+    // :246-262
+    const T KF = T(3.16e-10), SCALE = T(0.2685), CONST = T(4070.3);
+    T thrust[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const T c = clampT(pwms[k], T(20000), T(65535));
+        const T rp = SCALE * c + CONST;
+        thrust[k] = KF * (rp * rp);
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        T tk = thrust[3 - k] + noise4[k];                                        // thrust[[3,2,1,0]] + disturbance (:250-253)
+        if (tk < T(0)) tk = T(0);                                                // _thr2pwm (:307-343)
+        T pwm = (M<T>::sqrt(tk / T(1) / KF) - CONST) / SCALE;
+        pwm = clampT(pwm, T(20000), T(65535));
+        m.rpms[k] = SCALE * pwm + CONST;
+    }
+}
+
+}  // namespace adrp

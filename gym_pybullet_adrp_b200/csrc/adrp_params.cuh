@@ -27,8 +27,51 @@ struct KParams {
     T dt, ctrl_dt, g;
     T pid_gravity, pid_kf;                // DSLPIDControl's own URDF constants (control/BaseControl.py:35-39)
     T hover_lim;                          // 1.5 (HoverAviary.py:108) or 2.0 (MultiHoverAviary.py:121)
-    T init_xyz[ADRP_MAX_DRONES][3], init_quat[ADRP_MAX_DRONES][4], init_vel[ADRP_MAX_DRONES][3],
+    T init_xyz[ADRP_MAX_DRONES][3], init_rpy[ADRP_MAX_DRONES][3], init_quat[ADRP_MAX_DRONES][4], init_vel[ADRP_MAX_DRONES][3],
         init_pqr[ADRP_MAX_DRONES][3], target[ADRP_MAX_DRONES][3];
+};
+
+// Race env constants (envs/MultiRaceAviary.py; config/level*.yaml), by value next to KParams.
+constexpr int kGateFields = 6;           // x y z yaw cos(yaw) sin(yaw) of the ACTUAL (randomised) gate
+constexpr int kObstFields = 3;           // x y z of the actual obstacle
+template <typename T>
+struct RaceParams {
+    int G, NO;                            // gates, obstacles
+    int TF;                               // track fields per env = kGateFields*G + kObstFields*NO
+    int R;                                // uniform draws per env reset = 3G + 2NO + 10M
+    int compete;                          // RaceMode.COMPETE
+    int rnd_track, rnd_state, rnd_inertia, disturbances;
+    int lut_ticks;                        // length (bits) of the sub-rate schedule LUT
+    unsigned seed_lo, seed_hi;            // Philox key
+    unsigned long long env_offset;        // global index of env 0 of this shard
+    T gate_nom[ADRP_MAX_GATES][4];        // nominal x y z yaw
+    int gate_type[ADRP_MAX_GATES];
+    T obst_nom[ADRP_MAX_OBSTACLES][3];
+    T bounds_hi[3], contact_margin, visibility;
+    T gate_lo, gate_hi, obst_lo, obst_hi, pos_lo[3], pos_hi[3], rot_lo[3], rot_hi[3];
+    T inertia_lo[4], inertia_hi[4];       // mass, Ixx, Iyy, Izz offsets
+    T noise_std, wind_lo[3], wind_hi[3];
+    T mel_prev_rpy[ADRP_MAX_DRONES][3];   // init_rpy * pi/180 (MellingerControl.reset, :99-150)
+    float mel_mass;                       // firmware g_vehicleMass
+    float lpf_b0, lpf_b1, lpf_b2, lpf_a1, lpf_a2;   // gyro lpf2p coefficients (host: filter.c lpf2pSetCutoffFreq)
+};
+
+// Mellinger wrapper + firmware state per drone, SoA like the rigid-body state.
+enum MelT { MT_PRPY0 = 0, MT_PRPY1, MT_PRPY2, MT_PVEL0, MT_PVEL1, MT_PVEL2, MT_RPM0, MT_RPM1, MT_RPM2, MT_RPM3, MT_COUNT };
+enum MelF { MF_GD1X = 0, MF_GD1Y, MF_GD1Z, MF_GD2X, MF_GD2Y, MF_GD2Z, MF_IEX, MF_IEY, MF_IEZ, MF_IMX, MF_IMY, MF_IMZ,
+            MF_POR, MF_POP, MF_PSR, MF_PSP, MF_THRUST, MF_ACCZ, MF_COUNT };
+enum MelI { MI_TICK = 0, MI_TUMBLE, MI_LAST_ATT, MI_CTL_RP, MI_CTL_Y_ERR, MI_COUNT };   // CTL_RP = roll | pitch<<16; CTL_Y_ERR = yaw | error<<16
+
+template <typename T>
+struct RaceBuffers {
+    T* track;               // [TF][N]      actual gates / obstacles of each env
+    T* body;                // [4][Dpad]    Bullet mass, Ixx, Iyy, Izz of each drone (_drone_init, :409-431)
+    T* mel_t;               // [MT_COUNT][Dpad]
+    float* mel_f;           // [MF_COUNT][Dpad]
+    int32_t* mel_i;         // [MI_COUNT][Dpad]
+    int32_t* gate_latch;    // [Dpad]       current_gate | latch<<16
+    int32_t* episode;       // [N]          resets so far (Philox counter word)
+    const uint32_t* lut;    // [lut_ticks/32] bit t: (t/500 - (t-1)/500 > 0.002) in float64 (MellingerControl.py:395-411)
 };
 
 // Device buffers owned by the handle.

@@ -102,19 +102,17 @@ __device__ __forceinline__ void dyn_substep(const KParams<T>& P, Drone<T>& d, co
 // Bullet free body.  fz: total body-z force at the props + downwash; tb: body torque; fext: world force.
 template <typename T>
 __device__ __forceinline__ void pyb_substep(const KParams<T>& P, int phy, Drone<T>& d, const Mat3<T>& R, T fz,
-                                            const V3<T>& tb, const V3<T>& fext)
+                                            const V3<T>& tb, const V3<T>& fext, T m, T jx, T jy, T jz)
 {
-    const T m = P.pyb_mass;
     // world -> base frame
     const V3<T> fw = {R.m02 * fz + fext.x, R.m12 * fz + fext.y, R.m22 * fz + fext.z - m * P.g};
     const V3<T> f_l = mulT(R, fw), v_l = mulT(R, d.v), w_l = mulT(R, d.w);
     const T vn = M<T>::sqrt(dot(v_l, v_l)), wn = M<T>::sqrt(dot(w_l, w_l));
-    const V3<T> Jw = {P.pyb_jx * w_l.x, P.pyb_jy * w_l.y, P.pyb_jz * w_l.z};
+    const V3<T> Jw = {jx * w_l.x, jy * w_l.y, jz * w_l.z};
     const V3<T> gy = cross(w_l, Jw);
     const T kl = P.lin_damp + P.lin_damp * vn, ka = P.ang_damp + P.ang_damp * wn;
     const V3<T> a_l = {(f_l.x - m * v_l.x * kl) / m, (f_l.y - m * v_l.y * kl) / m, (f_l.z - m * v_l.z * kl) / m};
-    const V3<T> al_l = {(tb.x - Jw.x * ka - gy.x) / P.pyb_jx, (tb.y - Jw.y * ka - gy.y) / P.pyb_jy,
-                        (tb.z - Jw.z * ka - gy.z) / P.pyb_jz};
+    const V3<T> al_l = {(tb.x - Jw.x * ka - gy.x) / jx, (tb.y - Jw.y * ka - gy.y) / jy, (tb.z - Jw.z * ka - gy.z) / jz};
     const V3<T> a_w = mul(R, a_l), al_w = mul(R, al_l);
     d.v = {d.v.x + P.dt * a_w.x, d.v.y + P.dt * a_w.y, d.v.z + P.dt * a_w.z};
     d.w = {d.w.x + P.dt * al_w.x, d.w.y + P.dt * al_w.y, d.w.z + P.dt * al_w.z};

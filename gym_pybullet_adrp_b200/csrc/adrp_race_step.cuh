@@ -1,0 +1,274 @@
+// adrp_race_step.cuh -- kernels of the race env (included by adrp_race.cuh).
+#pragma once
+
+namespace adrp {
+
+// Env.reset for the masked envs (MultiRaceAviary.reset, :127-167); writes the initial observation if asked.
+template <typename T>
+__global__ void __launch_bounds__(kBlock)
+race_reset_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ RaceParams<T> RP, const KBuffers<T> b,
+                  const RaceBuffers<T> rb, const uint8_t* __restrict__ mask, const T* __restrict__ draws, T* __restrict__ obs)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    T* trk = reinterpret_cast<T*>(smem_raw);
+    const long long t = (long long)blockIdx.x * kBlock + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int i = (int)(t & (P.Mpad - 1));
+    const long long env = t / P.Mpad;
+    const int EPB = kBlock / P.Mpad, e = threadIdx.x / P.Mpad;
+    const bool valid = env < P.N && i < P.M;
+    const bool mine = valid && (!mask || mask[env]);
+    Drone<T> d;
+    Mel<T> m;
+    T body[4];
+    int episode = 0;
+    if (mine) episode = rb.episode[env];
+    __syncwarp();
+    if (mine) {
+        race_reset_drone(P, RP, rb, env, i, episode, draws, d, m, body);
+        store_drone(b, P.Dpad, t, d);
+        store_mel(rb, P.Dpad, t, m);
+        store_body(rb, P.Dpad, t, body);
+        rb.gate_latch[t] = 0;
+        if (i == 0) { rb.episode[env] = episode + 1; b.step_counter[env] = 0; }
+    }
+    if (!obs) return;
+    __syncthreads();                                           // track written above is read back below
+    if (valid && !mine) load_drone(b, P.Dpad, t, d);
+    if (!valid) init_drone(P, 0, d);
+    const long long env0 = (long long)blockIdx.x * EPB;
+    for (int idx = threadIdx.x; idx < RP.TF * EPB; idx += kBlock) {
+        const int f = idx / EPB, el = idx - f * EPB;
+        trk[idx] = env0 + el < P.N ? rb.track[(long long)f * P.N + env0 + el] : T(0);
+    }
+    __syncthreads();
+    const V3<T> rpy = euler_rpy(d.q);
+    const T hz = drone_half_height(P.coll_r, P.coll_h, rotmat(d.q).m22);
+    T* o = obs + (valid ? env * P.M + i : 0) * P.O;
+    const bool wr = mine;
+    race_write_obs(P, RP, trk, EPB, e, d, rpy, hz, wr ? (rb.gate_latch[t] & 0xffff) : 0, i, lane - i, wr, o);
+}
+
+// MultiRaceAviary.step (:171-270).  noise: NULL or (N, M, S, 7) = [wind force xyz (N), motor thrust noise x4 (N)].
+template <typename T>
+__global__ void __launch_bounds__(kBlock)
+race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ RaceParams<T> RP, const KBuffers<T> b,
+                 const RaceBuffers<T> rb, const T* __restrict__ action, const T* __restrict__ noise, T* __restrict__ obs,
+                 T* __restrict__ reward, uint8_t* __restrict__ terminated, uint8_t* __restrict__ truncated,
+                 uint8_t* __restrict__ drone_flags)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    T* trk = reinterpret_cast<T*>(smem_raw);
+    const long long t = (long long)blockIdx.x * kBlock + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int i = (int)(t & (P.Mpad - 1));
+    const long long env = t / P.Mpad;
+    const int lane_base = lane - i;
+    const int EPB = kBlock / P.Mpad, e = threadIdx.x / P.Mpad;
+    const bool valid = env < P.N && i < P.M;
+    const long long D = P.Dpad;
+    const int phy = P.physics;
+    const long long od = valid ? env * P.M + i : 0;
+
+    // ---- stage the block's track instances (coalesced over envs) in shared memory
+    const long long env0 = (long long)blockIdx.x * EPB;
+    for (int idx = threadIdx.x; idx < RP.TF * EPB; idx += kBlock) {
+        const int f = idx / EPB, el = idx - f * EPB;
+        trk[idx] = env0 + el < P.N ? rb.track[(long long)f * P.N + env0 + el] : T(0);
+    }
+
+    Drone<T> d;
+    Mel<T> m;
+    T body[4] = {P.pyb_mass, P.pyb_jx, P.pyb_jy, P.pyb_jz};
+    int gl = 0, counter = 0, episode = 0;
+    if (valid) {
+        load_drone(b, D, t, d);
+        load_mel(rb, D, t, m);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) body[k] = ld(rb.body, D, k, t);
+        gl = rb.gate_latch[t];
+        counter = b.step_counter[env];
+        episode = rb.episode[env];
+    } else {
+        init_drone(P, 0, d);
+        m = Mel<T>{};
+    }
+    int current_gate = gl & 0xffff, latch = gl >> 16;
+    const bool eliminated = (latch & ADRP_FLAG_ELIMINATED) != 0;
+
+    // ---- ndarray action -> FULLSTATE(pos, 0, 0, yaw, 0, step_counter) (:190-202)
+    MelSetpoint sp = {{0.0f, 0.0f, 0.0f}, 0.0f, 1.0f};
+    if (valid && !eliminated) {
+        const T* a = action + od * 4;
+        sp.pos[0] = (float)a[0]; sp.pos[1] = (float)a[1]; sp.pos[2] = (float)a[2];
+        T sy, cy;
+        M<T>::sincos(a[3] / T(2), &sy, &cy);                  // utils.get_quaternion_from_euler(0, 0, yaw)
+        sp.qz = (float)sy; sp.qw = (float)cy;
+    }
+
+    // ---- S fused substeps (:210-254)
+    for (int s = 0; s < P.S; ++s) {
+        // disturbance draws of this substep: injected, or Philox(seed; env, drone, tick, episode)
+        T nz[7] = {T(0), T(0), T(0), T(0), T(0), T(0), T(0)};
+        if (noise) {
+            if (valid) {
+                const T* np_ = noise + ((od * P.S) + s) * 7;
+#pragma unroll
+                for (int k = 0; k < 7; ++k) nz[k] = np_[k];
+            }
+        } else if (RP.disturbances) {
+            uint32_t o0[4], o1[4];
+            const uint32_t genv = (uint32_t)(RP.env_offset + (unsigned long long)env), tick = (uint32_t)(counter + s);
+            philox4x32(genv, (uint32_t)(64 + i), tick, (uint32_t)episode, RP.seed_lo, RP.seed_hi, o0);
+            philox4x32(genv, (uint32_t)(128 + i), tick, (uint32_t)episode, RP.seed_lo, RP.seed_hi, o1);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) nz[k] = RP.wind_lo[k] + u01<T>(o0[k]) * (RP.wind_hi[k] - RP.wind_lo[k]);
+            const T r0 = M<T>::sqrt(T(-2) * M<T>::log(u01_open<T>(o1[0]))), r1 = M<T>::sqrt(T(-2) * M<T>::log(u01_open<T>(o1[2])));
+            const T a0 = T(6.283185307179586) * u01<T>(o1[1]), a1 = T(6.283185307179586) * u01<T>(o1[3]);
+            T s0, c0, s1, c1;
+            M<T>::sincos(a0, &s0, &c0);
+            M<T>::sincos(a1, &s1, &c1);
+            nz[3] = RP.noise_std * r0 * c0; nz[4] = RP.noise_std * r0 * s0;
+            nz[5] = RP.noise_std * r1 * c1; nz[6] = RP.noise_std * r1 * s1;
+        }
+        // _apply_physics(self.rpms, self.prev_rpms) (:510-548): forces from the substep-start state
+        const Mat3<T> R = rotmat(d.q);
+        T f[4], tq[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { f[k] = m.rpms[k] * m.rpms[k] * P.kf; tq[k] = m.rpms[k] * m.rpms[k] * P.km; }
+        if (phy & ADRP_PHY_GND) {
+            T gnd[4];
+            ground_effect(P, d, R, f, gnd);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) f[k] += gnd[k];
+        }
+        V3<T> fext = {T(0), T(0), T(0)};
+        if (phy & ADRP_PHY_DRAG) {                             // prev_rpms = state row 16:20
+            const T sum = (T(2) * T(3.141592653589793) * d.last_rpm[0] / T(60) + T(2) * T(3.141592653589793) * d.last_rpm[1] / T(60)) +
+                          T(2) * T(3.141592653589793) * d.last_rpm[2] / T(60) + T(2) * T(3.141592653589793) * d.last_rpm[3] / T(60);
+            fext = {-P.drag_xy * sum * d.v.x, -P.drag_xy * sum * d.v.y, -P.drag_z * sum * d.v.z};
+        }
+        T dw = T(0);
+        if (phy & ADRP_PHY_DW) dw = downwash(P, d.p, lane_base, valid);
+        if (phy & ADRP_PHY_DYN) {
+            dyn_substep(P, d, R, f, tq, dw, fext);
+        } else {
+            const T fz = dw + f[0] + f[1] + f[2] + f[3];
+            const V3<T> tb = {P.prop_y[0] * f[0] + P.prop_y[1] * f[1] + P.prop_y[2] * f[2] + P.prop_y[3] * f[3],
+                              -P.prop_x[0] * f[0] - P.prop_x[1] * f[1] - P.prop_x[2] * f[2] - P.prop_x[3] * f[3],
+                              tq[0] - tq[1] + tq[2] - tq[3]};                            // BaseAviary.py:703
+            const V3<T> fw = {fext.x + nz[0], fext.y + nz[1], fext.z + nz[2]};         // drag + wind (:532-544)
+            pyb_substep(P, phy, d, R, fz, tb, fw, body[0], body[1], body[2], body[3]);
+        }
+        // controller round trip (:231-254)
+        if (eliminated) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { d.last_rpm[k] = T(0); m.rpms[k] = T(0); }      // :233-235
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) d.last_rpm[k] = m.rpms[k];                       // prev_rpms[i] = rpms[i] (:251)
+            mellinger_tick(RP, rb.lut, m, sp, d.p, d.q, d.v, nz + 3);                    // rpms[i] = recv() (:254)
+        }
+    }
+    __syncthreads();                                                                     // shared track is complete
+
+    // ---- _gate_progress (:471-506): 7 vertical rays through the drone's current gate; the gate counts as
+    // passed when the first body hit along any ray is this drone
+    const Mat3<T> Rn = rotmat(d.q);
+    const V3<T> axis = {Rn.m02, Rn.m12, Rn.m22};
+    {
+        const bool active = valid && RP.G > 0 && current_gate < RP.G;
+        const int g = active ? current_gate : 0;
+        const T* tg = trk + (kGateFields * g) * EPB + e;
+        const T gx = RP.G > 0 ? tg[0] : T(0), gy = RP.G > 0 ? tg[EPB] : T(0);
+        const T gc = RP.G > 0 ? tg[4 * EPB] : T(1), gs = RP.G > 0 ? tg[5 * EPB] : T(0);
+        const T height = RP.gate_type[g] == 0 ? T(1.0) : T(0.525);                       // :479-482
+        const T half_length = T(0.1875);
+        const T delta_x = T(0.05) * gc, delta_y = T(0.05) * gs;
+        const V3<T> dir = {T(0), T(0), (height + half_length) - (height - half_length)};
+        T best[7];
+        int best_id[7];
+#pragma unroll
+        for (int k = 0; k < 7; ++k) { best[k] = T(-1); best_id[k] = -1; }
+        for (int j = 0; j < P.Mpad; ++j) {
+            const int src = lane_base + j;
+            const V3<T> cj = {__shfl_sync(0xffffffffu, d.p.x, src), __shfl_sync(0xffffffffu, d.p.y, src), __shfl_sync(0xffffffffu, d.p.z, src)};
+            const V3<T> aj = {__shfl_sync(0xffffffffu, axis.x, src), __shfl_sync(0xffffffffu, axis.y, src), __shfl_sync(0xffffffffu, axis.z, src)};
+            if (!active || j >= P.M) continue;
+#pragma unroll
+            for (int k = 0; k < 7; ++k) {
+                // ray order of the reference: centre, +1, -1, +2, -2, +3, -3
+                const int mult = k == 0 ? 0 : ((k + 1) / 2) * ((k & 1) ? 1 : -1);
+                const V3<T> fr = {gx + (T)mult * delta_x, gy + (T)mult * delta_y, height - half_length};
+                const T th = ray_cylinder(fr, dir, cj, aj, P.coll_r, T(0.5) * P.coll_h);
+                if (th >= T(0) && (best[k] < T(0) || th < best[k])) { best[k] = th; best_id[k] = j; }
+            }
+        }
+        bool passed = false;
+#pragma unroll
+        for (int k = 0; k < 7; ++k) passed = passed || (best_id[k] == i && best[k] < T(0.9999));   // :502
+        if (valid && current_gate >= RP.G) latch |= ADRP_FLAG_FINISHED;                  // :505-506 (one step late)
+        if (active && passed) current_gate += 1;
+    }
+
+    // ---- observation (:566-661)
+    const V3<T> rpy = euler_rpy(d.q);
+    const T hz = drone_half_height(P.coll_r, P.coll_h, Rn.m22);
+    race_write_obs(P, RP, trk, EPB, e, d, rpy, hz, current_gate, i, lane_base, valid, obs + od * P.O);
+
+    // ---- _computeTerminated (:674-698) with _collision (:552-562)
+    int fl = 0;
+    if (M<T>::abs(d.p.x) > RP.bounds_hi[0] || M<T>::abs(d.p.y) > RP.bounds_hi[1] || M<T>::abs(d.p.z) > RP.bounds_hi[2]) fl |= ADRP_FLAG_OUT_OF_BOUNDS;   // :684
+    if (M<T>::abs(d.w.x) > T(20) || M<T>::abs(d.w.y) > T(20) || M<T>::abs(d.w.z) > T(20)) fl |= ADRP_FLAG_UNSTABLE;                                      // :685
+    if (!(phy & ADRP_PHY_DYN)) {                               // getContactPoints reflects the last stepSimulation: never in DYN
+        bool crashed = false;
+        for (int g = 0; g < RP.G; ++g) {
+            const T* tg = trk + (kGateFields * g) * EPB + e;
+            crashed = crashed || gate_distance(d.p, hz, P.coll_r, tg[0], tg[EPB], tg[2 * EPB], tg[4 * EPB], tg[5 * EPB], RP.gate_type[g]) < RP.contact_margin;
+        }
+        for (int ob = 0; ob < RP.NO; ++ob) {
+            const T* to = trk + (kGateFields * RP.G + kObstFields * ob) * EPB + e;
+            crashed = crashed || obstacle_distance(d.p, hz, P.coll_r, to[0], to[EPB], to[2 * EPB]) < RP.contact_margin;
+        }
+        crashed = crashed || (d.p.z - hz < RP.contact_margin);                           // plane
+        if (RP.compete) {                                                                // drones collide with each other (:153-154)
+            for (int j = 0; j < P.Mpad; ++j) {
+                const int src = lane_base + j;
+                const T ox = __shfl_sync(0xffffffffu, d.p.x, src), oy = __shfl_sync(0xffffffffu, d.p.y, src);
+                const T oz = __shfl_sync(0xffffffffu, d.p.z, src), ohz = __shfl_sync(0xffffffffu, hz, src);
+                if (j < P.M && j != i) {
+                    const T dxy = gap_circle_circle(d.p.x, d.p.y, P.coll_r, ox, oy, P.coll_r);
+                    crashed = crashed || combine_gaps(dxy, M<T>::abs(d.p.z - oz) - hz - ohz) < RP.contact_margin;
+                }
+            }
+        }
+        if (crashed) fl |= ADRP_FLAG_CRASHED;
+    }
+    if (fl) latch |= ADRP_FLAG_ELIMINATED;
+    if (m.error) fl |= ADRP_FLAG_TUMBLE_STOP;
+    const int not_done = valid && !(latch & (ADRP_FLAG_ELIMINATED | ADRP_FLAG_FINISHED));
+    const int term = group_or(not_done, P.Mpad) == 0;
+    const int trunc = counter >= P.trunc_steps;                                          // step_counter / PYB_FREQ > episode_len_sec (:709)
+    const bool done = P.auto_reset && (term || trunc);
+    if (valid && drone_flags) drone_flags[od] = (uint8_t)(fl | latch);
+    if (valid && i == 0) {
+        reward[env] = T(0);                                                              // :665-670
+        terminated[env] = (uint8_t)term;
+        truncated[env] = (uint8_t)trunc;
+    }
+    __syncwarp();
+    if (valid) {
+        if (done) {
+            race_reset_drone(P, RP, rb, env, i, episode, (const T*)nullptr, d, m, body);
+            store_body(rb, D, t, body);
+            current_gate = 0; latch = 0;
+            if (i == 0) rb.episode[env] = episode + 1;
+        }
+        if (i == 0) b.step_counter[env] = done ? 0 : counter + P.S;                      // BaseAviary.py:386
+        store_drone(b, D, t, d);
+        store_mel(rb, D, t, m);
+        rb.gate_latch[t] = current_gate | (latch << 16);
+    }
+}
+
+}  // namespace adrp

@@ -164,7 +164,7 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
             const V3<T> tb = {P.prop_y[0] * f[0] + P.prop_y[1] * f[1] + P.prop_y[2] * f[2] + P.prop_y[3] * f[3],
                               -(P.prop_x[0] * f[0] + P.prop_x[1] * f[1] + P.prop_x[2] * f[2] + P.prop_x[3] * f[3]),
                               tq[0] - tq[1] + tq[2] - tq[3]};                   // :703
-            pyb_substep(P, phy, d, R, fz, tb, fext);
+            pyb_substep(P, phy, d, R, fz, tb, fext, P.pyb_mass, P.pyb_jx, P.pyb_jy, P.pyb_jz);
         }
 #pragma unroll
         for (int k = 0; k < 4; ++k) d.last_rpm[k] = rpm[k];                      // :376

@@ -23,6 +23,11 @@
 #define EXP exp
 #define LOG log
 #define TAN tan
+/* libm float functions of the firmware core in the parity (f64) build: correctly rounded, so that the
+ * CUDA fp64 build can reproduce them bit for bit through its own double-precision functions */
+#define FW_ATAN2F(y, x) ((float)atan2((double)(y), (double)(x)))
+#define FW_SINF(x) ((float)sin((double)(x)))
+#define FW_COSF(x) ((float)cos((double)(x)))
 #include "adrp_oracle_impl.h"
 #include "adrp_oracle_race.h"
 #include "adrp_oracle_api.h"
@@ -37,6 +42,9 @@
 #undef EXP
 #undef LOG
 #undef TAN
+#undef FW_ATAN2F
+#undef FW_SINF
+#undef FW_COSF
 #undef CAT2
 #undef CAT
 #undef FN
@@ -52,6 +60,9 @@
 #define EXP expf
 #define LOG logf
 #define TAN tanf
+#define FW_ATAN2F(y, x) atan2f((y), (x))
+#define FW_SINF(x) sinf(x)
+#define FW_COSF(x) cosf(x)
 #include "adrp_oracle_impl.h"
 #include "adrp_oracle_race.h"
 #include "adrp_oracle_api.h"
@@ -109,6 +120,18 @@ int orc_step(void* h, const void* action, const void* noise, void* obs, void* re
     return ADRP_OK;
 }
 
+/* Race env: only the part of the step after the substep loop (gate progress, observation, flags, counters) on
+ * the state currently held -- lets a test evaluate the flag logic on the CUDA kernel's own trajectory. */
+int orc_race_post(void* h, void* obs, void* reward, uint8_t* terminated, uint8_t* truncated, uint8_t* drone_flags)
+{
+    if (DISPATCH(H64->race == NULL, H32->race == NULL)) return ADRP_EINVAL;
+    if (((orc_any*)h)->precision == ADRP_F64)
+        for (int n = 0; n < H64->N; ++n) race_post_env_f64(H64, n, (double*)obs, (double*)reward, terminated, truncated, drone_flags);
+    else
+        for (int n = 0; n < H32->N; ++n) race_post_env_f32(H32, n, (float*)obs, (float*)reward, terminated, truncated, drone_flags);
+    return ADRP_OK;
+}
+
 /* DSLPIDControl.computeControl on n rows (known-answer tests against tests/golden/dslpid_kat.npz). */
 int orc_dslpid_control(int precision, int drone_model, const adrp_drone_params* drone, double g, int n, double dt,
                        const void* pos, const void* quat, const void* vel, const void* tpos, const void* trpy,
@@ -141,7 +164,7 @@ float fw_lpf2p_apply(const float coef[5], float delay[2], float sample)
 void fw_controller_mellinger(float statics[10], const float sp[16], const float pos[3], const float vel[3],
                              const float q[4], const float gyro_deg[3], float mass, float out[4])
 {
-    mel_state_f32 m;
+    mel_state_f64 m;                 /* the pinned (parity-build) variant; the arithmetic is float32 either way */
     memset(&m, 0, sizeof(m));
     m.i_error_x = statics[0]; m.i_error_y = statics[1]; m.i_error_z = statics[2];
     m.i_error_m_x = statics[3]; m.i_error_m_y = statics[4]; m.i_error_m_z = statics[5];
@@ -149,7 +172,7 @@ void fw_controller_mellinger(float statics[10], const float sp[16], const float 
     m.prev_setpoint_omega_roll = statics[8]; m.prev_setpoint_omega_pitch = statics[9];
     memcpy(m.sp_pos, sp, 12); memcpy(m.sp_vel, sp + 3, 12); memcpy(m.sp_acc, sp + 6, 12);
     memcpy(m.sp_rate_deg, sp + 9, 12); memcpy(m.sp_quat, sp + 12, 16);
-    controller_mellinger_f32(&m, mass, pos, vel, q, gyro_deg);
+    controller_mellinger_f64(&m, mass, pos, vel, q, gyro_deg);
     statics[0] = m.i_error_x; statics[1] = m.i_error_y; statics[2] = m.i_error_z;
     statics[3] = m.i_error_m_x; statics[4] = m.i_error_m_y; statics[5] = m.i_error_m_z;
     statics[6] = m.prev_omega_roll; statics[7] = m.prev_omega_pitch;

@@ -1,7 +1,7 @@
 /* TEST INFRASTRUCTURE -- race env (envs/MultiRaceAviary.py) and Mellinger wrapper
  * (control/MellingerControl.py) restated on the CPU, REAL-generic; plus the DECLARED restatement of
  * the un-vendored firmware core (pycffirmware: controller_mellinger.c, filter.c lpf2p), which is
- * float32 in both builds.  PARITY UNPINNED for the firmware core and for the collision / ray queries
+ * float32 in both builds (its libm calls: FW_ATAN2F / FW_SINF / FW_COSF, see adrp_oracle.c).  PARITY UNPINNED for the firmware core and for the collision / ray queries
  * (oracle/track_geometry.py states the geometric model).  Included by adrp_oracle.c. */
 
 /* ---------------------------------------------------------------- Philox4x32-10 (Salmon et al. 2011) */
@@ -94,7 +94,7 @@ static void FN(controller_mellinger)(FN(mel_state)* m, float mass, const float p
     tt[2] = mass * (m->sp_acc[2] + GRAVITY_MAGNITUDE) + kp_z * r_error[2] + kd_z * v_error[2] + ki_z * m->i_error_z;
     /* desired yaw from the setpoint quaternion (mode.quat == modeAbs): quat2rpy().z in degrees */
     const float sx = m->sp_quat[0], sy = m->sp_quat[1], sz = m->sp_quat[2], sw = m->sp_quat[3];
-    float desiredYaw = FN(degreesf)(atan2f(2.0f * (sw * sz + sx * sy), 1 - 2 * (sy * sy + sz * sz)));
+    float desiredYaw = FN(degreesf)(FW_ATAN2F(2.0f * (sw * sz + sx * sy), 1 - 2 * (sy * sy + sz * sz)));
     /* R = quat2rotmat(state quaternion) */
     const float x = q[0], y = q[1], z = q[2], w = q[3];
     float R[3][3] = {{1 - 2 * y * y - 2 * z * z, 2 * x * y - 2 * z * w, 2 * x * z + 2 * y * w},
@@ -103,7 +103,7 @@ static void FN(controller_mellinger)(FN(mel_state)* m, float mass, const float p
     float current_thrust = tt[0] * R[0][2] + tt[1] * R[1][2] + tt[2] * R[2][2];
     float nt = sqrtf(tt[0] * tt[0] + tt[1] * tt[1] + tt[2] * tt[2]);
     float zd[3] = {tt[0] / nt, tt[1] / nt, tt[2] / nt};
-    float xc[3] = {cosf(FN(radiansf)(desiredYaw)), sinf(FN(radiansf)(desiredYaw)), 0};
+    float xc[3] = {FW_COSF(FN(radiansf)(desiredYaw)), FW_SINF(FN(radiansf)(desiredYaw)), 0};
     float yd[3] = {zd[1] * xc[2] - zd[2] * xc[1], zd[2] * xc[0] - zd[0] * xc[2], zd[0] * xc[1] - zd[1] * xc[0]};
     float ny = sqrtf(yd[0] * yd[0] + yd[1] * yd[1] + yd[2] * yd[2]);
     yd[0] /= ny; yd[1] /= ny; yd[2] /= ny;
@@ -516,6 +516,8 @@ static int FN(race_crashed)(FN(orc)* h, int n, int i)
     return 0;
 }
 
+static void FN(race_post_env)(FN(orc)* h, int n, REAL* obs, REAL* reward, uint8_t* te, uint8_t* tr, uint8_t* fl);
+
 /* MultiRaceAviary.step (:171-270) for env n.
  * noise: NULL or (N, M, S, 7) = [wind force xyz (N), motor thrust noise x4 (N)] per substep. */
 static void FN(race_step_env)(FN(orc)* h, int n, const REAL* action, const REAL* noise, REAL* obs, REAL* reward,
@@ -593,6 +595,15 @@ static void FN(race_step_env)(FN(orc)* h, int n, const REAL* action, const REAL*
             FN(mellinger_tick)(h, m, st, nz[i] + 3);                 /* rpms[i] = recv() (:254) */
         }
     }
+    FN(race_post_env)(h, n, obs, reward, te, tr, fl);
+}
+
+/* the part of MultiRaceAviary.step after the substep loop (:257-268): gate progress, observation, flags */
+static void FN(race_post_env)(FN(orc)* h, int n, REAL* obs, REAL* reward, uint8_t* te, uint8_t* tr, uint8_t* fl)
+{
+    FN(orc_race)* r = h->race;
+    const adrp_config* c = &h->cfg;
+    const int M = h->M, S = h->S, phy = c->physics;
     FN(gate_progress)(h, n);                                         /* :257-258 */
     FN(race_write_obs)(h, n, obs);                                   /* :261 */
     /* _computeTerminated (:674-698) */

@@ -32,6 +32,7 @@ def lib():
         _LIB.orc_reset.argtypes = [C.c_void_p] * 4
         _LIB.orc_set_state.argtypes = [C.c_void_p] * 2
         _LIB.orc_get_state.argtypes = [C.c_void_p] * 2
+        _LIB.orc_race_post.argtypes = [C.c_void_p] * 6
     return _LIB
 
 
@@ -84,6 +85,16 @@ class OracleEnv:
         te, tr = np.zeros(self.N, np.uint8), np.zeros(self.N, np.uint8)
         fl = np.zeros((self.N, self.M), np.uint8)
         lib().orc_step(self.h, _ptr(a), _ptr(nz), _ptr(obs), _ptr(rew), _ptr(te), _ptr(tr), _ptr(fl), nthreads)
+        return obs, rew, te, tr, fl
+
+    def race_post(self):
+        """Race env: gate progress, observation and flags of the state currently held (no substeps)."""
+        obs = np.zeros((self.N, self.M, self.O), self.dtype)
+        rew = np.zeros(self.N, self.dtype)
+        te, tr = np.zeros(self.N, np.uint8), np.zeros(self.N, np.uint8)
+        fl = np.zeros((self.N, self.M), np.uint8)
+        rc = lib().orc_race_post(self.h, _ptr(obs), _ptr(rew), _ptr(te), _ptr(tr), _ptr(fl))
+        assert rc == 0
         return obs, rew, te, tr, fl
 
 
