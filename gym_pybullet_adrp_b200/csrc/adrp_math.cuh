@@ -43,6 +43,13 @@ template <> struct M<double> {
     static __device__ __forceinline__ double fmin(double a, double b) { return ::fmin(a, b); }
 };
 
+// Product that is never contracted into a following add.  The motor thrusts / torques of a symmetric command
+// must cancel EXACTLY in the torque sums (as they do in the reference's float64 numpy): a fused multiply-add
+// would leave the rounding error of one product behind, and DSLPID's roll / yaw loops amplify any such seed
+// (SURVEY F5).  Everything else in the fp32 build is free to use FMA.
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+
 template <typename T> __device__ __forceinline__ T clampT(T v, T lo, T hi) { return v < lo ? lo : (v > hi ? hi : v); }
 
 template <typename T> struct V3 { T x, y, z; };

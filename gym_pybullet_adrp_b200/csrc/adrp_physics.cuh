@@ -30,7 +30,7 @@ __device__ __forceinline__ void ground_effect(const KParams<T>& P, const Drone<T
         T h = d.p.z + R.m20 * P.prop_x[i] + R.m21 * P.prop_y[i];
         h = M<T>::fmax(h, P.gnd_eff_h_clip);
         const T r = P.prop_radius / (T(4) * h);
-        gnd[i] = on ? rpm2kf[i] * P.gnd_eff_coeff * (r * r) : T(0);
+        gnd[i] = on ? mul_rn(rpm2kf[i] * P.gnd_eff_coeff, r * r) : T(0);
     }
 }
 

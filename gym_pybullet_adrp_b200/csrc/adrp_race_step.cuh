@@ -135,7 +135,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
         const Mat3<T> R = rotmat(d.q);
         T f[4], tq[4];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) { f[k] = m.rpms[k] * m.rpms[k] * P.kf; tq[k] = m.rpms[k] * m.rpms[k] * P.km; }
+        for (int k = 0; k < 4; ++k) { f[k] = mul_rn(m.rpms[k] * m.rpms[k], P.kf); tq[k] = mul_rn(m.rpms[k] * m.rpms[k], P.km); }
         if (phy & ADRP_PHY_GND) {
             T gnd[4];
             ground_effect(P, d, R, f, gnd);
@@ -154,8 +154,8 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
             dyn_substep(P, d, R, f, tq, dw, fext);
         } else {
             const T fz = dw + f[0] + f[1] + f[2] + f[3];
-            const V3<T> tb = {P.prop_y[0] * f[0] + P.prop_y[1] * f[1] + P.prop_y[2] * f[2] + P.prop_y[3] * f[3],
-                              -P.prop_x[0] * f[0] - P.prop_x[1] * f[1] - P.prop_x[2] * f[2] - P.prop_x[3] * f[3],
+            const V3<T> tb = {mul_rn(P.prop_y[0], f[0]) + mul_rn(P.prop_y[1], f[1]) + mul_rn(P.prop_y[2], f[2]) + mul_rn(P.prop_y[3], f[3]),
+                              mul_rn(-P.prop_x[0], f[0]) + mul_rn(-P.prop_x[1], f[1]) + mul_rn(-P.prop_x[2], f[2]) + mul_rn(-P.prop_x[3], f[3]),
                               tq[0] - tq[1] + tq[2] - tq[3]};                            // BaseAviary.py:703
             const V3<T> fw = {fext.x + nz[0], fext.y + nz[1], fext.z + nz[2]};         // drag + wind (:532-544)
             pyb_substep(P, phy, d, R, fz, tb, fw, body[0], body[1], body[2], body[3]);

@@ -136,7 +136,7 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
     // ---- S fused substeps (BaseAviary.py:347-376)
     T f0[4], tq[4];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) { f0[k] = rpm[k] * rpm[k] * P.kf; tq[k] = rpm[k] * rpm[k] * P.km; }
+    for (int k = 0; k < 4; ++k) { f0[k] = mul_rn(rpm[k] * rpm[k], P.kf); tq[k] = mul_rn(rpm[k] * rpm[k], P.km); }
     const T two_pi_60 = T(6.283185307179586) / T(60);
     for (int s = 0; s < P.S; ++s) {
         const Mat3<T> R = rotmat(d.q);
@@ -161,8 +161,8 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
             dyn_substep(P, d, R, f, tq, dw, fext);
         } else {
             const T fz = (f[0] + f[1] + f[2] + f[3]) + dw;
-            const V3<T> tb = {P.prop_y[0] * f[0] + P.prop_y[1] * f[1] + P.prop_y[2] * f[2] + P.prop_y[3] * f[3],
-                              -(P.prop_x[0] * f[0] + P.prop_x[1] * f[1] + P.prop_x[2] * f[2] + P.prop_x[3] * f[3]),
+            const V3<T> tb = {mul_rn(P.prop_y[0], f[0]) + mul_rn(P.prop_y[1], f[1]) + mul_rn(P.prop_y[2], f[2]) + mul_rn(P.prop_y[3], f[3]),
+                              -(mul_rn(P.prop_x[0], f[0]) + mul_rn(P.prop_x[1], f[1]) + mul_rn(P.prop_x[2], f[2]) + mul_rn(P.prop_x[3], f[3])),
                               tq[0] - tq[1] + tq[2] - tq[3]};                   // :703
             pyb_substep(P, phy, d, R, fz, tb, fext, P.pyb_mass, P.pyb_jx, P.pyb_jy, P.pyb_jz);
         }

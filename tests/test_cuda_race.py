@@ -113,7 +113,10 @@ def test_race_batched_philox_fp64(M, racemode, physics):
     N = 300
     rc = configs.load_config("level3")
     if M > 2:
-        rc["init_states"]["drone2"] = configs.configify({"pos": [0.7, 1.2, 0.05], "vel": [0, 0, 0], "rpy": [0, 0, 0], "pqr": [0, 0, 0]})
+        # downwash on: keep the drones > 1 m apart in xy (its alpha is singular for dz -> 0+, close formations are
+        # chaotic and amplify the last-bit differences between CUDA's and glibc's double-precision libm)
+        for i, pos in enumerate([[0.9, 0.9, 0.05], [-0.4, 1.3, 0.05], [2.0, -0.3, 0.05]]):
+            rc["init_states"][f"drone{i}"] = configs.configify({"pos": pos, "vel": [0, 0, 0], "rpy": [0, 0, 0], "pqr": [0, 0, 0]})
     rc["episode_len_sec"] = 1.0                               # truncation + auto-reset inside the run
     cfg = _abi.make_race_config(rc, num_envs=N, num_drones=M, physics=physics, racemode=racemode, precision=_abi.F64,
                                 auto_reset=True, seed=1337, env_offset=5)
@@ -131,7 +134,7 @@ def test_race_batched_philox_fp64(M, racemode, physics):
         np.testing.assert_array_equal(te.cpu().numpy(), te_o)
         np.testing.assert_array_equal(tr.cpu().numpy(), tr_o)
         resets += int(te_o.sum() + tr_o.sum())
-        np.testing.assert_allclose(h.get_state().cpu().numpy(), o.get_state(), rtol=0, atol=1e-9)
+        assert gc.rel_err(h.get_state().cpu().numpy(), o.get_state()) < TOL64, k
     assert resets > 0                                          # the in-kernel reset path ran
     h.close(); o.close()
 
