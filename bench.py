@@ -35,32 +35,78 @@ WORKLOADS = {
            "C4: 32768 envs x 8 CF2X, PYB_GND_DRAG_DW, 240/48 Hz, open-loop RPM, obs (N,8,20)"),
     "c2": (65536, 1, Physics.PYB, 240, 30, _abi.ENV_HOVER, _abi.ACT_RPM,
            "C2: HoverAviary 65536 envs x 1 CF2X, PYB, 240/30 Hz, RPM actions in [-1,1], obs (N,1,72), auto-reset"),
+    "c3": (16384, 2, Physics.PYB, 500, 25, _abi.ENV_RACE, _abi.ACT_MEL,
+           "C3: race env level3 COMPETE, 16384 envs x 2 CF2X, PYB, 500/25 Hz, Mellinger per substep, gates + obstacles + "
+           "drone-drone contacts, all randomisation and disturbances (Philox), obs (N,2,55), auto-reset"),
+    "c5m": (131072, 8, Physics.PYB_GND_DRAG_DW, 500, 25, _abi.ENV_RACE, _abi.ACT_MEL,
+            "C5M: 2^20 CF2X drones/GPU (131072 envs x 8), Bullet free body + GND+DRAG+DW, 500/25 Hz, Mellinger per substep, "
+            "formation hover setpoints, no track, obs (N,8,13)"),
 }
 
 
-def make_cfg(wl, n_envs, device=0, env_offset=0):
+def formation_xyz(M, z0=None):
+    """3 x 3 grid, 1.2 m pitch: the downwash term is evaluated for every pair but stays physical (its alpha is
+    singular for dz -> 0+ at small lateral distance, BaseAviary.py:808-810)."""
+    return [[1.2 * (k % 3), 1.2 * (k // 3), (0.5 + 0.25 * (k % 4)) if z0 is None else z0] for k in range(M)]
+
+
+def race_rc(wl):
+    from gym_pybullet_adrp_b200 import configs
+    M = WORKLOADS[wl][1]
+    if wl == "c3":
+        return configs.load_config("level3")
+    rc = configs.load_config("getting_started")
+    rc["gates"], rc["obstacles"] = [], []
+    rc["bounds"] = [[-10, -10, 0], [10, 10, 5]]
+    rc["episode_len_sec"] = 1e9
+    rc["init_states"] = configs.configify({f"drone{i}": {"pos": p, "vel": [0, 0, 0], "rpy": [0, 0, 0], "pqr": [0, 0, 0]}
+                                           for i, p in enumerate(formation_xyz(M, 0.05))})
+    return rc
+
+
+def make_cfg(wl, n_envs, device=0, env_offset=0, precision=_abi.F32):
     N, M, phy, pyb, ctrl, kind, act, _ = WORKLOADS[wl]
-    xyz = [[0.3 * (k % 3), 0.3 * (k // 3), 0.5 + 0.25 * (k % 4)] for k in range(M)] if M > 1 else None
+    if kind == _abi.ENV_RACE:
+        from gym_pybullet_adrp_b200.utils.enums import RaceMode
+        return _abi.make_race_config(race_rc(wl), num_envs=n_envs, num_drones=M, physics=phy, pyb_freq=pyb, ctrl_freq=ctrl,
+                                     racemode=RaceMode.COMPETE if wl == "c3" else RaceMode.COMPARE, precision=precision,
+                                     device=device, seed=1337, env_offset=env_offset, auto_reset=(wl == "c3"))
+    xyz = formation_xyz(M) if M > 1 else None
     return _abi.make_config(num_envs=n_envs, num_drones=M, drone_model=DroneModel.CF2X, physics=phy, pyb_freq=pyb,
-                            ctrl_freq=ctrl, action_type=act, env_kind=kind, precision=_abi.F32, device=device,
+                            ctrl_freq=ctrl, action_type=act, env_kind=kind, precision=precision, device=device,
                             initial_xyzs=xyz, auto_reset=(kind != _abi.ENV_CTRL), seed=5, env_offset=env_offset)
 
 
 def make_actions(wl, n_envs, M, A, seed, count):
     rng = np.random.default_rng(seed)
-    u = rng.uniform(-1, 1, (count, n_envs, M, A)).astype(np.float32)
+    kind = WORKLOADS[wl][5]
+    if kind == _abi.ENV_RACE:
+        # full-state setpoints [x, y, z, yaw]: c3 climbs and heads for the first gate, c5m holds a formation
+        cfg = make_cfg(wl, 1)
+        init = np.array([[cfg.init_xyz[i][k] for k in range(3)] for i in range(M)], np.float32)
+        a = np.zeros((count, n_envs, M, 4), np.float32)
+        for c in range(count):
+            a[c, :, :, 0:2] = init[None, :, 0:2] + rng.uniform(-0.2, 0.2, (n_envs, M, 2))
+            a[c, :, :, 2] = (0.4 if wl == "c3" else 0.6) + 0.15 * (np.arange(M) % 3)[None, :] + rng.uniform(0, 0.05, (n_envs, M))
+        return a
     if WORKLOADS[wl][6] == _abi.ACT_RPM_RAW:
-        return (HOVER_RPM * (1 + 0.05 * u)).astype(np.float32)      # rpm = HOVER_RPM (1 + 0.05 a), BaseRLAviary.py:192
-    return u
+        # rpm = HOVER_RPM (1 + 0.05 a) (BaseRLAviary.py:192) with a = collective U(-1,1) + 1 % per-motor differential:
+        # open-loop quadrotors tumble within a second under fully independent motor commands, and tumbling drones
+        # fly into the singularity of the reference's downwash formula (alpha ~ 1/dz^2, BaseAviary.py:808) -- the
+        # arithmetic per step is the same, but the rollout stays a flight instead of an overflow
+        u = rng.uniform(-1, 1, (count, n_envs, M, 1)) + 0.01 * rng.uniform(-1, 1, (count, n_envs, M, A))
+        u -= u.mean(axis=0, keepdims=True)           # the pool is replayed cyclically: no net thrust / torque bias per cycle
+        return (HOVER_RPM * (1 + 0.05 * u)).astype(np.float32)
+    return rng.uniform(-1, 1, (count, n_envs, M, A)).astype(np.float32)
 
 
 def initial_state(wl, n_envs, M, seed):
-    """C5: start heights U(0.2, 1.5), xy on a 0.3 m grid per env."""
+    """C5 / C4: the formation grid with start heights U(0.2, 1.5)."""
     rng = np.random.default_rng(seed)
     st = np.zeros((n_envs, M, 20), np.float32)
-    k = np.arange(M)
-    st[:, :, 0] = 0.3 * (k % 3)
-    st[:, :, 1] = 0.3 * (k // 3)
+    xyz = np.array(formation_xyz(M), np.float32)
+    st[:, :, 0] = xyz[None, :, 0]
+    st[:, :, 1] = xyz[None, :, 1]
     st[:, :, 2] = rng.uniform(0.2, 1.5, (n_envs, M))
     st[:, :, 6] = 1.0
     return st
@@ -69,14 +115,32 @@ def initial_state(wl, n_envs, M, seed):
 def algorithmic_bytes_per_drone_step(wl, O, A, M):
     """fp32 bytes that MUST cross HBM per drone per control step (DESIGN.md 'Measurement')."""
     phy = _abi.PHYSICS_MASK[WORKLOADS[wl][2]]
+    kind = WORKLOADS[wl][5]
     state_rd = 17                                        # pos3 quat4 vel3 (rates3 | ang_v3) last_rpm4
     state_wr = 20 if phy & _abi.PHY_DYN else 17          # DYN also stores world ang_v next to the body rates
-    ring = 0
-    if WORKLOADS[wl][5] != _abi.ENV_CTRL:
+    ring, extra = 0, 0
+    if kind == _abi.ENV_RACE:
+        # Mellinger wrapper + firmware state (10 T + 18 f32 + 5 i32) and gate / latch word, read and written;
+        # Bullet body mass / inertia read; the env's track instance (6 floats per gate, 3 per obstacle) read once per env
+        extra = 2 * (10 + 18 + 5 + 1) + 4 + (6 * 4 + 3 * 4 if wl == "c3" else 0) / M
+    elif kind != _abi.ENV_CTRL:
         ring = (O - 12) + A                               # read the action buffer once, write the newest slot
-    per_drone = 4 * (state_rd + A + state_wr + O + ring) + 1
+    per_drone = 4 * (state_rd + A + state_wr + O + ring + extra) + 1
     per_env = 4 + 2 + 4 + 4                               # reward, two flag bytes, step counter read+write
     return per_drone + per_env / M
+
+
+# SURVEY 8(d): algorithmic flops per substep-update (reading estimates, +-20 %)
+def algorithmic_flops_per_substep(wl):
+    N, M, physics, pyb, ctrl, kind, act, _ = WORKLOADS[wl]
+    phy = _abi.PHYSICS_MASK[physics]
+    fl = 160 if phy & _abi.PHY_DYN else 200
+    fl += 20 if (phy & _abi.PHY_GND or kind == _abi.ENV_RACE) else 0
+    fl += 45 if phy & _abi.PHY_GND else 0
+    fl += 25 if phy & _abi.PHY_DRAG else 0
+    fl += 17 * (M - 1) if phy & _abi.PHY_DW else 0
+    fl += 450 if kind == _abi.ENV_RACE else 0
+    return fl
 
 
 class ClockSampler(threading.Thread):
@@ -113,7 +177,7 @@ def cpu_port_rate(wl, n_envs_sample, steps, threads):
     """Oracle (CPU port of the reference arithmetic) on a bounded sample of the same workload."""
     from tests.oracle_lib import OracleEnv
     N, M = n_envs_sample, WORKLOADS[wl][1]
-    cfg = make_cfg(wl, N)
+    cfg = make_cfg(wl, N, precision=_abi.F64)           # the reference computes in numpy float64
     env = OracleEnv(cfg)
     if WORKLOADS[wl][5] == _abi.ENV_CTRL:
         env.set_state(initial_state(wl, N, M, 5))
@@ -127,6 +191,11 @@ def cpu_port_rate(wl, n_envs_sample, steps, threads):
     return N * M * steps / dt, dt
 
 
+def cpu_sample_envs(wl):
+    M, S = WORKLOADS[wl][1], WORKLOADS[wl][3] // WORKLOADS[wl][4]
+    return max(256, min(65536, (1 << 19) // (M * S)))    # ~0.5 M substep-updates per control step of the sample
+
+
 def run_reference(args):
     """--impl reference: the reference's own CPU arithmetic (oracle port; the reference itself needs
     PyBullet, which is not installable here or on the GPU box) on all host cores, bounded sample."""
@@ -136,7 +205,7 @@ def run_reference(args):
     threads = len(os.sched_getaffinity(0))
     wl = args.workload
     M, S = WORKLOADS[wl][1], WORKLOADS[wl][3] // WORKLOADS[wl][4]
-    n_sample = 8192 if M > 1 else 65536
+    n_sample = cpu_sample_envs(wl)
     for _ in range(max(args.warmup, 1)):
         cpu_port_rate(wl, n_sample, 1, threads)
     rate, dt = cpu_port_rate(wl, n_sample, args.steps, threads)
@@ -156,7 +225,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
-    ap.add_argument("--workload", default="c5", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=os.environ.get("ADRP_BENCH_WORKLOAD", "c5"), choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--envs-per-gpu", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -190,9 +259,16 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    def restart():
+        """Open-loop workloads: put the formation back (untimed) so that every phase measures flight, not the
+        late tumbling of an uncontrolled quadrotor."""
+        if WORKLOADS[wl][5] == _abi.ENV_CTRL:
+            h.set_state(initial_state(wl, N, M, 5 + rank))
+
     # ---------------- device-resident throughput ("value")
     for k in range(max(args.warmup, 3)):
         h.step(acts_dev[k % pool])
+    restart()
     sampler = ClockSampler(local)
     barrier()
     sampler.start()
@@ -212,6 +288,7 @@ def main():
     value = world * N * M * args.steps / (ms_total * 1e-3)
 
     # ---------------- kernel-only time for the roofline (CUDA events on the launching stream)
+    restart()
     h.set_profiling(True)
     for k in range(min(args.steps, 50)):
         h.step(acts_dev[k % pool])
@@ -221,6 +298,7 @@ def main():
 
     # ---------------- end to end through the host-buffer call (H2D + kernel + D2H every step)
     e2e_steps = max(3, min(args.steps, 20))
+    restart()
     for k in range(3):
         h.step_host(acts_np[k % pool])
     barrier()
@@ -252,6 +330,9 @@ def main():
         peak = float(peaks.get("hbm_gbs", 6650.0))
         bpd = algorithmic_bytes_per_drone_step(wl, h.O, h.A, M)
         achieved = bpd * N * M / (kernel_ms * 1e-3) / 1e9 if kernel_ms > 0 else None
+        fps = algorithmic_flops_per_substep(wl)
+        fp32_peak = _lib.fp32_peak_tflops(local)
+        fp32_ach = fps * S * N * M / (kernel_ms * 1e-3) / 1e12 if kernel_ms > 0 else None
         line = {
             "metric": "drone_steps_per_s", "value": value, "unit": "drone-steps/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
@@ -264,6 +345,9 @@ def main():
                          "frac": achieved / peak if achieved else None, "traffic": None,
                          "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback",
                          "kernel_ms": kernel_ms, "algorithmic_bytes_per_drone_step": bpd},
+            "fp32_roofline": {"achieved": fp32_ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": fp32_ach / fp32_peak if fp32_ach else None,
+                              "algorithmic_flops_per_substep_update": fps,
+                              "peak_source": "measured live: adrp_fp32_peak_tflops (16 FMA chains per thread)"},
             "e2e": {"value": e2e_value, "unit": "drone-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps},
             "gpu_launches": launches,
@@ -272,7 +356,7 @@ def main():
         }
         if world == 1 and not args.no_cpu_baseline:
             threads = len(os.sched_getaffinity(0))
-            n_sample = 8192 if M > 1 else 65536
+            n_sample = cpu_sample_envs(wl)
             cpu_port_rate(wl, n_sample, 1, threads)
             # size the sample for ~10-20 s of CPU work
             r1, d1 = cpu_port_rate(wl, n_sample, 4, threads)

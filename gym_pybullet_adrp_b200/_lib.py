@@ -17,7 +17,7 @@ LIB_PATH = os.path.join(PKG_DIR, "libadrp_b200.so")
 EXPORTS = ["adrp_create", "adrp_destroy", "adrp_obs_dim", "adrp_action_dim", "adrp_noise_dim",
            "adrp_reset_draws_dim", "adrp_substeps", "adrp_reset", "adrp_set_state", "adrp_get_state",
            "adrp_step", "adrp_step_host", "adrp_dslpid_control", "adrp_launch_count", "adrp_set_profiling",
-           "adrp_step_kernel_ms", "adrp_last_error", "adrp_abi_version", "adrp_config_size"]
+           "adrp_step_kernel_ms", "adrp_fp32_peak_tflops", "adrp_last_error", "adrp_abi_version", "adrp_config_size"]
 
 _lib = None
 
@@ -52,6 +52,8 @@ def load():
     lib.adrp_set_profiling.argtypes = [vp, C.c_int]
     lib.adrp_step_kernel_ms.argtypes = [vp, C.c_int]
     lib.adrp_step_kernel_ms.restype = C.c_double
+    lib.adrp_fp32_peak_tflops.argtypes = [C.c_int]
+    lib.adrp_fp32_peak_tflops.restype = C.c_double
     lib.adrp_last_error.argtypes = [vp]
     lib.adrp_last_error.restype = C.c_char_p
     if lib.adrp_abi_version() != _abi.ABI_VERSION or lib.adrp_config_size() != C.sizeof(_abi.ConfigC):
@@ -171,6 +173,14 @@ class Handle:
 
 
 _abi_EINVAL = -1
+
+
+def fp32_peak_tflops(device=0):
+    """Measured FP32 FMA peak of the device (TFLOP/s)."""
+    v = load().adrp_fp32_peak_tflops(int(device))
+    if v <= 0:
+        raise AdrpError("adrp_fp32_peak_tflops failed")
+    return float(v)
 
 
 def dslpid_control(precision, drone_model, n, dt, pos, quat, vel, tpos, trpy, tvel, trates, ctrl, device=0):

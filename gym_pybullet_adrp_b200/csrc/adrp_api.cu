@@ -16,6 +16,22 @@ using namespace adrp;
 
 namespace {
 
+// 16 independent FMA chains per thread, all operands in registers.
+__global__ void fma_peak_kernel(float* sink, int iters, float a, float b)
+{
+    float x[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) x[k] = (float)(threadIdx.x + k);
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) x[k] = fmaf(x[k], a, b);
+    }
+    float s = 0;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) s += x[k];
+    if (s == 123.456f) sink[threadIdx.x & 1023] = s;
+}
+
 thread_local std::string g_create_error;
 
 struct HandleBase {
@@ -518,6 +534,32 @@ double adrp_step_kernel_ms(adrp_handle* h, int reset)
     const double avg = b->kernel_ms_n ? b->kernel_ms_sum / (double)b->kernel_ms_n : -1.0;
     if (reset) { b->kernel_ms_sum = 0; b->kernel_ms_n = 0; }
     return avg;
+}
+
+double adrp_fp32_peak_tflops(int device)
+{
+    if (cudaSetDevice(device) != cudaSuccess) return -1.0;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return -1.0;
+    float* sink = nullptr;
+    if (cudaMalloc(&sink, sizeof(float) * 1024) != cudaSuccess) return -1.0;
+    const int iters = 4096, blocks = prop.multiProcessorCount * 8, threads = 256;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    double best = -1.0;
+    for (int rep = 0; rep < 5; ++rep) {
+        cudaEventRecord(e0);
+        fma_peak_kernel<<<blocks, threads>>>(sink, iters, 1.0001f, 0.9999f);
+        cudaEventRecord(e1);
+        if (cudaEventSynchronize(e1) != cudaSuccess) { best = -1.0; break; }
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        const double flops = 2.0 * 16.0 * (double)iters * (double)blocks * threads;
+        const double tf = flops / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(sink);
+    return best;
 }
 
 const char* adrp_last_error(const adrp_handle* h) { return h ? base(h)->err.c_str() : g_create_error.c_str(); }

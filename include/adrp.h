@@ -191,6 +191,11 @@ int64_t adrp_launch_count(const adrp_handle* h);
 int adrp_set_profiling(adrp_handle* h, int enabled);
 double adrp_step_kernel_ms(adrp_handle* h, int reset);
 
+/* Measured FP32 pipe peak of `device` (TFLOP/s, FMA = 2 flop): a register-resident chain of independent FMAs,
+ * timed with CUDA events; the denominator of bench.py's fp32 roofline (MEASURED_PEAKS.json has no FP32 figure).
+ * Returns a negative value on error. */
+double adrp_fp32_peak_tflops(int device);
+
 const char* adrp_last_error(const adrp_handle* h);   /* h may be NULL: error of the last failed adrp_create */
 int adrp_abi_version(void);
 int adrp_config_size(void);                           /* sizeof(adrp_config) for binding sanity checks */
