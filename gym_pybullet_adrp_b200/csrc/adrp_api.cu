@@ -113,7 +113,7 @@ void derive_params(const adrp_config& c, KParams<T>& P)
     const double HOVER = sqrt(GRAV / (4 * p.kf));
     const double MAXR = sqrt((p.thrust2weight * GRAV) / (4 * p.kf));
     const double MAXT = 4 * p.kf * MAXR * MAXR;
-    P.mass = (T)p.mass; P.kf = (T)p.kf; P.km = (T)p.km;
+    P.mass = (T)p.mass; P.inv_mass = (T)(1.0 / p.mass); P.kf = (T)p.kf; P.km = (T)p.km;
     P.arm_x = (T)(c.drone_model == ADRP_CF2P ? p.arm : p.arm / sqrt(2.0));
     P.jx = (T)p.ixx; P.jy = (T)p.iyy; P.jz = (T)p.izz;
     P.jinvx = (T)(1.0 / p.ixx); P.jinvy = (T)(1.0 / p.iyy); P.jinvz = (T)(1.0 / p.izz);

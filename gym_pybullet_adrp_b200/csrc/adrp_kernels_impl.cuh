@@ -47,8 +47,18 @@ cudaError_t Launch<T>::step(const KParams<T>& P, const KBuffers<T>& b, const T* 
 {
     const bool pid = P.action_type == ADRP_ACT_PID || P.action_type == ADRP_ACT_ONE_D_PID ||
                      P.action_type == ADRP_ACT_VEL || P.action_type == ADRP_ACT_PID_FULL;
-    if (pid) step_kernel<T, -1, 1><<<grid_for(P.Dpad), kBlock, 0, s>>>(P, b, action, obs, reward, te, tr, fl);
-    else step_kernel<T, -1, 0><<<grid_for(P.Dpad), kBlock, 0, s>>>(P, b, action, obs, reward, te, tr, fl);
+    const unsigned grid = grid_for(P.Dpad);
+#define ADRP_LAUNCH_STEP(MP) step_kernel<T, -1, 0, MP><<<grid, kBlock, 0, s>>>(P, b, action, obs, reward, te, tr, fl)
+    if (pid) step_kernel<T, -1, 1, 0><<<grid, kBlock, 0, s>>>(P, b, action, obs, reward, te, tr, fl);
+    else switch (P.Mpad) {
+        case 1: ADRP_LAUNCH_STEP(1); break;
+        case 2: ADRP_LAUNCH_STEP(2); break;
+        case 4: ADRP_LAUNCH_STEP(4); break;
+        case 8: ADRP_LAUNCH_STEP(8); break;
+        case 16: ADRP_LAUNCH_STEP(16); break;
+        default: ADRP_LAUNCH_STEP(32); break;
+    }
+#undef ADRP_LAUNCH_STEP
     return cudaGetLastError();
 }
 

@@ -26,6 +26,26 @@ template <> struct M<float> {
     static __device__ __forceinline__ float tan(float x) { return tanf(x); }
     static __device__ __forceinline__ float fmax(float a, float b) { return fmaxf(a, b); }
     static __device__ __forceinline__ float fmin(float a, float b) { return fminf(a, b); }
+    // ---- fp32 product build only: MUFU-based approximations (<= 2 ulp) for the substep loop.  The epilogue
+    // (flags, observation) keeps the IEEE forms above, so flags stay a bit-exact function of the stored state.
+    static constexpr bool fast = true;
+    static __device__ __forceinline__ float rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+    static __device__ __forceinline__ float fdiv(float a, float b) { return __fdividef(a, b); }
+    static __device__ __forceinline__ float fsqrt(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+    static __device__ __forceinline__ float frsqrt(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+    static __device__ __forceinline__ float fexp(float x) { return __expf(x); }
+    // sin / cos of the half rotation angle of one substep: minimax polynomials on |x| <= pi/4 (Cephes sinf / cosf
+    // kernels, ~1 ulp), the libm call beyond
+    static __device__ __forceinline__ void sincos_small(float x, float* s, float* c)
+    {
+        if (fabsf(x) <= 0.7853981633974483f) {
+            const float z = x * x;
+            *s = x + x * z * (-1.6666654611e-1f + z * (8.3321608736e-3f + z * -1.9515295891e-4f));
+            *c = 1.0f - 0.5f * z + z * z * (4.166664568298827e-2f + z * (-1.388731625493765e-3f + z * 2.443315711809948e-5f));
+        } else {
+            sincosf(x, s, c);
+        }
+    }
 };
 template <> struct M<double> {
     static __device__ __forceinline__ double sqrt(double x) { return ::sqrt(x); }
@@ -41,6 +61,14 @@ template <> struct M<double> {
     static __device__ __forceinline__ double tan(double x) { return ::tan(x); }
     static __device__ __forceinline__ double fmax(double a, double b) { return ::fmax(a, b); }
     static __device__ __forceinline__ double fmin(double a, double b) { return ::fmin(a, b); }
+    // fp64 parity build: every operation stays the IEEE statement the reference executes
+    static constexpr bool fast = false;
+    static __device__ __forceinline__ double rcp(double x) { return 1.0 / x; }
+    static __device__ __forceinline__ double fdiv(double a, double b) { return a / b; }
+    static __device__ __forceinline__ double fsqrt(double x) { return ::sqrt(x); }
+    static __device__ __forceinline__ double frsqrt(double x) { return 1.0 / ::sqrt(x); }
+    static __device__ __forceinline__ double fexp(double x) { return ::exp(x); }
+    static __device__ __forceinline__ void sincos_small(double x, double* s, double* c) { ::sincos(x, s, c); }
 };
 
 // Product that is never contracted into a following add.  The motor thrusts / torques of a symmetric command
@@ -83,6 +111,21 @@ template <typename T> __device__ __forceinline__ Mat3<T> rotmat(const Q4<T>& q)
     const T yy = q.y * ys, yz = q.y * zs, zz = q.z * zs;
     return {T(1) - (yy + zz), xy - wz, xz + wy, xy + wz, T(1) - (xx + zz), yz - wx, xz - wy, yz + wx, T(1) - (xx + yy)};
 }
+
+// rotmat for the substep loop: same formula, the normalisation through the build's fdiv.
+template <typename T> __device__ __forceinline__ Mat3<T> rotmat_loop(const Q4<T>& q)
+{
+    const T d = q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w;
+    const T s = M<T>::fdiv(T(2), d);
+    const T xs = q.x * s, ys = q.y * s, zs = q.z * s;
+    const T wx = q.w * xs, wy = q.w * ys, wz = q.w * zs;
+    const T xx = q.x * xs, xy = q.x * ys, xz = q.x * zs;
+    const T yy = q.y * ys, yz = q.y * zs, zz = q.z * zs;
+    return {T(1) - (yy + zz), xy - wz, xz + wy, xy + wz, T(1) - (xx + zz), yz - wx, xz - wy, yz + wx, T(1) - (xx + yy)};
+}
+
+// canon_quat for the substep loop (normalisation through the build's frsqrt)
+template <typename T> __device__ __forceinline__ Q4<T> canon_quat_loop(const Q4<T>& q);
 
 // pybullet.getEulerFromQuaternion, including its gimbal-lock branches.
 template <typename T> __device__ __forceinline__ V3<T> euler_rpy(const Q4<T>& q)
@@ -130,6 +173,18 @@ template <typename T> __device__ __forceinline__ Q4<T> canon_quat(const Q4<T>& q
     T inv = T(1) / M<T>::sqrt(d);
     T pivot;
     if (T(4) * ww > d) pivot = q.w;                                   // trace > 0
+    else pivot = xx < yy ? (yy < zz ? q.z : q.y) : (xx < zz ? q.z : q.x);
+    if (pivot < T(0)) inv = -inv;
+    return {q.x * inv, q.y * inv, q.z * inv, q.w * inv};
+}
+
+template <typename T> __device__ __forceinline__ Q4<T> canon_quat_loop(const Q4<T>& q)
+{
+    const T xx = q.x * q.x, yy = q.y * q.y, zz = q.z * q.z, ww = q.w * q.w;
+    const T d = xx + yy + zz + ww;
+    T inv = M<T>::frsqrt(d);
+    T pivot;
+    if (T(4) * ww > d) pivot = q.w;
     else pivot = xx < yy ? (yy < zz ? q.z : q.y) : (xx < zz ? q.z : q.x);
     if (pivot < T(0)) inv = -inv;
     return {q.x * inv, q.y * inv, q.z * inv, q.w * inv};

@@ -93,14 +93,17 @@ __device__ __forceinline__ void fw_mellinger(MelFw& m, const MelSetpoint& sp, fl
     const float R10 = 2 * x * y + 2 * z * w, R11 = 1 - 2 * x * x - 2 * z * z, R12 = 2 * y * z - 2 * x * w;
     const float R20 = 2 * x * z - 2 * y * w, R21 = 2 * y * z + 2 * x * w, R22 = 1 - 2 * x * x - 2 * y * y;
     const float current_thrust = tt[0] * R02 + tt[1] * R12 + tt[2] * R22;
-    const float nt = sqrtf(tt[0] * tt[0] + tt[1] * tt[1] + tt[2] * tt[2]);
-    const float zd0 = tt[0] / nt, zd1 = tt[1] / nt, zd2 = tt[2] / nt;
+    const float nt = M<T>::fast ? M<float>::fsqrt(tt[0] * tt[0] + tt[1] * tt[1] + tt[2] * tt[2]) : sqrtf(tt[0] * tt[0] + tt[1] * tt[1] + tt[2] * tt[2]);
+    float zd0, zd1, zd2;
+    if (M<T>::fast) { const float in = M<float>::rcp(nt); zd0 = tt[0] * in; zd1 = tt[1] * in; zd2 = tt[2] * in; }
+    else { zd0 = tt[0] / nt; zd1 = tt[1] / nt; zd2 = tt[2] / nt; }
     float xc0, xc1;
     FwMath<T>::sincos(fw_radians(desiredYaw), &xc1, &xc0);
     const float xc2 = 0.0f;
     float yd0 = zd1 * xc2 - zd2 * xc1, yd1 = zd2 * xc0 - zd0 * xc2, yd2 = zd0 * xc1 - zd1 * xc0;
-    const float ny = sqrtf(yd0 * yd0 + yd1 * yd1 + yd2 * yd2);
-    yd0 /= ny; yd1 /= ny; yd2 /= ny;
+    const float ny = M<T>::fast ? M<float>::fsqrt(yd0 * yd0 + yd1 * yd1 + yd2 * yd2) : sqrtf(yd0 * yd0 + yd1 * yd1 + yd2 * yd2);
+    if (M<T>::fast) { const float in = M<float>::rcp(ny); yd0 *= in; yd1 *= in; yd2 *= in; }
+    else { yd0 /= ny; yd1 /= ny; yd2 /= ny; }
     const float xd0 = yd1 * zd2 - yd2 * zd1, xd1 = yd2 * zd0 - yd0 * zd2, xd2 = yd0 * zd1 - yd1 * zd0;
     // eRM = Rdes^T R - R^T Rdes with Rdes = [xd yd zd] (columns): Rd[k][0] = xd_k, Rd[k][1] = yd_k, Rd[k][2] = zd_k
     float e21 = 0, e02 = 0, e10 = 0;
@@ -111,8 +114,10 @@ __device__ __forceinline__ void fw_mellinger(MelFw& m, const MelSetpoint& sp, fl
     const float rate_roll = fw_radians(gyro_deg[0]), rate_pitch = -fw_radians(gyro_deg[1]), rate_yaw = fw_radians(gyro_deg[2]);
     const float ew0 = fw_radians(sp_rate_deg) - rate_roll, ew1 = -fw_radians(sp_rate_deg) - rate_pitch,
                 ew2 = fw_radians(sp_rate_deg) - rate_yaw;
-    const float err_d_roll = ((fw_radians(sp_rate_deg) - m.prev_setpoint_omega_roll) - (rate_roll - m.prev_omega_roll)) / dt;
-    const float err_d_pitch = (-(fw_radians(sp_rate_deg) - m.prev_setpoint_omega_pitch) - (rate_pitch - m.prev_omega_pitch)) / dt;
+    float err_d_roll = (fw_radians(sp_rate_deg) - m.prev_setpoint_omega_roll) - (rate_roll - m.prev_omega_roll);
+    float err_d_pitch = -(fw_radians(sp_rate_deg) - m.prev_setpoint_omega_pitch) - (rate_pitch - m.prev_omega_pitch);
+    if (M<T>::fast) { err_d_roll *= 500.0f; err_d_pitch *= 500.0f; }
+    else { err_d_roll = err_d_roll / dt; err_d_pitch = err_d_pitch / dt; }
     m.prev_omega_roll = rate_roll; m.prev_omega_pitch = rate_pitch;
     m.prev_setpoint_omega_roll = fw_radians(sp_rate_deg);
     m.prev_setpoint_omega_pitch = fw_radians(sp_rate_deg);
@@ -154,19 +159,29 @@ __device__ __forceinline__ void mellinger_tick(const RaceParams<T>& RP, const ui
 {
     const T FIRMWARE_DT = (T)(1.0 / 500), RAD_TO_DEG = (T)(180.0 / 3.14159265358979323846), DEG_TO_RAD = (T)(3.14159265358979323846 / 180.0);
     const V3<T> rpy = euler_rpy(q);                                              // obs[i, 3:6] (:242)
-    const T rates[3] = {(rpy.x - m.prev_rpy.x) / FIRMWARE_DT, (rpy.y - m.prev_rpy.y) / FIRMWARE_DT,
-                        (rpy.z - m.prev_rpy.z) / FIRMWARE_DT};                   // :209
+    T rates[3], acc_z;
+    float qf[4];
+    if (M<T>::fast) {
+        rates[0] = (rpy.x - m.prev_rpy.x) * T(500); rates[1] = (rpy.y - m.prev_rpy.y) * T(500); rates[2] = (rpy.z - m.prev_rpy.z) * T(500);
+        acc_z = (v.z - m.prev_vel.z) * T(500.0 / 9.8) + T(1);
+        // euler -> degrees -> radians -> quaternion (:446-471) reproduces +-q up to rounding, and the firmware only
+        // reads q through its rotation matrix: hand it the state quaternion
+        qf[0] = (float)q.x; qf[1] = (float)q.y; qf[2] = (float)q.z; qf[3] = (float)q.w;
+    } else {
+        rates[0] = (rpy.x - m.prev_rpy.x) / FIRMWARE_DT; rates[1] = (rpy.y - m.prev_rpy.y) / FIRMWARE_DT;
+        rates[2] = (rpy.z - m.prev_rpy.z) / FIRMWARE_DT;                         // :209
+        acc_z = (v.z - m.prev_vel.z) / FIRMWARE_DT / T(9.8) + T(1);              // :213 (only acc.z is read downstream)
+        // _update_state (:446-471): degrees and back, then utils.get_quaternion_from_euler (utils/utils.py:20-43)
+        const T rdx = rpy.x * RAD_TO_DEG * DEG_TO_RAD, rdy = rpy.y * RAD_TO_DEG * DEG_TO_RAD, rdz = rpy.z * RAD_TO_DEG * DEG_TO_RAD;
+        T sr, cr, sp_, cp, sy, cy;
+        M<T>::sincos(rdx / T(2), &sr, &cr);
+        M<T>::sincos(rdy / T(2), &sp_, &cp);
+        M<T>::sincos(rdz / T(2), &sy, &cy);
+        qf[0] = (float)(sr * cp * cy - cr * sp_ * sy); qf[1] = (float)(cr * sp_ * cy + sr * cp * sy);
+        qf[2] = (float)(cr * cp * sy - sr * sp_ * cy); qf[3] = (float)(cr * cp * cy + sr * sp_ * sy);
+    }
     m.prev_rpy = rpy;
-    const T acc_z = (v.z - m.prev_vel.z) / FIRMWARE_DT / T(9.8) + T(1);          // :213 (only acc.z is read downstream)
     m.prev_vel = v;
-    // _update_state (:446-471): degrees and back, then utils.get_quaternion_from_euler (utils/utils.py:20-43)
-    const T rdx = rpy.x * RAD_TO_DEG * DEG_TO_RAD, rdy = rpy.y * RAD_TO_DEG * DEG_TO_RAD, rdz = rpy.z * RAD_TO_DEG * DEG_TO_RAD;
-    T sr, cr, sp_, cp, sy, cy;
-    M<T>::sincos(rdx / T(2), &sr, &cr);
-    M<T>::sincos(rdy / T(2), &sp_, &cp);
-    M<T>::sincos(rdz / T(2), &sy, &cy);
-    const float qf[4] = {(float)(sr * cp * cy - cr * sp_ * sy), (float)(cr * sp_ * cy + sr * cp * sy),
-                         (float)(cr * cp * sy - sr * sp_ * cy), (float)(cr * cp * cy + sr * sp_ * sy)};
     const float pos[3] = {(float)p.x, (float)p.y, (float)p.z}, vel[3] = {(float)v.x, (float)v.y, (float)v.z};
     m.acc_z = (float)acc_z;
     // _update_sensorData (:347-365): gyro in deg/s through lpf2p
@@ -186,13 +201,14 @@ __device__ __forceinline__ void mellinger_tick(const RaceParams<T>& RP, const ui
         }
         m.tick += 1;
         // _compute_pwms (:423-442)
-        const T r = (T)m.fw.roll / T(2), pp = (T)m.fw.pitch / T(2), y = (T)m.fw.yaw, t = (T)m.fw.thrust;
+        const T r = (T)m.fw.roll * T(0.5), pp = (T)m.fw.pitch * T(0.5), y = (T)m.fw.yaw, t = (T)m.fw.thrust;
         const T th[4] = {t - r + pp + y, t - r - pp - y, t + r - pp + y, t + r + pp - y};
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const T x = clampT(th[k], T(0), T(65535)) / T(65535) * T(60);
+            const T x = M<T>::fast ? clampT(th[k], T(0), T(65535)) * T(60.0 / 65535.0) : clampT(th[k], T(0), T(65535)) / T(65535) * T(60);
             const T volts = T(-0.0006239) * (x * x) + T(0.088) * x;
-            const T pct = volts / T(3) < T(1) ? volts / T(3) : T(1);
+            const T v3 = M<T>::fast ? volts * T(1.0 / 3.0) : volts / T(3);
+            const T pct = v3 < T(1) ? v3 : T(1);
             pwms[k] = pct * T(65535);
         }
     }
@@ -209,7 +225,7 @@ __device__ __forceinline__ void mellinger_tick(const RaceParams<T>& RP, const ui
     for (int k = 0; k < 4; ++k) {
         T tk = thrust[3 - k] + noise4[k];                                        // thrust[[3,2,1,0]] + disturbance (:250-253)
         if (tk < T(0)) tk = T(0);                                                // _thr2pwm (:307-343)
-        T pwm = (M<T>::sqrt(tk / T(1) / KF) - CONST) / SCALE;
+        T pwm = M<T>::fast ? (M<T>::fsqrt(tk * T(1.0 / 3.16e-10)) - CONST) * T(1.0 / 0.2685) : (M<T>::sqrt(tk / T(1) / KF) - CONST) / SCALE;
         pwm = clampT(pwm, T(20000), T(65535));
         m.rpms[k] = SCALE * pwm + CONST;
     }

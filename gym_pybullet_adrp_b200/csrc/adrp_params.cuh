@@ -21,7 +21,7 @@ struct KParams {
     int pyb_freq;
     int trunc_steps;                      // smallest step_counter with step_counter/PYB_FREQ > EPISODE_LEN_SEC
     // BaseAviary constants (envs/BaseAviary.py:74-128)
-    T mass, arm_x, kf, km, jx, jy, jz, jinvx, jinvy, jinvz, gravity, hover_rpm, max_rpm;
+    T mass, inv_mass, arm_x, kf, km, jx, jy, jz, jinvx, jinvy, jinvz, gravity, hover_rpm, max_rpm;
     T gnd_eff_coeff, prop_radius, gnd_eff_h_clip, drag_xy, drag_z, dw1, dw2, dw3, speed_limit;
     T prop_x[4], prop_y[4], pyb_mass, pyb_jx, pyb_jy, pyb_jz, lin_damp, ang_damp, coll_r, coll_h;
     T dt, ctrl_dt, g;

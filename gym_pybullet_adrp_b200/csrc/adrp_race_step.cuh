@@ -132,7 +132,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
             nz[5] = RP.noise_std * r1 * c1; nz[6] = RP.noise_std * r1 * s1;
         }
         // _apply_physics(self.rpms, self.prev_rpms) (:510-548): forces from the substep-start state
-        const Mat3<T> R = rotmat(d.q);
+        const Mat3<T> R = rotmat_loop(d.q);
         T f[4], tq[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) { f[k] = mul_rn(m.rpms[k] * m.rpms[k], P.kf); tq[k] = mul_rn(m.rpms[k] * m.rpms[k], P.km); }
@@ -143,13 +143,9 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
             for (int k = 0; k < 4; ++k) f[k] += gnd[k];
         }
         V3<T> fext = {T(0), T(0), T(0)};
-        if (phy & ADRP_PHY_DRAG) {                             // prev_rpms = state row 16:20
-            const T sum = (T(2) * T(3.141592653589793) * d.last_rpm[0] / T(60) + T(2) * T(3.141592653589793) * d.last_rpm[1] / T(60)) +
-                          T(2) * T(3.141592653589793) * d.last_rpm[2] / T(60) + T(2) * T(3.141592653589793) * d.last_rpm[3] / T(60);
-            fext = {-P.drag_xy * sum * d.v.x, -P.drag_xy * sum * d.v.y, -P.drag_z * sum * d.v.z};
-        }
+        if (phy & ADRP_PHY_DRAG) fext = drag_force(P, d);      // prev_rpms = state row 16:20
         T dw = T(0);
-        if (phy & ADRP_PHY_DW) dw = downwash(P, d.p, lane_base, valid);
+        if (phy & ADRP_PHY_DW) dw = downwash<T, 0>(P, d.p, lane_base, valid);
         if (phy & ADRP_PHY_DYN) {
             dyn_substep(P, d, R, f, tq, dw, fext);
         } else {

@@ -65,8 +65,8 @@ __device__ __forceinline__ int group_or(int v, int Mpad)
 }
 
 // PHY_CT >= 0: physics mask known at compile time (specialised kernels); -1: read from the params.
-// ACTC: 0 = RPM-type actions, 1 = DSLPID-type actions.
-template <typename T, int PHY_CT, int ACTC>
+// ACTC: 0 = RPM-type actions, 1 = DSLPID-type actions.  MP: lanes per env (0 = read from the params).
+template <typename T, int PHY_CT, int ACTC, int MP>
 __global__ void __launch_bounds__(kBlock)
 step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* __restrict__ action,
             T* __restrict__ obs, T* __restrict__ reward, uint8_t* __restrict__ terminated,
@@ -74,8 +74,9 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
 {
     const long long t = (long long)blockIdx.x * kBlock + threadIdx.x;
     const int lane = threadIdx.x & 31;
-    const int i = (int)(t & (P.Mpad - 1));
-    const long long env = t / P.Mpad;
+    const int mpad = MP > 0 ? MP : P.Mpad;
+    const int i = (int)(t & (mpad - 1));
+    const long long env = t / mpad;
     const int lane_base = lane - i;
     const bool valid = env < P.N && i < P.M;
     const long long D = P.Dpad;
@@ -137,9 +138,8 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
     T f0[4], tq[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) { f0[k] = mul_rn(rpm[k] * rpm[k], P.kf); tq[k] = mul_rn(rpm[k] * rpm[k], P.km); }
-    const T two_pi_60 = T(6.283185307179586) / T(60);
     for (int s = 0; s < P.S; ++s) {
-        const Mat3<T> R = rotmat(d.q);
+        const Mat3<T> R = rotmat_loop(d.q);
         T f[4] = {f0[0], f0[1], f0[2], f0[3]};
         if (phy & ADRP_PHY_GND) {
             T gnd[4];
@@ -148,15 +148,9 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
             for (int k = 0; k < 4; ++k) f[k] += gnd[k];
         }
         V3<T> fext = {T(0), T(0), T(0)};
-        if (phy & ADRP_PHY_DRAG) {
-            // _drag uses last_clipped_action: the previous step's RPM during the first substep (:363,:376)
-            const T sum = (T(2) * T(3.141592653589793) * d.last_rpm[0] / T(60) + T(2) * T(3.141592653589793) * d.last_rpm[1] / T(60)) +
-                          T(2) * T(3.141592653589793) * d.last_rpm[2] / T(60) + T(2) * T(3.141592653589793) * d.last_rpm[3] / T(60);
-            (void)two_pi_60;
-            fext = {-P.drag_xy * sum * d.v.x, -P.drag_xy * sum * d.v.y, -P.drag_z * sum * d.v.z};
-        }
+        if (phy & ADRP_PHY_DRAG) fext = drag_force(P, d);   // last_clipped_action: the previous step's RPM during the first substep (:363,:376)
         T dw = T(0);
-        if (phy & ADRP_PHY_DW) dw = downwash(P, d.p, lane_base, valid);
+        if (phy & ADRP_PHY_DW) dw = downwash<T, MP>(P, d.p, lane_base, valid);
         if (phy & ADRP_PHY_DYN) {
             dyn_substep(P, d, R, f, tq, dw, fext);
         } else {
@@ -213,9 +207,9 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
             tr = M<T>::abs(d.p.x) > P.hover_lim || M<T>::abs(d.p.y) > P.hover_lim || d.p.z > T(2) ||
                  M<T>::abs(rpy.x) > T(.4) || M<T>::abs(rpy.y) > T(.4);
         }
-        rew = group_sum(r, P.Mpad);
-        term = group_sum(dist, P.Mpad) < T(.0001);
-        trunc = group_or(tr, P.Mpad) | (counter >= P.trunc_steps);
+        rew = group_sum(r, mpad);
+        term = group_sum(dist, mpad) < T(.0001);
+        trunc = group_or(tr, mpad) | (counter >= P.trunc_steps);
     }
     const bool done = P.auto_reset && (term || trunc);
     if (valid && i == 0) {
