@@ -154,12 +154,18 @@ class Handle:
         """Host path (NumPy in, NumPy out): H2D, launch, D2H inside the C call."""
         a = np.ascontiguousarray(action, self.np_dtype).reshape(self.N, self.M, self.A)
         if not hasattr(self, "_hbuf"):
-            self._hbuf = (np.empty((self.N, self.M, self.O), self.np_dtype), np.empty(self.N, self.np_dtype),
+            # the observation buffer is page-locked, so the library DMAs into it directly (no staging copy)
+            self._hbuf = (self.pinned_empty((self.N, self.M, self.O)), np.empty(self.N, self.np_dtype),
                           np.empty(self.N, np.uint8), np.empty(self.N, np.uint8), np.empty((self.N, self.M), np.uint8))
         o, r, te, tr, fl = self._hbuf
         self._check(self.lib.adrp_step_host(self._h, a.ctypes.data, o.ctypes.data, r.ctypes.data, te.ctypes.data,
                                             tr.ctypes.data, fl.ctypes.data), "adrp_step_host")
         return o, r, te, tr, fl
+
+    def pinned_empty(self, shape):
+        """Page-locked NumPy array in the handle's dtype (for actions handed to ``step_host`` without a staging copy)."""
+        torch = _torch()
+        return torch.empty(tuple(shape), dtype=self.dtype, pin_memory=True).numpy()
 
     def set_profiling(self, on=True):
         self._check(self.lib.adrp_set_profiling(self._h, int(on)), "adrp_set_profiling")

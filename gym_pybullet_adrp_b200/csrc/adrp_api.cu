@@ -33,6 +33,7 @@ __global__ void fma_peak_kernel(float* sink, int iters, float a, float b)
 }
 
 thread_local std::string g_create_error;
+constexpr int kBlockHost = 128;          // = adrp::kBlock of the kernel translation units
 
 struct HandleBase {
     adrp_config cfg;
@@ -49,7 +50,7 @@ struct HandleBase {
     uint8_t *h_term = nullptr, *h_trunc = nullptr, *h_flags = nullptr;
     void *d_action = nullptr, *d_obs = nullptr, *d_reward = nullptr;
     uint8_t *d_term = nullptr, *d_trunc = nullptr, *d_flags = nullptr;
-    cudaStream_t own_stream = nullptr;
+    cudaStream_t own_stream = nullptr, own_stream2 = nullptr;
     virtual ~HandleBase() {}
 };
 
@@ -103,6 +104,7 @@ void derive_params(const adrp_config& c, KParams<T>& P)
     P.physics = c.physics; P.drone_model = c.drone_model; P.action_type = c.action_type; P.env_kind = c.env_kind;
     P.race_mode = c.race_mode; P.auto_reset = c.auto_reset; P.pid_model = c.dslpid_model;
     P.Dpad = (long long)P.N * P.Mpad;
+    P.env_begin = 0; P.env_end = P.N;
     P.pyb_freq = c.pyb_freq;
     // step_counter / PYB_FREQ > EPISODE_LEN_SEC, evaluated like Python does (double division)
     int ts = 0;
@@ -267,8 +269,11 @@ int do_reset(Handle<T>* h, const uint8_t* mask, const T* draws, T* obs, cudaStre
 }
 
 template <typename T>
-int do_step(Handle<T>* h, const T* action, const T* noise, T* obs, T* reward, uint8_t* te, uint8_t* tr, uint8_t* fl, cudaStream_t s)
+int do_step(Handle<T>* h, const T* action, const T* noise, T* obs, T* reward, uint8_t* te, uint8_t* tr, uint8_t* fl, cudaStream_t s,
+            int env_begin = 0, int env_end = -1)
 {
+    KParams<T> P = h->P;
+    P.env_begin = env_begin; P.env_end = env_end < 0 ? P.N : env_end;
     if (h->profiling) {
         if (h->ev_pending) {          // harvest the previous launch's time before re-recording the events
             float ms = 0;
@@ -279,8 +284,8 @@ int do_step(Handle<T>* h, const T* action, const T* noise, T* obs, T* reward, ui
         CUDA_TRY(h, cudaEventRecord(h->ev0, s));
     }
     h->launches++;
-    if (h->race) CUDA_TRY(h, Launch<T>::race_step(h->P, h->RP, h->B, h->RB, action, noise, obs, reward, te, tr, fl, s));
-    else CUDA_TRY(h, Launch<T>::step(h->P, h->B, action, obs, reward, te, tr, fl, s));
+    if (h->race) CUDA_TRY(h, Launch<T>::race_step(P, h->RP, h->B, h->RB, action, noise, obs, reward, te, tr, fl, s));
+    else CUDA_TRY(h, Launch<T>::step(P, h->B, action, obs, reward, te, tr, fl, s));
     if (h->profiling) { CUDA_TRY(h, cudaEventRecord(h->ev1, s)); h->ev_pending = true; }
     return ADRP_OK;
 }
@@ -350,6 +355,7 @@ int adrp_destroy(adrp_handle* h)
     cudaFreeHost(b->h_term); cudaFreeHost(b->h_trunc); cudaFreeHost(b->h_flags);
     cudaFree(b->d_action); cudaFree(b->d_obs); cudaFree(b->d_reward); cudaFree(b->d_term); cudaFree(b->d_trunc); cudaFree(b->d_flags);
     if (b->own_stream) cudaStreamDestroy(b->own_stream);
+    if (b->own_stream2) cudaStreamDestroy(b->own_stream2);
     delete b;
     return ADRP_OK;
 }
@@ -429,6 +435,7 @@ int ensure_staging(Handle<T>* h)
     const KParams<T>& P = h->P;
     const size_t nd = (size_t)P.N * P.M;
     CUDA_TRY(h, cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
+    CUDA_TRY(h, cudaStreamCreateWithFlags(&h->own_stream2, cudaStreamNonBlocking));
     CUDA_TRY(h, cudaMallocHost(&h->h_action, sizeof(T) * nd * P.A));
     CUDA_TRY(h, cudaMallocHost(&h->h_obs, sizeof(T) * nd * P.O));
     CUDA_TRY(h, cudaMallocHost(&h->h_reward, sizeof(T) * P.N));
@@ -444,7 +451,17 @@ int ensure_staging(Handle<T>* h)
     return ADRP_OK;
 }
 
-// Host-buffer step: pageable user memory -> pinned staging -> device -> kernel -> device -> pinned -> user.
+bool is_pinned(const void* p)
+{
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return at.type == cudaMemoryTypeHost;
+}
+
+// Host-buffer step (the call a NumPy user of the reference makes).  The env range is cut into chunks that
+// alternate between two streams: chunk c+1's action upload and kernel overlap chunk c's observation download
+// (envs are independent, so a chunk is a complete step of its envs).  Page-locked caller buffers (cudaHostAlloc /
+// cudaHostRegister, e.g. torch pin_memory) are DMA'd directly; pageable ones go through the handle's pinned staging.
 template <typename T>
 int do_step_host(Handle<T>* h, const void* action, void* obs, void* reward, uint8_t* te, uint8_t* tr, uint8_t* fl)
 {
@@ -452,18 +469,30 @@ int do_step_host(Handle<T>* h, const void* action, void* obs, void* reward, uint
     if (rc != ADRP_OK) return rc;
     const KParams<T>& P = h->P;
     const size_t nd = (size_t)P.N * P.M;
-    cudaStream_t s = h->own_stream;
-    memcpy(h->h_action, action, sizeof(T) * nd * P.A);
-    CUDA_TRY(h, cudaMemcpyAsync(h->d_action, h->h_action, sizeof(T) * nd * P.A, cudaMemcpyHostToDevice, s));
-    rc = do_step<T>(h, (const T*)h->d_action, (const T*)nullptr, (T*)h->d_obs, (T*)h->d_reward, h->d_term, h->d_trunc, h->d_flags, s);
-    if (rc != ADRP_OK) return rc;
-    CUDA_TRY(h, cudaMemcpyAsync(h->h_obs, h->d_obs, sizeof(T) * nd * P.O, cudaMemcpyDeviceToHost, s));
-    CUDA_TRY(h, cudaMemcpyAsync(h->h_reward, h->d_reward, sizeof(T) * P.N, cudaMemcpyDeviceToHost, s));
-    CUDA_TRY(h, cudaMemcpyAsync(h->h_term, h->d_term, P.N, cudaMemcpyDeviceToHost, s));
-    CUDA_TRY(h, cudaMemcpyAsync(h->h_trunc, h->d_trunc, P.N, cudaMemcpyDeviceToHost, s));
-    if (fl) CUDA_TRY(h, cudaMemcpyAsync(h->h_flags, h->d_flags, nd, cudaMemcpyDeviceToHost, s));
-    CUDA_TRY(h, cudaStreamSynchronize(s));
-    memcpy(obs, h->h_obs, sizeof(T) * nd * P.O);
+    const bool pin_a = is_pinned(action), pin_o = is_pinned(obs);
+    const T* a_src = pin_a ? (const T*)action : (const T*)h->h_action;
+    T* o_dst = pin_o ? (T*)obs : (T*)h->h_obs;
+    if (!pin_a) memcpy(h->h_action, action, sizeof(T) * nd * P.A);
+    const int epb = kBlockHost / P.Mpad;                                   // envs per thread block
+    int chunks = (int)(nd * P.O * sizeof(T) / (8u << 20));                  // ~8 MiB of observations per chunk
+    chunks = chunks < 1 ? 1 : (chunks > 8 ? 8 : chunks);
+    int per = ((P.N + chunks - 1) / chunks + epb - 1) / epb * epb;
+    for (int c = 0, e0 = 0; e0 < P.N; ++c, e0 += per) {
+        const int e1 = e0 + per < P.N ? e0 + per : P.N;
+        cudaStream_t s = c & 1 ? h->own_stream2 : h->own_stream;
+        const size_t r0 = (size_t)e0 * P.M, rn = (size_t)(e1 - e0) * P.M;
+        CUDA_TRY(h, cudaMemcpyAsync((T*)h->d_action + r0 * P.A, a_src + r0 * P.A, sizeof(T) * rn * P.A, cudaMemcpyHostToDevice, s));
+        rc = do_step<T>(h, (const T*)h->d_action, (const T*)nullptr, (T*)h->d_obs, (T*)h->d_reward, h->d_term, h->d_trunc, h->d_flags, s, e0, e1);
+        if (rc != ADRP_OK) return rc;
+        CUDA_TRY(h, cudaMemcpyAsync(o_dst + r0 * P.O, (T*)h->d_obs + r0 * P.O, sizeof(T) * rn * P.O, cudaMemcpyDeviceToHost, s));
+        CUDA_TRY(h, cudaMemcpyAsync((T*)h->h_reward + e0, (T*)h->d_reward + e0, sizeof(T) * (e1 - e0), cudaMemcpyDeviceToHost, s));
+        CUDA_TRY(h, cudaMemcpyAsync(h->h_term + e0, h->d_term + e0, e1 - e0, cudaMemcpyDeviceToHost, s));
+        CUDA_TRY(h, cudaMemcpyAsync(h->h_trunc + e0, h->d_trunc + e0, e1 - e0, cudaMemcpyDeviceToHost, s));
+        if (fl) CUDA_TRY(h, cudaMemcpyAsync(h->h_flags + r0, h->d_flags + r0, rn, cudaMemcpyDeviceToHost, s));
+    }
+    CUDA_TRY(h, cudaStreamSynchronize(h->own_stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->own_stream2));
+    if (!pin_o) memcpy(obs, h->h_obs, sizeof(T) * nd * P.O);
     memcpy(reward, h->h_reward, sizeof(T) * P.N);
     memcpy(te, h->h_term, P.N);
     memcpy(tr, h->h_trunc, P.N);

@@ -5,6 +5,8 @@
 
 namespace adrp {
 
+static_assert(kBlock == 128, "adrp_api.cu cuts host-path chunks in units of 128-thread blocks");
+
 inline unsigned grid_for(long long D) { return (unsigned)((D + kBlock - 1) / kBlock); }
 
 template <typename T>
@@ -47,7 +49,7 @@ cudaError_t Launch<T>::step(const KParams<T>& P, const KBuffers<T>& b, const T* 
 {
     const bool pid = P.action_type == ADRP_ACT_PID || P.action_type == ADRP_ACT_ONE_D_PID ||
                      P.action_type == ADRP_ACT_VEL || P.action_type == ADRP_ACT_PID_FULL;
-    const unsigned grid = grid_for(P.Dpad);
+    const unsigned grid = grid_for((long long)(P.env_end - P.env_begin) * P.Mpad);
 #define ADRP_LAUNCH_STEP(MP) step_kernel<T, -1, 0, MP><<<grid, kBlock, 0, s>>>(P, b, action, obs, reward, te, tr, fl)
     if (pid) step_kernel<T, -1, 1, 0><<<grid, kBlock, 0, s>>>(P, b, action, obs, reward, te, tr, fl);
     else switch (P.Mpad) {
@@ -99,7 +101,7 @@ cudaError_t Launch<T>::race_step(const KParams<T>& P, const RaceParams<T>& RP, c
                                  const T* action, const T* noise, T* obs, T* reward, uint8_t* te, uint8_t* tr,
                                  uint8_t* fl, cudaStream_t s)
 {
-    race_step_kernel<T><<<grid_for(P.Dpad), kBlock, race_smem_bytes(P, RP), s>>>(P, RP, b, rb, action, noise, obs, reward, te, tr, fl);
+    race_step_kernel<T><<<grid_for((long long)(P.env_end - P.env_begin) * P.Mpad), kBlock, race_smem_bytes(P, RP), s>>>(P, RP, b, rb, action, noise, obs, reward, te, tr, fl);
     return cudaGetLastError();
 }
 

@@ -18,6 +18,7 @@ struct KParams {
     int N, M, Mpad, S, A, O, B;           // envs, drones/env, lanes/env, substeps, action dim, obs dim, action-buffer length
     int physics, drone_model, action_type, env_kind, race_mode, auto_reset, pid_model;
     long long Dpad;                       // N * Mpad
+    int env_begin, env_end;               // env range of THIS launch (chunked host path); the whole shard otherwise
     int pyb_freq;
     int trunc_steps;                      // smallest step_counter with step_counter/PYB_FREQ > EPISODE_LEN_SEC
     // BaseAviary constants (envs/BaseAviary.py:74-128)

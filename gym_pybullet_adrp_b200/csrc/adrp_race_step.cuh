@@ -59,19 +59,19 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T* trk = reinterpret_cast<T*>(smem_raw);
-    const long long t = (long long)blockIdx.x * kBlock + threadIdx.x;
+    const long long t = (long long)P.env_begin * P.Mpad + (long long)blockIdx.x * kBlock + threadIdx.x;
     const int lane = threadIdx.x & 31;
     const int i = (int)(t & (P.Mpad - 1));
     const long long env = t / P.Mpad;
     const int lane_base = lane - i;
     const int EPB = kBlock / P.Mpad, e = threadIdx.x / P.Mpad;
-    const bool valid = env < P.N && i < P.M;
+    const bool valid = env < P.env_end && i < P.M;
     const long long D = P.Dpad;
     const int phy = P.physics;
     const long long od = valid ? env * P.M + i : 0;
 
     // ---- stage the block's track instances (coalesced over envs) in shared memory
-    const long long env0 = (long long)blockIdx.x * EPB;
+    const long long env0 = (long long)P.env_begin + (long long)blockIdx.x * EPB;
     for (int idx = threadIdx.x; idx < RP.TF * EPB; idx += kBlock) {
         const int f = idx / EPB, el = idx - f * EPB;
         trk[idx] = env0 + el < P.N ? rb.track[(long long)f * P.N + env0 + el] : T(0);

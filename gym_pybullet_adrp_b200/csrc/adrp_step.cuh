@@ -72,13 +72,13 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
             T* __restrict__ obs, T* __restrict__ reward, uint8_t* __restrict__ terminated,
             uint8_t* __restrict__ truncated, uint8_t* __restrict__ drone_flags)
 {
-    const long long t = (long long)blockIdx.x * kBlock + threadIdx.x;
-    const int lane = threadIdx.x & 31;
     const int mpad = MP > 0 ? MP : P.Mpad;
+    const long long t = (long long)P.env_begin * mpad + (long long)blockIdx.x * kBlock + threadIdx.x;
+    const int lane = threadIdx.x & 31;
     const int i = (int)(t & (mpad - 1));
     const long long env = t / mpad;
     const int lane_base = lane - i;
-    const bool valid = env < P.N && i < P.M;
+    const bool valid = env < P.env_end && i < P.M;
     const long long D = P.Dpad;
     const int phy = PHY_CT >= 0 ? PHY_CT : P.physics;
     const long long od = valid ? env * P.M + i : 0;      // row of this drone in (N, M, .) tensors
@@ -195,7 +195,7 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
     // ---- reward and flags (HoverAviary.py:68-117; MultiHoverAviary.py:75-130; CtrlAviary.py:144-200)
     T rew = T(-1);
     int term = 0, trunc = 0;
-    const int counter = (valid || env < P.N) ? b.step_counter[env < P.N ? env : 0] : 0;
+    const int counter = env < P.env_end ? b.step_counter[env] : 0;
     if (P.env_kind != ADRP_ENV_CTRL) {
         T r = T(0), dist = T(0);
         int tr = 0;
