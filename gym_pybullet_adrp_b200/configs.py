@@ -42,7 +42,7 @@ _BLOCKS = {
                           "dynamics": {"distrib": _U, "low": [-0.1, -0.1, -0.1], "high": [0.1, 0.1, 0.1]}},
 }
 _SWITCHES = ["random_drone_state", "random_drone_inertia", "random_gates_obstacles", "disturbances"]
-_LEVEL_FLAGS = {"getting_started": (0, 0, 0, 0), "level0": (1, 0, 0, 0), "level1": (1, 1, 0, 0),
+_LEVEL_FLAGS = {"getting_started": (0, 0, 0, 0), "level0": (1, 0, 0, 0), "level1": (1, 1, 0, 1),
                 "level2": (1, 1, 1, 1), "level3": (1, 1, 1, 1), "twogates": (1, 0, 0, 0)}
 _TRACK = {
     "gates": [[0.45, -1.0, 0.525, 0, 0, 2.35, 1], [1.0, -1.55, 1.0, 0, 0, -0.78, 0],

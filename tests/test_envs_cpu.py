@@ -1,0 +1,76 @@
+"""CPU: API surface of the env / controller classes (names, constructor arguments, attributes, spaces and error
+behaviour of the reference) -- nothing here touches a GPU: the C-ABI handle is created lazily."""
+import numpy as np
+import pytest
+
+from gym_pybullet_adrp_b200 import configs
+from gym_pybullet_adrp_b200.envs import CtrlAviary, HoverAviary, MultiHoverAviary, MultiRaceAviary
+from gym_pybullet_adrp_b200.utils.enums import ActionType, DroneModel, ObservationType, Physics, RaceMode
+
+
+def test_enum_values_are_the_references():
+    assert DroneModel("cf2x_IROS") is DroneModel.CF2X and Physics("pyb_gnd_drag_dw") is Physics.PYB_GND_DRAG_DW
+    assert ActionType("one_d_pid") is ActionType.ONE_D_PID and RaceMode(1) is RaceMode.COMPETE
+    with pytest.raises(ValueError):
+        DroneModel("cf2x")                       # the fork renamed the value
+
+
+def test_base_constants_match_survey_appendix_f():
+    e = CtrlAviary()
+    assert e.PYB_STEPS_PER_CTRL == 1 and e.NUM_DRONES == 1
+    assert abs(e.HOVER_RPM - 16364.4219) < 1e-3 and abs(e.MAX_RPM - 24546.6328) < 1e-3
+    assert abs(e.GND_EFF_H_CLIP - 0.0377637) < 1e-6 and abs(e.MAX_THRUST - 0.761607) < 1e-6
+    np.testing.assert_allclose(e.INIT_XYZS, [[0, 0, 0.1125]])
+    assert e.observation_space.shape == (1, 20) and e.action_space.shape == (1, 4)
+    assert e.action_space.high.max() == pytest.approx(e.MAX_RPM, rel=1e-6)
+
+
+def test_constructor_errors_like_reference():
+    with pytest.raises(ValueError, match="not divisible"):
+        CtrlAviary(pyb_freq=240, ctrl_freq=7)
+    with pytest.raises(ValueError, match="initial_xyzs"):
+        CtrlAviary(num_drones=2, initial_xyzs=np.zeros((3, 3)))
+    with pytest.raises(NotImplementedError, match="unavailable on this box"):
+        HoverAviary(gui=True)
+    with pytest.raises(NotImplementedError, match="unavailable on this box"):
+        HoverAviary(obs=ObservationType.RGB)
+
+
+def test_rl_spaces():
+    e = HoverAviary()
+    assert (e.CTRL_FREQ, e.PYB_FREQ, e.ACTION_BUFFER_SIZE, e.EPISODE_LEN_SEC) == (30, 240, 15, 8)
+    assert e.observation_space.shape == (1, 72) and e.action_space.shape == (1, 4)
+    e = HoverAviary(act=ActionType.ONE_D_RPM)
+    assert e.observation_space.shape == (1, 27) and e.action_space.shape == (1, 1)
+    e = MultiHoverAviary(num_drones=3, act=ActionType.PID)
+    assert e.observation_space.shape == (3, 12 + 15 * 3)
+    np.testing.assert_allclose(e.TARGET_POS[:, 2], e.INIT_XYZS[:, 2] + [1, 0.5, 1 / 3])
+
+
+def test_race_env_surface():
+    rc = configs.load_config("level3")
+    e = MultiRaceAviary(rc, racemode=RaceMode.COMPETE)
+    assert (e.PYB_FREQ, e.CTRL_FREQ, e.PYB_STEPS_PER_CTRL, e.NUM_DRONES) == (500, 25, 20, 2)
+    assert e.observation_space.shape == (2, 55) and e.action_space.shape == (2, 4)
+    assert MultiRaceAviary(rc, racemode=RaceMode.COMPARE).observation_space.shape == (2, 49)
+    np.testing.assert_allclose(e.INIT_XYZS, [[0.9, 0.9, 0.05], [1.1, 1.1, 0.05]])
+    cfg = e._make_config()
+    assert cfg.track.num_gates == 4 and cfg.rnd.disturbances == 1 and cfg.drone.pyb_mass == 0.027   # cf2x.urdf body (E16)
+    with pytest.raises(ValueError):
+        MultiRaceAviary(rc, num_drones=3)._make_config()       # level3 has two init_states
+
+
+def test_config_files_equal_builtin_tables():
+    """The built-in level tables are the reference's YAML files (skipped where /root/reference is absent)."""
+    import os
+    ref = "/root/reference/config"
+    if not os.path.isdir(ref):
+        pytest.skip("reference not mounted")
+    for name in ("getting_started", "level0", "level1", "level2", "level3", "twogates"):
+        a, b = configs.load_config(os.path.join(ref, name + ".yaml")), configs.builtin_config(name)
+        for key in ("gates", "obstacles", "bounds", "init_states", "episode_len_sec", "random_drone_state",
+                    "random_drone_inertia", "random_gates_obstacles", "disturbances", "ctrl_freq"):
+            assert a.get(key) == b.get(key), (name, key)
+        for key in ("random_drone_state_info", "random_drone_inertia_info", "random_gates_obstacles_info", "disturbances_info"):
+            if b.get(key.replace("_info", "")):
+                assert a[key] == b[key], (name, key)

@@ -1,0 +1,92 @@
+"""GPU: the env / controller classes (the reference's interface) end to end against the golden vectors the
+reference's own classes produced -- the tests read like the reference's usage (examples/pid.py, learn.py, sim.py)."""
+import numpy as np
+import pytest
+
+from gym_pybullet_adrp_b200 import configs
+from gym_pybullet_adrp_b200.control import DSLPIDControl
+from gym_pybullet_adrp_b200.envs import CtrlAviary, HoverAviary, MultiHoverAviary, MultiRaceAviary
+from gym_pybullet_adrp_b200.utils.enums import ActionType, DroneModel, Physics, RaceMode
+from tests import golden_cases as gc
+
+pytestmark = pytest.mark.gpu
+
+
+def test_pid_example_loop_ctrl_aviary_plus_dslpid():
+    """examples/pid.py:101-147: CtrlAviary stepped with the RPMs DSLPIDControl.computeControlFromState returns
+    (BASELINE config 1: one CF2X, DYN, 240/30 Hz, hover target straight above)."""
+    meta, z = gc.load("pid_dyn_c1")
+    env = CtrlAviary(drone_model=DroneModel.CF2X, num_drones=1, initial_xyzs=np.array(meta["init_xyz"]), physics=Physics.DYN,
+                     pyb_freq=240, ctrl_freq=30, precision="fp64")
+    ctrl = DSLPIDControl(drone_model=DroneModel.CF2X)
+    obs, info = env.reset()
+    assert obs.shape == (1, 20) and info == {"answer": 42}
+    action = np.zeros((1, 4))
+    worst = 0.0
+    for k in range(1, meta["steps"]):
+        obs, reward, terminated, truncated, info = env.step(action)
+        if k == 1:                                          # the golden run starts from its first recorded state
+            continue
+        action[0, :], _, _ = ctrl.computeControlFromState(control_timestep=env.CTRL_TIMESTEP, state=obs[0],
+                                                          target_pos=np.array(meta["target"]))
+        assert reward == -1 and terminated is False and truncated is False
+    # closed loop reaches the hover target like the reference's run does
+    assert abs(obs[0, 2] - z["obs"][-1][2]) < 0.05 and abs(obs[0, 2] - 1.0) < 0.1
+    np.testing.assert_allclose(env._getDroneStateVector(0)[0:3], obs[0, 0:3], atol=1e-12)
+    env.close()
+
+
+@pytest.mark.parametrize("name", ["hover_pyb_rpm", "hover_dyn_one_d_rpm", "hover_pyb_one_d_pid"])
+def test_hover_aviary_matches_reference_run(name):
+    meta, z = gc.load(name)
+    env = HoverAviary(physics=Physics[meta["physics"]], pyb_freq=meta["pyb_freq"], ctrl_freq=meta["ctrl_freq"],
+                      act=ActionType[meta["act"]], initial_xyzs=np.array(meta["init_xyz"]), precision="fp64")
+    obs, _ = env.reset()
+    assert obs.shape == env.observation_space.shape and obs.dtype == np.float32      # BaseRLAviary.py:312
+    assert gc.rel_err(obs, z["obs0"]) < 1e-6
+    for k in range(meta["steps"]):
+        obs, rew, te, tr, info = env.step(z["actions"][k])
+        assert gc.rel_err(obs[:, :12], z["obs"][k][:, :12]) < 1e-6
+        np.testing.assert_array_equal(obs[:, 12:], z["obs"][k][:, 12:].astype(np.float32))
+        assert abs(rew - z["reward"][k]) < 1e-9 * max(1, abs(z["reward"][k]))
+        assert te == bool(z["terminated"][k]) and tr == bool(z["truncated"][k])
+    env.close()
+
+
+def test_multihover_batched_envs_are_independent_copies():
+    """num_envs > 1: torch tensors with a leading env axis; every env fed the golden actions reproduces the golden run."""
+    import torch
+    meta, z = gc.load("multihover_pyb_rpm_m2")
+    N = 5
+    env = MultiHoverAviary(num_drones=2, physics=Physics[meta["physics"]], pyb_freq=meta["pyb_freq"], ctrl_freq=meta["ctrl_freq"],
+                           act=ActionType[meta["act"]], initial_xyzs=np.array(meta["init_xyz"]), precision="fp64", num_envs=N,
+                           auto_reset=False)
+    obs, _ = env.reset()
+    assert isinstance(obs, torch.Tensor) and tuple(obs.shape) == (N, 2, env.observation_space.shape[1])
+    for k in range(meta["steps"]):
+        a = np.broadcast_to(z["actions"][k], (N,) + z["actions"][k].shape)
+        obs, rew, te, tr, _ = env.step(a)
+        assert tuple(rew.shape) == (N,) and te.dtype == torch.bool
+        o = obs.cpu().numpy()
+        assert gc.rel_err(o[:, :, :12], np.broadcast_to(z["obs"][k][:, :12], o[:, :, :12].shape)) < 1e-6
+        assert np.allclose(rew.cpu().numpy(), z["reward"][k], rtol=1e-9)
+    env.close()
+
+
+def test_multi_race_aviary_matches_reference_run():
+    """scripts/sim.py-style loop on the reference's own race run (level3, COMPARE), draws and disturbances injected."""
+    meta, z = gc.load("race_pyb_compare_level3")
+    rc = configs.load_config(meta["level"])
+    env = MultiRaceAviary(rc, num_drones=meta["M"], physics=Physics[meta["physics"]], racemode=RaceMode[meta["racemode"]],
+                          precision="fp64")
+    obs, info = env.reset(draws=gc.place_draws(rc, z["draws"], meta["M"])[None])
+    assert obs.shape == (2, 49)
+    for k in range(meta["steps"]):
+        obs, reward, terminated, truncated, info = env.step(z["actions"][k], noise=z["noise"][k][None])
+        assert gc.rel_err(obs, z["obs"][k]) < 1e-9, k
+        np.testing.assert_array_equal(env.drones_eliminated, z["eliminated"][k])
+        np.testing.assert_array_equal(env.current_gate, z["current_gate"][k])
+        assert reward == 0 and terminated == bool(z["terminated"][k]) and truncated == bool(z["truncated"][k])
+    with pytest.raises(NotImplementedError):
+        env.step([("fst", ())] * 2)
+    env.close()
