@@ -255,8 +255,13 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
     __syncwarp();
     if (valid) {
         if (done) {
-            race_reset_drone(P, RP, rb, env, i, episode, (const T*)nullptr, d, m, body);
-            store_body(rb, D, t, body);
+            // reset into copies: the out-of-line call takes addresses, and the live state must stay in registers
+            Drone<T> d2;
+            Mel<T> m2;
+            T body2[4];
+            race_reset_drone(P, RP, rb, env, i, episode, (const T*)nullptr, d2, m2, body2);
+            d = d2; m = m2;
+            store_body(rb, D, t, body2);
             current_gate = 0; latch = 0;
             if (i == 0) rb.episode[env] = episode + 1;
         }

@@ -89,9 +89,10 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
     // ---- action -> RPM (CtrlAviary.py:140; BaseRLAviary.py:160-239)
     T rpm[4];
     const T* a = action + od * P.A;
-    T act_in[12];
+    constexpr int AMAX = ACTC == 0 ? 4 : 12;             // RPM-type actions have at most 4 components
+    T act_in[AMAX];
 #pragma unroll
-    for (int k = 0; k < 12; ++k) act_in[k] = (valid && k < P.A) ? a[k] : T(0);
+    for (int k = 0; k < AMAX; ++k) act_in[k] = (valid && k < P.A) ? a[k] : T(0);
     PidState<T> pc;
     if (ACTC == 0) {
         if (P.action_type == ADRP_ACT_RPM_RAW) {
@@ -101,7 +102,7 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
             // NumPy evaluates (1 + 0.05*a) on the float32 action before promoting (BaseRLAviary.py:192)
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                const float av = (float)act_in[P.action_type == ADRP_ACT_ONE_D_RPM ? 0 : k];
+                const float av = (float)(P.action_type == ADRP_ACT_ONE_D_RPM ? act_in[0] : act_in[k]);
                 rpm[k] = P.hover_rpm * (T)__fadd_rn(1.0f, __fmul_rn(0.05f, av));
             }
         }
@@ -182,7 +183,9 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
         // action buffer (deque(maxlen=ctrl_freq//2), BaseRLAviary.py:66-67,187): the newest action
         // overwrites the oldest ring slot; the observation lists the slots oldest -> newest
         head = b.ring_head[env];
-        for (int k = 0; k < P.A; ++k) st(b.ring, D, head * P.A + k, t, act_in[k]);
+#pragma unroll
+        for (int k = 0; k < AMAX; ++k)
+            if (k < P.A) st(b.ring, D, head * P.A + k, t, act_in[k]);
         const int nh = head + 1 == P.B ? 0 : head + 1;
         for (int j = 0; j < P.B; ++j) {
             int slot = nh + j;
