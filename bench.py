@@ -84,10 +84,15 @@ def make_actions(wl, n_envs, M, A, seed, count):
         # full-state setpoints [x, y, z, yaw]: c3 climbs and heads for the first gate, c5m holds a formation
         cfg = make_cfg(wl, 1)
         init = np.array([[cfg.init_xyz[i][k] for k in range(3)] for i in range(M)], np.float32)
+        # one hover target per drone (formation slot + U(-0.2, 0.2) m, staggered heights), re-sent every control step
+        # with centimetre jitter: setpoint JUMPS of decimetres every 40 ms would tumble some of the 10^6 drones, and a
+        # tumbling drone that crosses a neighbour's height meets the downwash singularity
         a = np.zeros((count, n_envs, M, 4), np.float32)
+        xy = init[None, :, 0:2] + rng.uniform(-0.2, 0.2, (n_envs, M, 2))
+        z = (0.4 if wl == "c3" else 0.6) + 0.15 * (np.arange(M) % 3)[None, :] + rng.uniform(0, 0.05, (n_envs, M))
         for c in range(count):
-            a[c, :, :, 0:2] = init[None, :, 0:2] + rng.uniform(-0.2, 0.2, (n_envs, M, 2))
-            a[c, :, :, 2] = (0.4 if wl == "c3" else 0.6) + 0.15 * (np.arange(M) % 3)[None, :] + rng.uniform(0, 0.05, (n_envs, M))
+            a[c, :, :, 0:2] = xy + rng.uniform(-0.01, 0.01, (n_envs, M, 2))
+            a[c, :, :, 2] = z + rng.uniform(-0.01, 0.01, (n_envs, M))
         return a
     if WORKLOADS[wl][6] == _abi.ACT_RPM_RAW:
         # rpm = HOVER_RPM (1 + 0.05 a) (BaseRLAviary.py:192) with a = collective U(-1,1) + 1 % per-motor differential:
@@ -141,6 +146,23 @@ def algorithmic_flops_per_substep(wl):
     fl += 17 * (M - 1) if phy & _abi.PHY_DW else 0
     fl += 450 if kind == _abi.ENV_RACE else 0
     return fl
+
+
+def ncu_traffic_bytes(wl, n_envs):
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the step kernel, from the committed
+    `ncu --set full` capture of this workload (profiles/r01b_ncu_<wl>_metrics.csv); None if there is none or the
+    capture was taken at another size."""
+    path = os.path.join(ROOT, "profiles", f"r01b_ncu_{wl}_metrics.csv")
+    if n_envs != WORKLOADS[wl][0] or not os.path.exists(path):
+        return None
+    import csv
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    total = 0.0
+    with open(path) as f:
+        for name, unit, value in csv.reader(f):
+            if name in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                total += float(value) * scale.get(unit, 1.0)
+    return total or None
 
 
 class ClockSampler(threading.Thread):
@@ -347,7 +369,7 @@ def main():
                        else "working set fits L2 (small workload)", "action_pool": pool},
             "substep_updates_per_s": value * S,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak if achieved else None, "traffic": None,
+                         "frac": achieved / peak if achieved else None, "traffic": ncu_traffic_bytes(wl, N),
                          "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback",
                          "kernel_ms": kernel_ms, "algorithmic_bytes_per_drone_step": bpd},
             "fp32_roofline": {"achieved": fp32_ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": fp32_ach / fp32_peak if fp32_ach else None,

@@ -204,7 +204,8 @@ void derive_race(const adrp_config& c, const KParams<T>& P, RaceParams<T>& R)
     host_lpf2p(500.0f, 30.0f, lp);      // lpf2pInit(gyrolpf, FIRMWARE_FREQ, ACCEL_LPF_CUTOFF_FREQ): the swapped cutoffs of :116-117
     R.lpf_b0 = lp[0]; R.lpf_b1 = lp[1]; R.lpf_b2 = lp[2]; R.lpf_a1 = lp[3]; R.lpf_a2 = lp[4];
     // one firmware tick per physics substep while the episode lasts, plus the steps a caller may take after truncation
-    R.lut_ticks = ((P.trunc_steps + 64 * P.S + 1 + 31) / 32) * 32;
+    const long long want = (long long)P.trunc_steps + 64LL * P.S + 1;          // beyond the table the kernel evaluates the float64 test itself
+    R.lut_ticks = (int)(((want < (1LL << 22) ? want : (1LL << 22)) + 31) / 32) * 32;
 }
 
 template <typename T>
