@@ -124,6 +124,13 @@ void derive_params(const adrp_config& c, KParams<T>& P)
     P.gnd_eff_h_clip = (T)(0.25 * p.prop_radius * sqrt((15 * MAXR * MAXR * p.kf * p.gnd_eff_coeff) / MAXT));
     P.drag_xy = (T)p.drag_coeff_xy; P.drag_z = (T)p.drag_coeff_z;
     P.dw1 = (T)p.dw_coeff_1; P.dw2 = (T)p.dw_coeff_2; P.dw3 = (T)p.dw_coeff_3;
+    {
+        const double sc = 1.0 / sqrt(0.5 * 1.4426950408889634);
+        const double c0 = p.dw_coeff_1 * (0.25 * p.prop_radius) * (0.25 * p.prop_radius);
+        P.dwf_a = (T)(p.dw_coeff_2 * sc); P.dwf_b = (T)(p.dw_coeff_3 * sc);
+        P.dwf_l2c = (T)(c0 > 0 ? log2(c0) : -1e30);
+        P.half_dt = (T)(0.5 / c.pyb_freq); P.qr4 = (T)(0.25 * p.prop_radius);
+    }
     P.speed_limit = (T)(0.03 * p.max_speed_kmh * (1000.0 / 3600.0));
     for (int k = 0; k < 4; ++k) { P.prop_x[k] = (T)p.prop_x[k]; P.prop_y[k] = (T)p.prop_y[k]; }
     P.pyb_mass = (T)p.pyb_mass; P.pyb_jx = (T)p.pyb_ixx; P.pyb_jy = (T)p.pyb_iyy; P.pyb_jz = (T)p.pyb_izz;

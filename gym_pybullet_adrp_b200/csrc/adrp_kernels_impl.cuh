@@ -78,12 +78,32 @@ cudaError_t Launch<T>::get_state(const KParams<T>& P, const KBuffers<T>& b, T* r
     return cudaGetLastError();
 }
 
+// The race step kernel the launch uses: the product build unrolls the neighbour loops for 1 / 2 / 4 / 8 lanes per
+// env; the parity build (and wider envs) read the lane count from the params.
+template <typename T>
+using RaceStepFn = void (*)(KParams<T>, RaceParams<T>, KBuffers<T>, RaceBuffers<T>, const T*, const T*, T*, T*, uint8_t*,
+                            uint8_t*, uint8_t*);
+template <typename T>
+inline RaceStepFn<T> race_step_fn(int mpad)
+{
+    if (M<T>::fast) {
+        switch (mpad) {
+            case 1: return race_step_kernel<T, 1>;
+            case 2: return race_step_kernel<T, 2>;
+            case 4: return race_step_kernel<T, 4>;
+            case 8: return race_step_kernel<T, 8>;
+            default: break;
+        }
+    }
+    return race_step_kernel<T, 0>;
+}
+
 template <typename T>
 cudaError_t Launch<T>::race_prepare(const RaceParams<T>& RP, const KParams<T>& P)
 {
     const size_t bytes = race_smem_bytes(P, RP);
     if (bytes <= 48 * 1024) return cudaSuccess;
-    cudaError_t e = cudaFuncSetAttribute(race_step_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    cudaError_t e = cudaFuncSetAttribute(race_step_fn<T>(P.Mpad), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(race_reset_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
 }
@@ -101,7 +121,7 @@ cudaError_t Launch<T>::race_step(const KParams<T>& P, const RaceParams<T>& RP, c
                                  const T* action, const T* noise, T* obs, T* reward, uint8_t* te, uint8_t* tr,
                                  uint8_t* fl, cudaStream_t s)
 {
-    race_step_kernel<T><<<grid_for((long long)(P.env_end - P.env_begin) * P.Mpad), kBlock, race_smem_bytes(P, RP), s>>>(P, RP, b, rb, action, noise, obs, reward, te, tr, fl);
+    race_step_fn<T>(P.Mpad)<<<grid_for((long long)(P.env_end - P.env_begin) * P.Mpad), kBlock, race_smem_bytes(P, RP), s>>>(P, RP, b, rb, action, noise, obs, reward, te, tr, fl);
     return cudaGetLastError();
 }
 

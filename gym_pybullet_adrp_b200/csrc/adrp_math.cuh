@@ -30,10 +30,11 @@ template <> struct M<float> {
     // (flags, observation) keeps the IEEE forms above, so flags stay a bit-exact function of the stored state.
     static constexpr bool fast = true;
     static __device__ __forceinline__ float rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
-    static __device__ __forceinline__ float fdiv(float a, float b) { return __fdividef(a, b); }
+    static __device__ __forceinline__ float fdiv(float a, float b) { return a * rcp(b); }
     static __device__ __forceinline__ float fsqrt(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
     static __device__ __forceinline__ float frsqrt(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
-    static __device__ __forceinline__ float fexp(float x) { return __expf(x); }
+    static __device__ __forceinline__ float fexp2(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+    static __device__ __forceinline__ float fexp(float x) { return fexp2(x * 1.4426950408889634f); }
     // sin / cos of the half rotation angle of one substep: minimax polynomials on |x| <= pi/4 (Cephes sinf / cosf
     // kernels, ~1 ulp), the libm call beyond
     static __device__ __forceinline__ void sincos_small(float x, float* s, float* c)
@@ -45,6 +46,34 @@ template <> struct M<float> {
         } else {
             sincosf(x, s, c);
         }
+    }
+    static __device__ __forceinline__ float clamp(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
+    // atan2 for the substep loop: octant reduction through one MUFU.RCP, then atan(a) = a + a^3 q(a^2) on [0, 1]
+    // (degree-7 minimax q, 7e-8 absolute error = 1 ulp at pi/4); signed zeros / infinities are not special-cased
+    static __device__ __forceinline__ float atan2_loop(float y, float x)
+    {
+        const float ax = fabsf(x), ay = fabsf(y);
+        const float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
+        const float a = mn * rcp(fmaxf(mx, 1e-37f));
+        const float z = a * a;
+        float q = 2.6222428084e-03f;
+        q = q * z + -1.5132528995e-02f;
+        q = q * z + 4.1121847573e-02f;
+        q = q * z + -7.3667049965e-02f;
+        q = q * z + 1.0573931535e-01f;
+        q = q * z + -1.4185975150e-01f;
+        q = q * z + 1.9990396606e-01f;
+        q = q * z + -3.3332987058e-01f;
+        float r = (a * z) * q + a;
+        if (ay > ax) r = 1.5707963267948966f - r;
+        if (x < 0.0f) r = 3.141592653589793f - r;
+        return copysignf(r, y);
+    }
+    // cos(th) and sin(th)/th from z = th^2 (both even in th: no square root, no division); valid for z <= (pi/4)^2
+    static __device__ __forceinline__ void cos_sinc_sq(float z, float* c, float* sinc)
+    {
+        *sinc = 1.0f + z * (-1.6666654611e-1f + z * (8.3321608736e-3f + z * -1.9515295891e-4f));
+        *c = 1.0f - 0.5f * z + z * z * (4.166664568298827e-2f + z * (-1.388731625493765e-3f + z * 2.443315711809948e-5f));
     }
 };
 template <> struct M<double> {
@@ -67,8 +96,17 @@ template <> struct M<double> {
     static __device__ __forceinline__ double fdiv(double a, double b) { return a / b; }
     static __device__ __forceinline__ double fsqrt(double x) { return ::sqrt(x); }
     static __device__ __forceinline__ double frsqrt(double x) { return 1.0 / ::sqrt(x); }
+    static __device__ __forceinline__ double fexp2(double x) { return ::exp2(x); }
     static __device__ __forceinline__ double fexp(double x) { return ::exp(x); }
     static __device__ __forceinline__ void sincos_small(double x, double* s, double* c) { ::sincos(x, s, c); }
+    static __device__ __forceinline__ double clamp(double v, double lo, double hi) { return v < lo ? lo : (v > hi ? hi : v); }
+    static __device__ __forceinline__ double atan2_loop(double y, double x) { return ::atan2(y, x); }
+    static __device__ __forceinline__ void cos_sinc_sq(double z, double* c, double* sinc)
+    {
+        const double th = ::sqrt(z);
+        *c = ::cos(th);
+        *sinc = th > 0.0 ? ::sin(th) / th : 1.0;
+    }
 };
 
 // Product that is never contracted into a following add.  The motor thrusts / torques of a symmetric command
@@ -137,6 +175,19 @@ template <typename T> __device__ __forceinline__ V3<T> euler_rpy(const Q4<T>& q)
     if (sarg >= T(0.99999)) return {T(0), HALF_PI, T(2) * M<T>::atan2(-q.x, q.y)};
     return {M<T>::atan2(T(2) * (q.y * q.z + q.w * q.x), squ - sqx - sqy + sqz), M<T>::asin(sarg),
             M<T>::atan2(T(2) * (q.x * q.y + q.w * q.z), squ + sqx - sqy - sqz)};
+}
+
+// euler_rpy for the substep loop (the Mellinger wrapper differentiates it every tick): same branches, the
+// build's loop atan2.
+template <typename T> __device__ __forceinline__ V3<T> euler_rpy_loop(const Q4<T>& q)
+{
+    const T sqx = q.x * q.x, sqy = q.y * q.y, sqz = q.z * q.z, squ = q.w * q.w;
+    const T sarg = T(-2) * (q.x * q.z - q.w * q.y);
+    const T HALF_PI = T(1.5707963267948966);
+    if (sarg <= T(-0.99999)) return {T(0), -HALF_PI, T(2) * M<T>::atan2(q.x, -q.y)};
+    if (sarg >= T(0.99999)) return {T(0), HALF_PI, T(2) * M<T>::atan2(-q.x, q.y)};
+    return {M<T>::atan2_loop(T(2) * (q.y * q.z + q.w * q.x), squ - sqx - sqy + sqz), M<T>::asin(sarg),
+            M<T>::atan2_loop(T(2) * (q.x * q.y + q.w * q.z), squ + sqx - sqy - sqz)};
 }
 
 // |roll| < pi/2 and |pitch| < pi/2 (the _groundEffect gate, envs/BaseAviary.py:749) without

@@ -49,6 +49,10 @@ struct Mel {
 struct MelSetpoint { float pos[3], qz, qw; };   // full-state command: vel = acc = rates = 0, yaw-only quaternion (:510-543)
 
 __device__ __forceinline__ float fw_clamp(float v, float lo, float hi) { return v < lo ? lo : (v > hi ? hi : v); }
+template <typename T> __device__ __forceinline__ float fw_clampT(float v, float lo, float hi)
+{
+    return M<T>::fast ? fminf(fmaxf(v, lo), hi) : fw_clamp(v, lo, hi);
+}
 __device__ __forceinline__ float fw_radians(float d) { return (3.14159265358979323846f / 180.0f) * d; }
 __device__ __forceinline__ float fw_degrees(float r) { return (180.0f / 3.14159265358979323846f) * r; }
 
@@ -79,15 +83,16 @@ __device__ __forceinline__ void fw_mellinger(MelFw& m, const MelSetpoint& sp, fl
     float r_error[3], v_error[3], tt[3];
 #pragma unroll
     for (int k = 0; k < 3; ++k) { r_error[k] = sp.pos[k] - pos[k]; v_error[k] = sp_vel - vel[k]; }
-    m.i_error_z += r_error[2] * dt; m.i_error_z = fw_clamp(m.i_error_z, -i_range_z, i_range_z);
-    m.i_error_x += r_error[0] * dt; m.i_error_x = fw_clamp(m.i_error_x, -i_range_xy, i_range_xy);
-    m.i_error_y += r_error[1] * dt; m.i_error_y = fw_clamp(m.i_error_y, -i_range_xy, i_range_xy);
+    m.i_error_z += r_error[2] * dt; m.i_error_z = fw_clampT<T>(m.i_error_z, -i_range_z, i_range_z);
+    m.i_error_x += r_error[0] * dt; m.i_error_x = fw_clampT<T>(m.i_error_x, -i_range_xy, i_range_xy);
+    m.i_error_y += r_error[1] * dt; m.i_error_y = fw_clampT<T>(m.i_error_y, -i_range_xy, i_range_xy);
     tt[0] = mass * sp_acc + kp_xy * r_error[0] + kd_xy * v_error[0] + ki_xy * m.i_error_x;
     tt[1] = mass * sp_acc + kp_xy * r_error[1] + kd_xy * v_error[1] + ki_xy * m.i_error_y;
     tt[2] = mass * (sp_acc + GRAVITY_MAGNITUDE) + kp_z * r_error[2] + kd_z * v_error[2] + ki_z * m.i_error_z;
     // desired yaw from the setpoint quaternion (0, 0, qz, qw), in degrees
     const float sx = 0.0f, sy = 0.0f, sz = sp.qz, sw = sp.qw;
-    const float desiredYaw = fw_degrees(FwMath<T>::atan2(2.0f * (sw * sz + sx * sy), 1 - 2 * (sy * sy + sz * sz)));
+    // (fp32 product build: cos / sin of that angle are the atan2 arguments themselves, see below)
+    const float dy_s = 2.0f * (sw * sz + sx * sy), dy_c = 1 - 2 * (sy * sy + sz * sz);
     const float x = q[0], y = q[1], z = q[2], w = q[3];
     const float R00 = 1 - 2 * y * y - 2 * z * z, R01 = 2 * x * y - 2 * z * w, R02 = 2 * x * z + 2 * y * w;
     const float R10 = 2 * x * y + 2 * z * w, R11 = 1 - 2 * x * x - 2 * z * z, R12 = 2 * y * z - 2 * x * w;
@@ -98,7 +103,15 @@ __device__ __forceinline__ void fw_mellinger(MelFw& m, const MelSetpoint& sp, fl
     if (M<T>::fast) { const float in = M<float>::rcp(nt); zd0 = tt[0] * in; zd1 = tt[1] * in; zd2 = tt[2] * in; }
     else { zd0 = tt[0] / nt; zd1 = tt[1] / nt; zd2 = tt[2] / nt; }
     float xc0, xc1;
-    FwMath<T>::sincos(fw_radians(desiredYaw), &xc1, &xc0);
+    if (M<T>::fast) {
+        // the yaw-only setpoint quaternion is (0, 0, sin(yaw/2), cos(yaw/2)): (dy_c, dy_s) = (cos yaw, sin yaw) up to
+        // its norm, so the degrees -> radians -> sincos round trip of the firmware reduces to a normalisation
+        const float in = M<float>::frsqrt(dy_c * dy_c + dy_s * dy_s);
+        xc0 = dy_c * in; xc1 = dy_s * in;
+    } else {
+        const float desiredYaw = fw_degrees(FwMath<T>::atan2(dy_s, dy_c));
+        FwMath<T>::sincos(fw_radians(desiredYaw), &xc1, &xc0);
+    }
     const float xc2 = 0.0f;
     float yd0 = zd1 * xc2 - zd2 * xc1, yd1 = zd2 * xc0 - zd0 * xc2, yd2 = zd0 * xc1 - zd1 * xc0;
     const float ny = M<T>::fast ? M<float>::fsqrt(yd0 * yd0 + yd1 * yd1 + yd2 * yd2) : sqrtf(yd0 * yd0 + yd1 * yd1 + yd2 * yd2);
@@ -121,17 +134,17 @@ __device__ __forceinline__ void fw_mellinger(MelFw& m, const MelSetpoint& sp, fl
     m.prev_omega_roll = rate_roll; m.prev_omega_pitch = rate_pitch;
     m.prev_setpoint_omega_roll = fw_radians(sp_rate_deg);
     m.prev_setpoint_omega_pitch = fw_radians(sp_rate_deg);
-    m.i_error_m_x += (-eR0) * dt; m.i_error_m_x = fw_clamp(m.i_error_m_x, -i_range_m_xy, i_range_m_xy);
-    m.i_error_m_y += (-eR1) * dt; m.i_error_m_y = fw_clamp(m.i_error_m_y, -i_range_m_xy, i_range_m_xy);
-    m.i_error_m_z += (-eR2) * dt; m.i_error_m_z = fw_clamp(m.i_error_m_z, -i_range_m_z, i_range_m_z);
+    m.i_error_m_x += (-eR0) * dt; m.i_error_m_x = fw_clampT<T>(m.i_error_m_x, -i_range_m_xy, i_range_m_xy);
+    m.i_error_m_y += (-eR1) * dt; m.i_error_m_y = fw_clampT<T>(m.i_error_m_y, -i_range_m_xy, i_range_m_xy);
+    m.i_error_m_z += (-eR2) * dt; m.i_error_m_z = fw_clampT<T>(m.i_error_m_z, -i_range_m_z, i_range_m_z);
     const float Mx = -kR_xy * eR0 + kw_xy * ew0 + ki_m_xy * m.i_error_m_x + kd_omega_rp * err_d_roll;
     const float My = -kR_xy * eR1 + kw_xy * ew1 + ki_m_xy * m.i_error_m_y + kd_omega_rp * err_d_pitch;
     const float Mz = -kR_z * eR2 + kw_z * ew2 + ki_m_z * m.i_error_m_z;
     m.thrust = massThrust * current_thrust;
     if (m.thrust > 0) {
-        m.roll = (int)(short)fw_clamp(Mx, -32000, 32000);
-        m.pitch = (int)(short)fw_clamp(My, -32000, 32000);
-        m.yaw = (int)(short)fw_clamp(-Mz, -32000, 32000);
+        m.roll = (int)(short)fw_clampT<T>(Mx, -32000, 32000);
+        m.pitch = (int)(short)fw_clampT<T>(My, -32000, 32000);
+        m.yaw = (int)(short)fw_clampT<T>(-Mz, -32000, 32000);
     } else {
         m.roll = m.pitch = m.yaw = 0;
         m.i_error_x = m.i_error_y = m.i_error_z = 0;          // controllerMellingerReset()
@@ -158,7 +171,7 @@ __device__ __forceinline__ void mellinger_tick(const RaceParams<T>& RP, const ui
                                                const T noise4[4])
 {
     const T FIRMWARE_DT = (T)(1.0 / 500), RAD_TO_DEG = (T)(180.0 / 3.14159265358979323846), DEG_TO_RAD = (T)(3.14159265358979323846 / 180.0);
-    const V3<T> rpy = euler_rpy(q);                                              // obs[i, 3:6] (:242)
+    const V3<T> rpy = euler_rpy_loop(q);                                         // obs[i, 3:6] (:242)
     T rates[3], acc_z;
     float qf[4];
     if (M<T>::fast) {
@@ -205,10 +218,10 @@ __device__ __forceinline__ void mellinger_tick(const RaceParams<T>& RP, const ui
         const T th[4] = {t - r + pp + y, t - r - pp - y, t + r - pp + y, t + r + pp - y};
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const T x = M<T>::fast ? clampT(th[k], T(0), T(65535)) * T(60.0 / 65535.0) : clampT(th[k], T(0), T(65535)) / T(65535) * T(60);
+            const T x = M<T>::fast ? M<T>::clamp(th[k], T(0), T(65535)) * T(60.0 / 65535.0) : clampT(th[k], T(0), T(65535)) / T(65535) * T(60);
             const T volts = T(-0.0006239) * (x * x) + T(0.088) * x;
             const T v3 = M<T>::fast ? volts * T(1.0 / 3.0) : volts / T(3);
-            const T pct = v3 < T(1) ? v3 : T(1);
+            const T pct = M<T>::fast ? M<T>::fmin(v3, T(1)) : (v3 < T(1) ? v3 : T(1));
             pwms[k] = pct * T(65535);
         }
     }
@@ -217,16 +230,16 @@ __device__ __forceinline__ void mellinger_tick(const RaceParams<T>& RP, const ui
     T thrust[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        const T c = clampT(pwms[k], T(20000), T(65535));
+        const T c = M<T>::clamp(pwms[k], T(20000), T(65535));
         const T rp = SCALE * c + CONST;
         thrust[k] = KF * (rp * rp);
     }
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         T tk = thrust[3 - k] + noise4[k];                                        // thrust[[3,2,1,0]] + disturbance (:250-253)
-        if (tk < T(0)) tk = T(0);                                                // _thr2pwm (:307-343)
+        if (M<T>::fast) tk = M<T>::fmax(tk, T(0)); else if (tk < T(0)) tk = T(0);  // _thr2pwm (:307-343)
         T pwm = M<T>::fast ? (M<T>::fsqrt(tk * T(1.0 / 3.16e-10)) - CONST) * T(1.0 / 0.2685) : (M<T>::sqrt(tk / T(1) / KF) - CONST) / SCALE;
-        pwm = clampT(pwm, T(20000), T(65535));
+        pwm = M<T>::clamp(pwm, T(20000), T(65535));
         m.rpms[k] = SCALE * pwm + CONST;
     }
 }

@@ -24,6 +24,9 @@ struct KParams {
     // BaseAviary constants (envs/BaseAviary.py:74-128)
     T mass, inv_mass, arm_x, kf, km, jx, jy, jz, jinvx, jinvy, jinvz, gravity, hover_rpm, max_rpm;
     T gnd_eff_coeff, prop_radius, gnd_eff_h_clip, drag_xy, drag_z, dw1, dw2, dw3, speed_limit;
+    // fp32 product build, downwash in base-2 form: term = 2^(dwf_l2c - dxy^2 / (dwf_a dz + dwf_b)^2) / dz^2 with
+    // dwf_l2c = log2(dw1 (prop_radius/4)^2) and (dwf_a, dwf_b) = (dw2, dw3) / sqrt(log2(e) / 2)
+    T dwf_a, dwf_b, dwf_l2c, half_dt, qr4;
     T prop_x[4], prop_y[4], pyb_mass, pyb_jx, pyb_jy, pyb_jz, lin_damp, ang_damp, coll_r, coll_h;
     T dt, ctrl_dt, g;
     T pid_gravity, pid_kf;                // DSLPIDControl's own URDF constants (control/BaseControl.py:35-39)

@@ -28,12 +28,25 @@ template <typename T>
 __device__ __forceinline__ void ground_effect(const KParams<T>& P, const Drone<T>& d, const Mat3<T>& R,
                                               const T rpm2kf[4], T gnd[4])
 {
+    if (M<T>::fast) {
+        // |roll|, |pitch| < pi/2 read off the rotation matrix of this substep: for a unit quaternion the
+        // cosine term of the roll atan2 is m22 and the pitch asin argument is -m20
+        const bool on = R.m22 > T(0) && M<T>::abs(R.m20) < T(0.99999);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            T h = d.p.z + R.m20 * P.prop_x[i] + R.m21 * P.prop_y[i];
+            h = M<T>::fmax(h, P.gnd_eff_h_clip);
+            const T r = P.qr4 * M<T>::rcp(h);
+            gnd[i] = on ? mul_rn(rpm2kf[i] * P.gnd_eff_coeff, r * r) : T(0);
+        }
+        return;
+    }
     const bool on = level_enough(d.q);
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
         T h = d.p.z + R.m20 * P.prop_x[i] + R.m21 * P.prop_y[i];
         h = M<T>::fmax(h, P.gnd_eff_h_clip);
-        const T r = M<T>::fdiv(P.prop_radius, T(4) * h);
+        const T r = P.prop_radius / (T(4) * h);
         gnd[i] = on ? mul_rn(rpm2kf[i] * P.gnd_eff_coeff, r * r) : T(0);
     }
 }
@@ -55,12 +68,37 @@ __device__ __forceinline__ V3<T> drag_force(const KParams<T>& P, const Drone<T>&
 // Downwash from the drones of the same env that fly above this one (:805-811).  The env's M drones
 // sit in MP consecutive lanes of one warp, so the neighbour positions come over warp shuffles.
 // MP > 0: lanes per env known at compile time (unrolled); MP == 0: read from the params.
+//
+// fp32 product build: alpha exp(-(dxy/beta)^2 / 2) = 2^(l2c - dxy^2 / (a dz + b)^2) / dz^2 (constants folded on the
+// host, KParams::dwf_*): two MUFU.RCP and one MUFU.EX2 per pair, no square root, no branch.  The partners come
+// over butterfly shuffles (lane ^ k, k = 1 .. MP-1), which visit every other drone of the env exactly once.
+template <typename T>
+__device__ __forceinline__ T downwash_pair_fast(const KParams<T>& P, T dx, T dy, T dz)
+{
+    const T dxy2 = dx * dx + dy * dy;
+    const T rz = M<T>::rcp(dz);
+    const T ib = M<T>::rcp(P.dwf_a * dz + P.dwf_b);
+    const T e = M<T>::fexp2(P.dwf_l2c - (dxy2 * ib) * ib);
+    const T term = (e * rz) * rz;
+    return (dz > T(0) && dxy2 < T(100)) ? term : T(0);
+}
+
 template <typename T, int MP>
 __device__ __forceinline__ T downwash(const KParams<T>& P, const V3<T>& p, int lane_base, bool valid)
 {
     T fz = T(0);
     const T pz_pub = valid ? p.z : T(-1e30);          // padding lanes never count as "above"
     const int mpad = MP > 0 ? MP : P.Mpad;
+    if (M<T>::fast) {
+#pragma unroll
+        for (int k = 1; k < mpad; ++k) {
+            const T ox = __shfl_xor_sync(0xffffffffu, p.x, k);
+            const T oy = __shfl_xor_sync(0xffffffffu, p.y, k);
+            const T oz = __shfl_xor_sync(0xffffffffu, pz_pub, k);
+            fz -= downwash_pair_fast(P, ox - p.x, oy - p.y, oz - p.z);
+        }
+        return fz;
+    }
 #pragma unroll
     for (int j = 0; j < mpad; ++j) {
         const int src = lane_base + j;
@@ -69,22 +107,13 @@ __device__ __forceinline__ T downwash(const KParams<T>& P, const V3<T>& p, int l
         const T oz = __shfl_sync(0xffffffffu, pz_pub, src);
         const T dz = oz - p.z;
         const T dx = ox - p.x, dy = oy - p.y;
-        if (M<T>::fast) {
-            // alpha = DW1 (R / 4dz)^2, exp(-(dxy / beta)^2 / 2) without the square root; no branch
-            const T dxy2 = dx * dx + dy * dy;
-            const T a = (T(0.25) * P.prop_radius) * M<T>::rcp(dz);
-            const T ib = M<T>::rcp(P.dw2 * dz + P.dw3);
-            const T term = (P.dw1 * (a * a)) * M<T>::fexp(T(-0.5) * (dxy2 * (ib * ib)));
-            fz -= (dz > T(0) && dxy2 < T(100)) ? term : T(0);
-        } else {
-            const T dxy = M<T>::sqrt(dx * dx + dy * dy);
-            if (dz > T(0) && dxy < T(10)) {
-                const T a = P.prop_radius / (T(4) * dz);
-                const T alpha = P.dw1 * (a * a);
-                const T beta = P.dw2 * dz + P.dw3;
-                const T r = dxy / beta;
-                fz -= alpha * M<T>::exp(T(-0.5) * (r * r));
-            }
+        const T dxy = M<T>::sqrt(dx * dx + dy * dy);
+        if (dz > T(0) && dxy < T(10)) {
+            const T a = P.prop_radius / (T(4) * dz);
+            const T alpha = P.dw1 * (a * a);
+            const T beta = P.dw2 * dz + P.dw3;
+            const T r = dxy / beta;
+            fz -= alpha * M<T>::exp(T(-0.5) * (r * r));
         }
     }
     return fz;
@@ -94,7 +123,7 @@ __device__ __forceinline__ T downwash(const KParams<T>& P, const V3<T>& p, int l
 // (downwash), fext world force (drag).
 template <typename T>
 __device__ __forceinline__ void dyn_substep(const KParams<T>& P, Drone<T>& d, const Mat3<T>& R, const T f[4],
-                                            const T tq[4], T extra_z, const V3<T>& fext)
+                                            const T tq[4], T extra_z, const V3<T>& fext, bool last)
 {
     const T thrust = (f[0] + f[1] + f[2] + f[3]) + extra_z;
     const V3<T> fw = {R.m02 * thrust + fext.x, R.m12 * thrust + fext.y, R.m22 * thrust - P.gravity + fext.z};   // :847-848
@@ -121,17 +150,38 @@ __device__ __forceinline__ void dyn_substep(const KParams<T>& P, Drone<T>& d, co
     d.p = {d.p.x + P.dt * d.v.x, d.p.y + P.dt * d.v.y, d.p.z + P.dt * d.v.z};                    // :866
     // _integrateQ (:883-896): q <- [cos(th) I + (2/|w|) sin(th) Lambda/2] q,  th = |w| dt / 2
     const T wn2 = dot(d.rt, d.rt);
-    const T wn = M<T>::fsqrt(wn2);
+    const T px = d.rt.x, qy = d.rt.y, rz = d.rt.z;
+    const Q4<T> q = d.q;
+    if (M<T>::fast) {
+        // cos(th) and sin(th)/|w| = (dt/2) sinc(th) are even in th: polynomials in th^2, no sqrt / division
+        const T z = wn2 * (P.half_dt * P.half_dt);
+        T c, k;
+        if (z <= T(0.6168502750680849)) {
+            M<T>::cos_sinc_sq(z, &c, &k);
+            k *= P.half_dt;
+        } else {
+            const T wn = M<T>::fsqrt(wn2);
+            T s;
+            M<T>::sincos_small(wn * P.half_dt, &s, &c);
+            k = s * M<T>::rcp(wn);
+        }
+        d.q = {c * q.x + k * (rz * q.y - qy * q.z + px * q.w), c * q.y + k * (-rz * q.x + px * q.z + qy * q.w),
+               c * q.z + k * (qy * q.x - px * q.y + rz * q.w), c * q.w + k * (-px * q.x - qy * q.y - rz * q.z)};
+        // the pose round trip through Bullet only renormalises and fixes the sign: _integrateQ is linear in q and
+        // every consumer inside the loop normalises by |q|^2, so the product build applies it once per control
+        // step (step kernel epilogue); the world rates are needed after the last substep only
+        if (last) d.w = mul(R, d.rt);
+        return;
+    }
+    const T wn = M<T>::sqrt(wn2);
     if (!(M<T>::abs(wn) <= T(1e-8))) {
         T s, c;
-        M<T>::sincos_small(wn * P.dt / T(2), &s, &c);
-        const T k = M<T>::fast ? s * M<T>::rcp(wn) : T(2) / wn * s * T(0.5);
-        const T px = d.rt.x, qy = d.rt.y, rz = d.rt.z;
-        const Q4<T> q = d.q;
+        M<T>::sincos(wn * P.dt / T(2), &s, &c);
+        const T k = T(2) / wn * s * T(0.5);
         d.q = {c * q.x + k * (rz * q.y - qy * q.z + px * q.w), c * q.y + k * (-rz * q.x + px * q.z + qy * q.w),
                c * q.z + k * (qy * q.x - px * q.y + rz * q.w), c * q.w + k * (-px * q.x - qy * q.y - rz * q.z)};
     }
-    d.q = canon_quat_loop(d.q);
+    d.q = canon_quat(d.q);
     d.w = mul(R, d.rt);                                                          // :875-879 (pre-update R)
 }
 
@@ -163,22 +213,32 @@ __device__ __forceinline__ void pyb_substep(const KParams<T>& P, int phy, Drone<
     d.w = {d.w.x + P.dt * al_w.x, d.w.y + P.dt * al_w.y, d.w.z + P.dt * al_w.z};
     d.p = {d.p.x + P.dt * d.v.x, d.p.y + P.dt * d.v.y, d.p.z + P.dt * d.v.z};
     // exponential map (btMultiBody::stepPositionsMultiDof)
-    T ang = M<T>::fsqrt(dot(d.w, d.w));
-    if (ang * P.dt > T(0.7853981633974483)) ang = T(0.7853981633974483) / P.dt;
+    const T w2 = dot(d.w, d.w);
     T k, cw;
-    if (ang < T(0.001)) {
-        k = T(0.5) * P.dt - (P.dt * P.dt * P.dt) * T(0.020833333333) * ang * ang;
-        cw = M<T>::fast ? T(1) - T(0.125) * (ang * P.dt) * (ang * P.dt) : M<T>::cos(ang * P.dt * T(0.5));
+    if (M<T>::fast && w2 * (P.dt * P.dt) <= T(0.6168502750680849)) {
+        // |w| dt <= pi/4 (no clamp): cos(|w| dt/2) and sin(|w| dt/2)/|w| as polynomials in (|w| dt/2)^2, which also
+        // covers Bullet's own Taylor branch below 1e-3 rad/s
+        M<T>::cos_sinc_sq(w2 * (P.half_dt * P.half_dt), &cw, &k);
+        k *= P.half_dt;
     } else {
-        T s;
-        M<T>::sincos_small(T(0.5) * ang * P.dt, &s, &cw);
-        k = M<T>::fdiv(s, ang);
+        T ang = M<T>::fsqrt(w2);
+        if (ang * P.dt > T(0.7853981633974483)) ang = T(0.7853981633974483) / P.dt;
+        if (ang < T(0.001)) {
+            k = T(0.5) * P.dt - (P.dt * P.dt * P.dt) * T(0.020833333333) * ang * ang;
+            cw = M<T>::cos(ang * P.dt * T(0.5));
+        } else {
+            T s;
+            M<T>::sincos_small(T(0.5) * ang * P.dt, &s, &cw);
+            k = M<T>::fdiv(s, ang);
+        }
     }
     const V3<T> ax = {d.w.x * k, d.w.y * k, d.w.z * k};
     const Q4<T> q = d.q;
     d.q = {cw * q.x + ax.x * q.w + ax.y * q.z - ax.z * q.y, cw * q.y + ax.y * q.w + ax.z * q.x - ax.x * q.z,
            cw * q.z + ax.z * q.w + ax.x * q.y - ax.y * q.x, cw * q.w - ax.x * q.x - ax.y * q.y - ax.z * q.z};
-    d.q = canon_quat_loop(d.q);
+    // Bullet renormalises every step; the product build does it once per control step (kernel epilogue): the
+    // update is linear in q and rotmat_loop divides by |q|^2
+    if (!M<T>::fast) d.q = canon_quat(d.q);
     if (phy & ADRP_PHY_GROUND) {
         // declared plane response: project the lowest point of the collision cylinder back to z = 0,
         // cancel the approaching normal velocity, Coulomb friction mu = 0.5 on the tangential part

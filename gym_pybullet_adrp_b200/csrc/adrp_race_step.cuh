@@ -50,7 +50,8 @@ race_reset_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ 
 }
 
 // MultiRaceAviary.step (:171-270).  noise: NULL or (N, M, S, 7) = [wind force xyz (N), motor thrust noise x4 (N)].
-template <typename T>
+// MP: lanes per env at compile time (unrolled neighbour loops), 0 = read from the params.
+template <typename T, int MP>
 __global__ void __launch_bounds__(kBlock)
 race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ RaceParams<T> RP, const KBuffers<T> b,
                  const RaceBuffers<T> rb, const T* __restrict__ action, const T* __restrict__ noise, T* __restrict__ obs,
@@ -59,12 +60,13 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T* trk = reinterpret_cast<T*>(smem_raw);
-    const long long t = (long long)P.env_begin * P.Mpad + (long long)blockIdx.x * kBlock + threadIdx.x;
+    const int mpad = MP > 0 ? MP : P.Mpad;
+    const long long t = (long long)P.env_begin * mpad + (long long)blockIdx.x * kBlock + threadIdx.x;
     const int lane = threadIdx.x & 31;
-    const int i = (int)(t & (P.Mpad - 1));
-    const long long env = t / P.Mpad;
+    const int i = (int)(t & (mpad - 1));
+    const long long env = t / mpad;
     const int lane_base = lane - i;
-    const int EPB = kBlock / P.Mpad, e = threadIdx.x / P.Mpad;
+    const int EPB = kBlock / mpad, e = threadIdx.x / mpad;
     const bool valid = env < P.env_end && i < P.M;
     const long long D = P.Dpad;
     const int phy = P.physics;
@@ -145,9 +147,9 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
         V3<T> fext = {T(0), T(0), T(0)};
         if (phy & ADRP_PHY_DRAG) fext = drag_force(P, d);      // prev_rpms = state row 16:20
         T dw = T(0);
-        if (phy & ADRP_PHY_DW) dw = downwash<T, 0>(P, d.p, lane_base, valid);
+        if (phy & ADRP_PHY_DW) dw = downwash<T, MP>(P, d.p, lane_base, valid);
         if (phy & ADRP_PHY_DYN) {
-            dyn_substep(P, d, R, f, tq, dw, fext);
+            dyn_substep(P, d, R, f, tq, dw, fext, s == P.S - 1);
         } else {
             const T fz = dw + f[0] + f[1] + f[2] + f[3];
             const V3<T> tb = {mul_rn(P.prop_y[0], f[0]) + mul_rn(P.prop_y[1], f[1]) + mul_rn(P.prop_y[2], f[2]) + mul_rn(P.prop_y[3], f[3]),
@@ -166,6 +168,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
             mellinger_tick(RP, rb.lut, m, sp, d.p, d.q, d.v, nz + 3);                    // rpms[i] = recv() (:254)
         }
     }
+    if (M<T>::fast) d.q = canon_quat_loop(d.q);             // once per control step in the product build (adrp_physics.cuh)
     __syncthreads();                                                                     // shared track is complete
 
     // ---- _gate_progress (:471-506): 7 vertical rays through the drone's current gate; the gate counts as
@@ -186,7 +189,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
         int best_id[7];
 #pragma unroll
         for (int k = 0; k < 7; ++k) { best[k] = T(-1); best_id[k] = -1; }
-        for (int j = 0; j < P.Mpad; ++j) {
+        for (int j = 0; j < mpad; ++j) {
             const int src = lane_base + j;
             const V3<T> cj = {__shfl_sync(0xffffffffu, d.p.x, src), __shfl_sync(0xffffffffu, d.p.y, src), __shfl_sync(0xffffffffu, d.p.z, src)};
             const V3<T> aj = {__shfl_sync(0xffffffffu, axis.x, src), __shfl_sync(0xffffffffu, axis.y, src), __shfl_sync(0xffffffffu, axis.z, src)};
@@ -228,7 +231,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
         }
         crashed = crashed || (d.p.z - hz < RP.contact_margin);                           // plane
         if (RP.compete) {                                                                // drones collide with each other (:153-154)
-            for (int j = 0; j < P.Mpad; ++j) {
+            for (int j = 0; j < mpad; ++j) {
                 const int src = lane_base + j;
                 const T ox = __shfl_sync(0xffffffffu, d.p.x, src), oy = __shfl_sync(0xffffffffu, d.p.y, src);
                 const T oz = __shfl_sync(0xffffffffu, d.p.z, src), ohz = __shfl_sync(0xffffffffu, hz, src);
@@ -243,7 +246,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
     if (fl) latch |= ADRP_FLAG_ELIMINATED;
     if (m.error) fl |= ADRP_FLAG_TUMBLE_STOP;
     const int not_done = valid && !(latch & (ADRP_FLAG_ELIMINATED | ADRP_FLAG_FINISHED));
-    const int term = group_or(not_done, P.Mpad) == 0;
+    const int term = group_or(not_done, mpad) == 0;
     const int trunc = counter >= P.trunc_steps;                                          // step_counter / PYB_FREQ > episode_len_sec (:709)
     const bool done = P.auto_reset && (term || trunc);
     if (valid && drone_flags) drone_flags[od] = (uint8_t)(fl | latch);

@@ -153,7 +153,7 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
         T dw = T(0);
         if (phy & ADRP_PHY_DW) dw = downwash<T, MP>(P, d.p, lane_base, valid);
         if (phy & ADRP_PHY_DYN) {
-            dyn_substep(P, d, R, f, tq, dw, fext);
+            dyn_substep(P, d, R, f, tq, dw, fext, s == P.S - 1);
         } else {
             const T fz = (f[0] + f[1] + f[2] + f[3]) + dw;
             const V3<T> tb = {mul_rn(P.prop_y[0], f[0]) + mul_rn(P.prop_y[1], f[1]) + mul_rn(P.prop_y[2], f[2]) + mul_rn(P.prop_y[3], f[3]),
@@ -164,6 +164,7 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
 #pragma unroll
         for (int k = 0; k < 4; ++k) d.last_rpm[k] = rpm[k];                      // :376
     }
+    if (M<T>::fast) d.q = canon_quat_loop(d.q);          // once per control step in the product build (adrp_physics.cuh)
 
     // ---- observation (CtrlAviary.py:106-117; BaseRLAviary.py:284-322)
     const V3<T> rpy = euler_rpy(d.q);
