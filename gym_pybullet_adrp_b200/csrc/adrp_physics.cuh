@@ -83,12 +83,49 @@ __device__ __forceinline__ T downwash_pair_fast(const KParams<T>& P, T dx, T dy,
     return (dz > T(0) && dxy2 < T(100)) ? term : T(0);
 }
 
+// Both directions of one pair from a single evaluation (the formula depends on |dz| and dxy only): `mine` is the
+// force on this drone when the partner flies above it, `theirs` the force on the partner when it flies below.
+template <typename T>
+__device__ __forceinline__ void downwash_pair_sym(const KParams<T>& P, T dx, T dy, T dz, T& mine, T& theirs)
+{
+    const T dxy2 = dx * dx + dy * dy;
+    const T az = M<T>::abs(dz);
+    const T rz = M<T>::rcp(az);
+    const T ib = M<T>::rcp(P.dwf_a * az + P.dwf_b);
+    const T e = M<T>::fexp2(P.dwf_l2c - (dxy2 * ib) * ib);
+    const T term = (e * rz) * rz;
+    const bool near = dxy2 < T(100);
+    mine = (near && dz > T(0)) ? term : T(0);
+    theirs = (near && dz < T(0)) ? term : T(0);
+}
+
 template <typename T, int MP>
 __device__ __forceinline__ T downwash(const KParams<T>& P, const V3<T>& p, int lane_base, bool valid)
 {
     T fz = T(0);
     const T pz_pub = valid ? p.z : T(-1e30);          // padding lanes never count as "above"
     const int mpad = MP > 0 ? MP : P.Mpad;
+    if (M<T>::fast && MP >= 4) {
+        // every unordered pair once: lane i evaluates (i, i+k mod MP) for k = 1 .. MP/2-1 and hands the partner's
+        // share back over one more shuffle; the antipodal pairs (k = MP/2) are evaluated from both ends
+        const int i = (threadIdx.x & 31) - lane_base;
+#pragma unroll
+        for (int k = 1; k < MP / 2; ++k) {
+            const int fwd = lane_base + ((i + k) & (MP - 1)), back = lane_base + ((i - k) & (MP - 1));
+            const T ox = __shfl_sync(0xffffffffu, p.x, fwd);
+            const T oy = __shfl_sync(0xffffffffu, p.y, fwd);
+            const T oz = __shfl_sync(0xffffffffu, pz_pub, fwd);
+            T mine, theirs;
+            downwash_pair_sym(P, ox - p.x, oy - p.y, oz - pz_pub, mine, theirs);
+            fz -= mine;
+            fz -= __shfl_sync(0xffffffffu, theirs, back);
+        }
+        const T ox = __shfl_xor_sync(0xffffffffu, p.x, MP / 2);
+        const T oy = __shfl_xor_sync(0xffffffffu, p.y, MP / 2);
+        const T oz = __shfl_xor_sync(0xffffffffu, pz_pub, MP / 2);
+        fz -= downwash_pair_fast(P, ox - p.x, oy - p.y, oz - pz_pub);
+        return fz;
+    }
     if (M<T>::fast) {
 #pragma unroll
         for (int k = 1; k < mpad; ++k) {
@@ -170,7 +207,7 @@ __device__ __forceinline__ void dyn_substep(const KParams<T>& P, Drone<T>& d, co
         // the pose round trip through Bullet only renormalises and fixes the sign: _integrateQ is linear in q and
         // every consumer inside the loop normalises by |q|^2, so the product build applies it once per control
         // step (step kernel epilogue); the world rates are needed after the last substep only
-        if (last) d.w = mul(R, d.rt);
+        if (last) d.w = mul(rotmat_loop(q), d.rt);        // (the loop itself reads the third row / column of R only)
         return;
     }
     const T wn = M<T>::sqrt(wn2);
