@@ -150,11 +150,13 @@ def algorithmic_flops_per_substep(wl):
 
 def ncu_traffic_bytes(wl, n_envs):
     """dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the step kernel, from the committed
-    `ncu --set full` capture of this workload (profiles/r01b_ncu_<wl>_metrics.csv); None if there is none or the
-    capture was taken at another size."""
-    path = os.path.join(ROOT, "profiles", f"r01b_ncu_{wl}_metrics.csv")
-    if n_envs != WORKLOADS[wl][0] or not os.path.exists(path):
+    `ncu --set full` capture of this workload (the newest profiles/r*_ncu_<wl>_metrics.csv); None if there is none
+    or the capture was taken at another size."""
+    import glob
+    found = sorted(glob.glob(os.path.join(ROOT, "profiles", f"r*_ncu_{wl}_metrics.csv")))
+    if n_envs != WORKLOADS[wl][0] or not found:
         return None
+    path = found[-1]
     import csv
     scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     total = 0.0

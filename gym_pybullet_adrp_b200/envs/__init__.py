@@ -5,5 +5,6 @@ from .CtrlAviary import CtrlAviary
 from .HoverAviary import HoverAviary
 from .MultiHoverAviary import MultiHoverAviary
 from .MultiRaceAviary import MultiRaceAviary
+from .VelocityAviary import VelocityAviary
 
-__all__ = ["BaseAviary", "BaseRLAviary", "CtrlAviary", "HoverAviary", "MultiHoverAviary", "MultiRaceAviary"]
+__all__ = ["BaseAviary", "BaseRLAviary", "CtrlAviary", "HoverAviary", "MultiHoverAviary", "MultiRaceAviary", "VelocityAviary"]

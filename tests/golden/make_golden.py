@@ -32,6 +32,7 @@ import numpy as np  # noqa: E402
 from gym_pybullet_adrp.envs.CtrlAviary import CtrlAviary  # noqa: E402
 from gym_pybullet_adrp.envs.HoverAviary import HoverAviary  # noqa: E402
 from gym_pybullet_adrp.envs.MultiHoverAviary import MultiHoverAviary  # noqa: E402
+from gym_pybullet_adrp.envs.VelocityAviary import VelocityAviary  # noqa: E402
 from gym_pybullet_adrp.control.DSLPIDControl import DSLPIDControl  # noqa: E402
 from gym_pybullet_adrp.utils.enums import ActionType, DroneModel, ObservationType, Physics  # noqa: E402
 
@@ -69,6 +70,9 @@ def rl_case(name, cls, M, physics, act, pyb, ctrl, steps, seed, scale=1.0):
     obs0, _ = env.reset()
     A = env.action_space.shape[1]
     actions = (scale * rng.uniform(-1, 1, size=(steps, M, A))).astype(np.float32)
+    if act == ActionType.VEL:
+        actions[:, :, 2] = rng.uniform(-1, 1, size=(steps, M)).astype(np.float32)    # mostly vertical
+        actions[:, :, 3] = rng.uniform(0, 1, size=(steps, M)).astype(np.float32)
     if act in (ActionType.PID,):
         # vertical targets only: the one stable DSLPID closed loop in this fork
         actions[:, :, 0:2] = np.asarray(env.INIT_XYZS)[None, :, 0:2]
@@ -85,6 +89,29 @@ def rl_case(name, cls, M, physics, act, pyb, ctrl, steps, seed, scale=1.0):
     env.close()
     _save(name, meta, obs0=np.asarray(obs0, dtype=np.float64), actions=actions, obs=obs, reward=rew,
           terminated=term, truncated=trunc)
+
+
+def vel_case(name, physics, M, pyb, ctrl, steps, seed, xyz=None):
+    """VelocityAviary (VelocityAviary.py:129-170): velocity commands through DSLPID inside the env step.
+    Mostly vertical commands (the lateral DSLPID loop of this fork diverges), one zero-norm row."""
+    rng = np.random.default_rng(seed)
+    env = VelocityAviary(drone_model=DroneModel.CF2X, num_drones=M, physics=physics, pyb_freq=pyb, ctrl_freq=ctrl,
+                         initial_xyzs=xyz, gui=False, user_debug_gui=False)
+    obs0, _ = env.reset()
+    actions = np.zeros((steps, M, 4))
+    actions[:, :, 2] = rng.uniform(-1, 1, size=(steps, M))
+    actions[:, :, 0:2] = 0.02 * rng.uniform(-1, 1, size=(steps, M, 2))
+    actions[:, :, 3] = rng.uniform(0, 1, size=(steps, M))
+    actions[steps // 3, 0, :3] = 0.0                                    # |v| == 0 branch (:148-151)
+    obs = np.zeros((steps, M, 20))
+    for k in range(steps):
+        o, r, te, tr, _ = env.step(actions[k])
+        obs[k] = o
+    meta = dict(env="velocity", model="CF2X", physics=physics.name, M=M, pyb_freq=pyb, ctrl_freq=ctrl, steps=steps,
+                init_xyz=np.asarray(env.INIT_XYZS).tolist(), init_rpy=np.asarray(env.INIT_RPYS).tolist(),
+                speed_limit=env.SPEED_LIMIT)
+    env.close()
+    _save(name, meta, obs0=np.asarray(obs0, dtype=np.float64), actions=actions, obs=obs)
 
 
 def pid_case(name, physics, steps):
@@ -134,6 +161,12 @@ def dslpid_unit_case(name, seed, n):
 
 def main():
     X, Pm, Rc = DroneModel.CF2X, DroneModel.CF2P, DroneModel.RACE
+    if len(sys.argv) > 1 and sys.argv[1] == "--new":
+        # cases added after the first freeze: generate only these, the earlier .npz files stay untouched
+        vel_case("vel_pyb_m2", Physics.PYB, 2, 240, 48, 60, 51, xyz=np.array([[0, 0, 0.5], [0.6, 0, 0.8]]))
+        vel_case("vel_dyn_m1", Physics.DYN, 1, 240, 240, 120, 52, xyz=np.array([[0, 0, 0.4]]))
+        rl_case("hover_pyb_vel", HoverAviary, 1, Physics.PYB, ActionType.VEL, 240, 30, 30, 53, scale=0.05)
+        return
     # per-substep pins (S = 1) and 1 s flights (S = 8 / 5)
     ctrl_case("ctrl_dyn_cf2x_s1", X, Physics.DYN, 1, 240, 240, 240, 11, 0.03)
     ctrl_case("ctrl_dyn_cf2x_s8_m3", X, Physics.DYN, 3, 240, 30, 30, 12, 0.03)

@@ -19,8 +19,11 @@ CTRL_CASES = ["ctrl_dyn_cf2x_s1", "ctrl_dyn_cf2x_s8_m3", "ctrl_dyn_cf2p_s8", "ct
 RL_CASES = ["hover_pyb_rpm", "hover_dyn_one_d_rpm", "hover_dyn_pid", "hover_pyb_one_d_pid",
             "multihover_pyb_rpm_m2", "hover_pyb_rpm_long"]
 PID_CASES = ["pid_dyn_c1", "pid_pyb_c1"]
+VEL_CASES = ["vel_pyb_m2", "vel_dyn_m1"]                 # VelocityAviary (ActionType.VEL through the env's own DSLPID)
+RL_VEL_CASES = ["hover_pyb_vel"]                         # BaseRLAviary ActionType.VEL (:208-223)
 
-ACT = {"RPM": _abi.ACT_RPM, "ONE_D_RPM": _abi.ACT_ONE_D_RPM, "PID": _abi.ACT_PID, "ONE_D_PID": _abi.ACT_ONE_D_PID}
+ACT = {"RPM": _abi.ACT_RPM, "ONE_D_RPM": _abi.ACT_ONE_D_RPM, "PID": _abi.ACT_PID, "ONE_D_PID": _abi.ACT_ONE_D_PID,
+       "VEL": _abi.ACT_VEL}
 
 
 def load(name):
@@ -36,6 +39,8 @@ def config_for(meta, precision=_abi.F64, num_envs=1, **over):
               precision=precision, initial_xyzs=meta["init_xyz"], initial_rpys=meta.get("init_rpy"))
     if kind == "ctrl":
         kw.update(action_type=_abi.ACT_RPM_RAW, env_kind=_abi.ENV_CTRL)
+    elif kind == "velocity":
+        kw.update(action_type=_abi.ACT_VEL, env_kind=_abi.ENV_CTRL)
     elif kind == "ctrl+dslpid":
         kw.update(action_type=_abi.ACT_PID_FULL, env_kind=_abi.ENV_CTRL)
     else:

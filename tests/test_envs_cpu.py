@@ -36,6 +36,17 @@ def test_constructor_errors_like_reference():
         HoverAviary(obs=ObservationType.RGB)
 
 
+def test_velocity_aviary_surface():
+    """VelocityAviary.py:87-104: speed limit and spaces, no GPU needed."""
+    from gym_pybullet_adrp_b200.envs import VelocityAviary
+    env = VelocityAviary(num_drones=3)
+    assert abs(env.SPEED_LIMIT - 0.03 * 30 * (1000 / 3600)) < 1e-15          # cf2x max_speed_kmh = 30
+    assert env.action_space.shape == (3, 4) and env.action_space.low[0].tolist() == [-1, -1, -1, 0]
+    assert env.observation_space.shape == (3, 20)
+    with pytest.raises(ValueError, match="DSLPIDControl"):
+        VelocityAviary(drone_model=DroneModel.RACE)
+
+
 def test_rl_spaces():
     e = HoverAviary()
     assert (e.CTRL_FREQ, e.PYB_FREQ, e.ACTION_BUFFER_SIZE, e.EPISODE_LEN_SEC) == (30, 240, 15, 8)

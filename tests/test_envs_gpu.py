@@ -5,7 +5,7 @@ import pytest
 
 from gym_pybullet_adrp_b200 import configs
 from gym_pybullet_adrp_b200.control import DSLPIDControl
-from gym_pybullet_adrp_b200.envs import CtrlAviary, HoverAviary, MultiHoverAviary, MultiRaceAviary
+from gym_pybullet_adrp_b200.envs import CtrlAviary, HoverAviary, MultiHoverAviary, MultiRaceAviary, VelocityAviary
 from gym_pybullet_adrp_b200.utils.enums import ActionType, DroneModel, Physics, RaceMode
 from tests import golden_cases as gc
 
@@ -50,6 +50,22 @@ def test_hover_aviary_matches_reference_run(name):
         np.testing.assert_array_equal(obs[:, 12:], z["obs"][k][:, 12:].astype(np.float32))
         assert abs(rew - z["reward"][k]) < 1e-9 * max(1, abs(z["reward"][k]))
         assert te == bool(z["terminated"][k]) and tr == bool(z["truncated"][k])
+    env.close()
+
+
+def test_velocity_aviary_matches_reference_run():
+    """VelocityAviary.step: (vx, vy, vz, speed fraction) per drone -> DSLPID -> physics, all in one launch."""
+    meta, z = gc.load("vel_pyb_m2")
+    env = VelocityAviary(num_drones=meta["M"], initial_xyzs=np.array(meta["init_xyz"]), physics=Physics[meta["physics"]],
+                         pyb_freq=meta["pyb_freq"], ctrl_freq=meta["ctrl_freq"], precision="fp64")
+    assert abs(env.SPEED_LIMIT - meta["speed_limit"]) < 1e-15
+    assert env.action_space.shape == (meta["M"], 4) and env.observation_space.shape == (meta["M"], 20)
+    obs, _ = env.reset()
+    assert gc.rel_err(obs, z["obs0"]) < 1e-9
+    for k in range(meta["steps"]):
+        obs, rew, te, tr, info = env.step(z["actions"][k])
+        assert gc.rel_err(obs, z["obs"][k]) < 1e-9, k
+        assert rew == -1 and te is False and tr is False and info == {"answer": 42}
     env.close()
 
 
