@@ -11,7 +11,7 @@ import math
 from .assets import DroneParams, drone_params
 from .utils.enums import ActionType, DroneModel, Physics, RaceMode
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 MAX_DRONES, MAX_GATES, MAX_OBSTACLES, STATE_DIM = 32, 8, 8, 20
 
 F32, F64 = 0, 1
@@ -19,6 +19,7 @@ PHY_DYN, PHY_GND, PHY_DRAG, PHY_DW, PHY_GROUND = 1, 2, 4, 8, 16
 ACT_RPM_RAW, ACT_RPM, ACT_ONE_D_RPM, ACT_PID, ACT_ONE_D_PID, ACT_VEL, ACT_MEL, ACT_PID_FULL = range(8)
 ENV_CTRL, ENV_HOVER, ENV_MULTIHOVER, ENV_RACE = range(4)
 FLAG_ELIMINATED, FLAG_FINISHED, FLAG_CRASHED, FLAG_OUT_OF_BOUNDS, FLAG_UNSTABLE, FLAG_TUMBLE_STOP = 1, 2, 4, 8, 16, 32
+WRAP_OBS, WRAP_REWARD = 1, 2                           # adrp_config.wrappers (gym_pybullet_adrp/utils/wrapper.py fused)
 
 MODEL_ID = {DroneModel.CF2X: 0, DroneModel.CF2P: 1, DroneModel.RACE: 2}
 ACTION_DIM = {ACT_RPM_RAW: 4, ACT_RPM: 4, ACT_ONE_D_RPM: 1, ACT_PID: 3, ACT_ONE_D_PID: 1, ACT_VEL: 4, ACT_MEL: 4,
@@ -68,7 +69,7 @@ class ConfigC(C.Structure):
     _fields_ = [("abi_version", i32), ("device", i32), ("precision", i32), ("num_envs", i32),
                 ("drones_per_env", i32), ("drone_model", i32), ("physics", i32), ("pyb_freq", i32),
                 ("ctrl_freq", i32), ("action_type", i32), ("env_kind", i32), ("race_mode", i32),
-                ("auto_reset", i32), ("dslpid_model", i32), ("bug_compat", C.c_uint32), ("reserved0", i32),
+                ("auto_reset", i32), ("dslpid_model", i32), ("bug_compat", C.c_uint32), ("wrappers", i32),
                 ("g", d), ("episode_len_sec", d), ("mel_mass", d), ("seed", C.c_uint64), ("env_offset", C.c_uint64),
                 ("init_xyz", (d * 3) * MAX_DRONES), ("init_rpy", (d * 3) * MAX_DRONES),
                 ("init_vel", (d * 3) * MAX_DRONES), ("init_pqr", (d * 3) * MAX_DRONES),
@@ -145,7 +146,7 @@ def make_config(*, num_envs, num_drones=1, drone_model=DroneModel.CF2X, physics=
 
 def make_race_config(race_config, *, num_envs, num_drones=2, drone_model=DroneModel.CF2X, physics=Physics.PYB,
                      pyb_freq=500, ctrl_freq=25, racemode=RaceMode.COMPARE, precision=F32, device=0, seed=None,
-                     env_offset=0, auto_reset=False, physics_mask=None, mel_mass=0.027) -> ConfigC:
+                     env_offset=0, auto_reset=False, physics_mask=None, mel_mass=0.027, wrappers=0) -> ConfigC:
     """adrp_config for MultiRaceAviary(race_config, ...) (envs/MultiRaceAviary.py:31-123)."""
     rc = race_config
     drones = list(rc["init_states"].keys())[:num_drones]
@@ -162,6 +163,7 @@ def make_race_config(race_config, *, num_envs, num_drones=2, drone_model=DroneMo
                     env_offset=env_offset, physics_mask=physics_mask,
                     body_model="cf2x",            # Bullet mass / inertia from the legacy urdf (:409-416)
                     mel_mass=mel_mass)
+    c.wrappers = int(wrappers)
     t = c.track
     gates, obst = rc["gates"], rc["obstacles"]
     if len(gates) > MAX_GATES or len(obst) > MAX_OBSTACLES:

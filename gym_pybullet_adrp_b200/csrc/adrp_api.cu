@@ -182,6 +182,7 @@ void derive_race(const adrp_config& c, const KParams<T>& P, RaceParams<T>& R)
     R.TF = kGateFields * R.G + kObstFields * R.NO;
     R.R = 3 * R.G + 2 * R.NO + 10 * c.drones_per_env;
     R.compete = c.race_mode == ADRP_RACE_COMPETE;
+    R.wrappers = c.wrappers;
     R.rnd_track = r.random_gates_obstacles; R.rnd_state = r.random_drone_state;
     R.rnd_inertia = r.random_drone_inertia; R.disturbances = r.disturbances;
     R.seed_lo = (unsigned)(c.seed & 0xffffffffu); R.seed_hi = (unsigned)(c.seed >> 32);
@@ -237,6 +238,10 @@ int alloc_buffers(Handle<T>* h)
         CUDA_TRY(h, cudaMalloc(&rb.gate_latch, sizeof(int32_t) * D));
         CUDA_TRY(h, cudaMalloc(&rb.episode, sizeof(int32_t) * P.N));
         CUDA_TRY(h, cudaMemset(rb.episode, 0, sizeof(int32_t) * P.N));
+        CUDA_TRY(h, cudaMalloc(&rb.shape_gate, sizeof(int32_t) * P.N));
+        CUDA_TRY(h, cudaMalloc(&rb.shape_vec, sizeof(T) * 6 * P.N));
+        CUDA_TRY(h, cudaMemset(rb.shape_gate, 0xFF, sizeof(int32_t) * P.N));
+        CUDA_TRY(h, cudaMemset(rb.shape_vec, 0, sizeof(T) * 6 * P.N));
         CUDA_TRY(h, cudaMemset(rb.mel_t, 0, sizeof(T) * MT_COUNT * D));
         CUDA_TRY(h, cudaMemset(rb.mel_f, 0, sizeof(float) * MF_COUNT * D));
         CUDA_TRY(h, cudaMemset(rb.mel_i, 0, sizeof(int32_t) * MI_COUNT * D));
@@ -263,7 +268,8 @@ void free_buffers(Handle<T>* h)
     if (h->race) {
         RaceBuffers<T>& rb = h->RB;
         cudaFree(rb.track); cudaFree(rb.body); cudaFree(rb.mel_t); cudaFree(rb.mel_f); cudaFree(rb.mel_i);
-        cudaFree(rb.gate_latch); cudaFree(rb.episode); cudaFree(const_cast<uint32_t*>(rb.lut));
+        cudaFree(rb.gate_latch); cudaFree(rb.episode); cudaFree(rb.shape_gate); cudaFree(rb.shape_vec);
+        cudaFree(const_cast<uint32_t*>(rb.lut));
     }
 }
 
@@ -331,6 +337,8 @@ int validate(const adrp_config* c)
     if (c->precision != ADRP_F32 && c->precision != ADRP_F64) { g_create_error = "unknown precision"; return ADRP_EINVAL; }
     if (action_dim(c->action_type) == 0) { g_create_error = "unknown action_type"; return ADRP_EINVAL; }
     if ((c->env_kind == ADRP_ENV_RACE) != (c->action_type == ADRP_ACT_MEL)) { g_create_error = "ADRP_ACT_MEL (Mellinger full-state setpoints) is the race env's action type, and its only one"; return ADRP_EINVAL; }
+    if (c->wrappers & ~(ADRP_WRAP_OBS | ADRP_WRAP_REWARD)) { g_create_error = "unknown bit in wrappers"; return ADRP_EINVAL; }
+    if (c->wrappers && c->env_kind != ADRP_ENV_RACE) { g_create_error = "wrappers (utils/wrapper.py) apply to the race env"; return ADRP_EINVAL; }
     if (c->env_kind == ADRP_ENV_RACE && (c->track.num_gates < 0 || c->track.num_gates > ADRP_MAX_GATES || c->track.num_obstacles < 0 || c->track.num_obstacles > ADRP_MAX_OBSTACLES)) { g_create_error = "too many gates / obstacles"; return ADRP_EINVAL; }
     if (c->env_kind == ADRP_ENV_HOVER && c->drones_per_env != 1) { g_create_error = "HoverAviary is single-drone"; return ADRP_EINVAL; }
     return ADRP_OK;

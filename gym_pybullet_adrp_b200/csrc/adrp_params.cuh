@@ -44,6 +44,7 @@ struct RaceParams {
     int TF;                               // track fields per env = kGateFields*G + kObstFields*NO
     int R;                                // uniform draws per env reset = 3G + 2NO + 10M
     int compete;                          // RaceMode.COMPETE
+    int wrappers;                         // ADRP_WRAP_* (utils/wrapper.py fused into the step)
     int rnd_track, rnd_state, rnd_inertia, disturbances;
     int lut_ticks;                        // length (bits) of the sub-rate schedule LUT
     unsigned seed_lo, seed_hi;            // Philox key
@@ -75,6 +76,8 @@ struct RaceBuffers {
     int32_t* mel_i;         // [MI_COUNT][Dpad]
     int32_t* gate_latch;    // [Dpad]       current_gate | latch<<16
     int32_t* episode;       // [N]          resets so far (Philox counter word)
+    int32_t* shape_gate;    // [N]          RewardWrapper.current_gate_id, -1 = read it on the next step (wrapper.py:96-101)
+    T* shape_vec;           // [6][N]       RewardWrapper.current_target xyz, previous_pos xyz
     const uint32_t* lut;    // [lut_ticks/32] bit t: (t/500 - (t-1)/500 > 0.002) in float64 (MellingerControl.py:395-411)
 };
 

@@ -30,7 +30,7 @@ race_reset_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ 
         store_mel(rb, P.Dpad, t, m);
         store_body(rb, P.Dpad, t, body);
         rb.gate_latch[t] = 0;
-        if (i == 0) { rb.episode[env] = episode + 1; b.step_counter[env] = 0; }
+        if (i == 0) { rb.episode[env] = episode + 1; b.step_counter[env] = 0; rb.shape_gate[env] = -1; }
     }
     if (!obs) return;
     __syncthreads();                                           // track written above is read back below
@@ -104,10 +104,35 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
         const T* a = action + od * 4;
         sp.pos[0] = (float)a[0]; sp.pos[1] = (float)a[1]; sp.pos[2] = (float)a[2];
         T sy, cy;
-        M<T>::sincos(a[3] / T(2), &sy, &cy);                  // utils.get_quaternion_from_euler(0, 0, yaw)
+        const T yaw = (RP.wrappers & ADRP_WRAP_OBS) ? T(0) : a[3];   // DroneObservationWrapper.step (wrapper.py:52-57)
+        M<T>::sincos(yaw / T(2), &sy, &cy);                   // utils.get_quaternion_from_euler(0, 0, yaw)
         sp.qz = (float)sy; sp.qw = (float)cy;
     }
 
+    // ---- RewardWrapper.reset (wrapper.py:96-101) reads drone 0's row of the reset observation: current gate id,
+    // observed pose of gate 0, position.  Evaluated on the state the episode starts from, by drone 0's thread.
+    int sh_gate = 0;
+    T sh[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+    const bool shaper = (RP.wrappers & ADRP_WRAP_REWARD) && valid && i == 0;
+    if (shaper) {
+        sh_gate = rb.shape_gate[env];
+        if (sh_gate < 0) {
+            sh_gate = current_gate;
+            if (RP.G > 0) {
+                const T* tg = rb.track + env;                  // gate 0 of this env, straight from HBM (6 reads per episode)
+                const long long N = P.N;
+                const T hz0 = drone_half_height(P.coll_r, P.coll_h, rotmat(d.q).m22);
+                const bool in_range = gate_distance(d.p, hz0, P.coll_r, tg[0], tg[N], tg[2 * N], tg[4 * N], tg[5 * N], RP.gate_type[0]) < RP.visibility;
+                sh[0] = in_range ? tg[0] : RP.gate_nom[0][0];
+                sh[1] = in_range ? tg[N] : RP.gate_nom[0][1];
+                sh[2] = in_range ? tg[2 * N] : RP.gate_nom[0][2];
+            }
+            sh[3] = d.p.x; sh[4] = d.p.y; sh[5] = d.p.z;
+        } else {
+#pragma unroll
+            for (int k = 0; k < 6; ++k) sh[k] = rb.shape_vec[(long long)k * P.N + env];
+        }
+    }
     // ---- S fused substeps (:210-254)
     for (int s = 0; s < P.S; ++s) {
         // disturbance draws of this substep: injected, or Philox(seed; env, drone, tick, episode)
@@ -246,12 +271,33 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
     if (fl) latch |= ADRP_FLAG_ELIMINATED;
     if (m.error) fl |= ADRP_FLAG_TUMBLE_STOP;
     const int not_done = valid && !(latch & (ADRP_FLAG_ELIMINATED | ADRP_FLAG_FINISHED));
-    const int term = group_or(not_done, mpad) == 0;
+    int term = group_or(not_done, mpad) == 0;
+    T rew = T(0);                                                                        // :665-670
+    if (shaper) {
+        // RewardWrapper._compute_reward (wrapper.py:121-186) on this step's observation row of drone 0.  Declared
+        // where the reference raises: info has no "task_completed" key in this fork -> drone 0's FINISHED latch;
+        // gate id == number of gates has no entry in its pose table -> the target is kept.
+        const T* o = obs + od * P.O;
+        T r_passed = T(0), r_end = T(0);
+        if (current_gate > sh_gate % 4) {
+            sh_gate = current_gate;
+            if (current_gate < RP.G) { sh[0] = o[12 + 4 * current_gate]; sh[1] = o[13 + 4 * current_gate]; sh[2] = o[14 + 4 * current_gate]; }
+            r_passed = T(5);
+        }
+        if (term) r_end = (latch & ADRP_FLAG_FINISHED) ? T(10) : T(-1);
+        const T dpx = sh[0] - sh[3], dpy = sh[1] - sh[4], dcx = sh[0] - d.p.x, dcy = sh[1] - d.p.y;
+        const T prog_xy = M<T>::sqrt(dpx * dpx + dpy * dpy) - M<T>::sqrt(dcx * dcx + dcy * dcy);
+        const T prog_z = M<T>::abs(sh[2] - sh[5]) - M<T>::abs(sh[2] - d.p.z);
+        rew = prog_xy + prog_z + r_passed + r_end;
+        sh[3] = d.p.x; sh[4] = d.p.y; sh[5] = d.p.z;
+    }
+    if (RP.wrappers & ADRP_WRAP_OBS)                                                     // wrapper.py:60-61
+        term |= __shfl_sync(0xffffffffu, current_gate, lane_base) >= 2;
     const int trunc = counter >= P.trunc_steps;                                          // step_counter / PYB_FREQ > episode_len_sec (:709)
     const bool done = P.auto_reset && (term || trunc);
     if (valid && drone_flags) drone_flags[od] = (uint8_t)(fl | latch);
     if (valid && i == 0) {
-        reward[env] = T(0);                                                              // :665-670
+        reward[env] = rew;
         terminated[env] = (uint8_t)term;
         truncated[env] = (uint8_t)trunc;
     }
@@ -269,6 +315,11 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
             if (i == 0) rb.episode[env] = episode + 1;
         }
         if (i == 0) b.step_counter[env] = done ? 0 : counter + P.S;                      // BaseAviary.py:386
+        if (shaper) {
+            rb.shape_gate[env] = done ? -1 : sh_gate;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) rb.shape_vec[(long long)k * P.N + env] = sh[k];
+        }
         store_drone(b, D, t, d);
         store_mel(rb, D, t, m);
         rb.gate_latch[t] = current_gate | (latch << 16);

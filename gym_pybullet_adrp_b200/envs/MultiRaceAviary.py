@@ -37,6 +37,7 @@ class MultiRaceAviary(BaseAviary):
         init_xyzs = np.array([race_config["init_states"][d]["pos"] for d in names], dtype=float)
         init_rpys = np.array([race_config["init_states"][d]["rpy"] for d in names], dtype=float) * np.pi / 180   # :95
         self._physics_mask = batch.pop("physics_mask", None)
+        self._wrappers = int(batch.pop("wrappers", 0))       # _abi.WRAP_* (utils/wrapper.py fused into the step kernel)
         super().__init__(drone_model=drone_model, num_drones=num_drones, initial_xyzs=init_xyzs, initial_rpys=init_rpys,
                          physics=physics, pyb_freq=pyb_freq, ctrl_freq=ctrl_freq, gui=gui, record=record, **batch)
 
@@ -45,7 +46,8 @@ class MultiRaceAviary(BaseAviary):
                                      drone_model=self.DRONE_MODEL, physics=self.PHYSICS, pyb_freq=self.PYB_FREQ,
                                      ctrl_freq=self.CTRL_FREQ, racemode=self.racemode, precision=self.PRECISION,
                                      device=self.DEVICE, seed=self._seed or None, env_offset=self._env_offset,
-                                     auto_reset=self._auto_reset, physics_mask=self._physics_mask)
+                                     auto_reset=self._auto_reset, physics_mask=self._physics_mask,
+                                     wrappers=self._wrappers)
 
     # ------------------------------------------------------------------ spaces (:284-343)
     def _actionSpace(self):

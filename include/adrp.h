@@ -18,7 +18,7 @@
 extern "C" {
 #endif
 
-#define ADRP_ABI_VERSION 3
+#define ADRP_ABI_VERSION 4
 #define ADRP_MAX_DRONES 32      /* drones per env: one env lives inside one warp */
 #define ADRP_MAX_GATES 8
 #define ADRP_MAX_OBSTACLES 8
@@ -65,6 +65,16 @@ enum {
     ADRP_FLAG_ELIMINATED = 1, ADRP_FLAG_FINISHED = 2, ADRP_FLAG_CRASHED = 4,
     ADRP_FLAG_OUT_OF_BOUNDS = 8, ADRP_FLAG_UNSTABLE = 16, ADRP_FLAG_TUMBLE_STOP = 32
 };
+
+/* adrp_config.wrappers: gym_pybullet_adrp/utils/wrapper.py fused into the race step as epilogues.
+ *   ADRP_WRAP_OBS     DroneObservationWrapper.step (:39-63): the yaw component of every setpoint action is zeroed
+ *                     and `terminated` is also raised once drone 0 has passed two gates.
+ *   ADRP_WRAP_REWARD  RewardWrapper (:66-186): `reward` becomes the gate-progress shaping of drone 0
+ *                     (xy progress + z progress towards the current gate, +5 per gate passed, -1 / +10 when the
+ *                     env terminates without / with drone 0 having finished), with the wrapper's state
+ *                     (current gate id, current target, previous position) kept per env on the device.
+ * Composition is DroneObservationWrapper(RewardWrapper(env)): the reward sees the env's own `terminated`. */
+enum { ADRP_WRAP_OBS = 1, ADRP_WRAP_REWARD = 2 };
 
 /* URDF-level constants of one drone model (BaseAviary._parseURDFParameters, :989-1021). */
 typedef struct adrp_drone_params {
@@ -115,7 +125,7 @@ typedef struct adrp_config {
     int32_t auto_reset;           /* 1: envs whose terminated|truncated is set are re-initialised inside the step */
     int32_t dslpid_model;         /* drone model the DSLPID mixer/constants come from (BaseRLAviary.py:75-76 always CF2X) */
     uint32_t bug_compat;          /* reserved: SURVEY Appendix E quirks, all reproduced (must be 0xFFFFFFFF) */
-    int32_t reserved0;
+    int32_t wrappers;             /* ADRP_WRAP_* mask: the reference's gymnasium wrappers fused into the step (race env) */
     double g;                     /* 9.8 (BaseAviary.py:75) */
     double episode_len_sec;       /* HoverAviary 8 s (:52), race config episode_len_sec */
     double mel_mass;              /* firmware g_vehicleMass (pycffirmware, declared 0.027) */

@@ -155,6 +155,8 @@ typedef struct FN(orc_race) {
     uint8_t* latch;                /* (N, M)  ADRP_FLAG_ELIMINATED | ADRP_FLAG_FINISHED */
     int32_t* episode;              /* (N) resets so far: Philox counter word */
     FN(mel_state)* mel;            /* (N, M) */
+    REAL* shaping;                 /* (N, 7) RewardWrapper state: current_gate_id (-1: not yet initialised),
+                                      current_target xyz, previous_pos xyz (utils/wrapper.py:78-80,98-101) */
     FN(lpf_coef) gyro_lpf;         /* lpf2pInit(gyrolpf, 500, ACCEL_LPF_CUTOFF_FREQ = 30)  (:116-117, E12) */
 } FN(orc_race);
 
@@ -170,6 +172,8 @@ static FN(orc_race)* FN(race_create)(FN(orc)* h)
     r->latch = (uint8_t*)calloc(N * M, 1);
     r->episode = (int32_t*)calloc(N, sizeof(int32_t));
     r->mel = (FN(mel_state)*)calloc(N * M, sizeof(FN(mel_state)));
+    r->shaping = (REAL*)calloc(N * 7, sizeof(REAL));
+    for (size_t n = 0; n < N; ++n) r->shaping[7 * n] = (REAL)-1;
     FN(lpf2p_init)(&r->gyro_lpf, 500.0f, 30.0f);
     h->O = 12 + 5 * r->G + 4 * r->O + 1 + (h->cfg.race_mode == ADRP_RACE_COMPETE ? 6 * (h->M - 1) : 0);
     return r;
@@ -178,7 +182,7 @@ static FN(orc_race)* FN(race_create)(FN(orc)* h)
 static void FN(race_destroy)(FN(orc_race)* r)
 {
     free(r->gates_actual); free(r->obst_actual); free(r->body); free(r->current_gate); free(r->latch);
-    free(r->episode); free(r->mel); free(r);
+    free(r->episode); free(r->mel); free(r->shaping); free(r);
 }
 
 /* uniform draws consumed by one reset: gates 3 each, obstacles 2 each, per drone 4 inertia + 3 pos + 3 rot */
@@ -197,6 +201,7 @@ static void FN(race_init_env)(FN(orc)* h, int n, const REAL* draws)
     const adrp_config* c = &h->cfg;
     const int M = h->M, R = FN(race_draws_dim)(h);
     REAL u[3 * ADRP_MAX_GATES + 2 * ADRP_MAX_OBSTACLES + 10 * ADRP_MAX_DRONES];
+    r->shaping[7 * (size_t)n] = (REAL)-1;                             /* RewardWrapper.reset: re-read on the next step */
     if (draws) {
         for (int k = 0; k < R; ++k) u[k] = draws[k];
     } else {
@@ -533,11 +538,25 @@ static void FN(race_step_env)(FN(orc)* h, int n, const REAL* action, const REAL*
         if (r->latch[(size_t)n * M + i] & ADRP_FLAG_ELIMINATED) continue;
         const REAL* a = action + ((size_t)n * M + i) * 4;
         for (int k = 0; k < 3; ++k) { m->sp_pos[k] = (float)a[k]; m->sp_vel[k] = 0; m->sp_acc[k] = 0; m->sp_rate_deg[k] = 0; }
-        REAL yaw = a[3];                                             /* get_quaternion_from_euler(0, 0, yaw) (:525) */
+        REAL yaw = (c->wrappers & ADRP_WRAP_OBS) ? (REAL)0 : a[3];   /* wrapper.py:52-57; get_quaternion_from_euler(0, 0, yaw) (:525) */
         m->sp_quat[0] = (float)(SIN((REAL)0) * COS((REAL)0) * COS(yaw / 2) - COS((REAL)0) * SIN((REAL)0) * SIN(yaw / 2));
         m->sp_quat[1] = (float)(COS((REAL)0) * SIN((REAL)0) * COS(yaw / 2) + SIN((REAL)0) * COS((REAL)0) * SIN(yaw / 2));
         m->sp_quat[2] = (float)(COS((REAL)0) * COS((REAL)0) * SIN(yaw / 2) - SIN((REAL)0) * SIN((REAL)0) * COS(yaw / 2));
         m->sp_quat[3] = (float)(COS((REAL)0) * COS((REAL)0) * COS(yaw / 2) + SIN((REAL)0) * SIN((REAL)0) * SIN(yaw / 2));
+    }
+    /* RewardWrapper.reset (wrapper.py:96-101) reads the reset observation of drone 0: current gate id, the
+     * observed pose of gate 0 and the position.  Evaluated here, on the state the episode starts from. */
+    if ((c->wrappers & ADRP_WRAP_REWARD) && r->shaping[7 * (size_t)n] < 0) {
+        REAL* sh = r->shaping + 7 * (size_t)n;
+        const REAL* st = h->state + (size_t)n * M * 20;
+        sh[0] = (REAL)r->current_gate[(size_t)n * M];
+        for (int k = 0; k < 3; ++k) sh[1 + k] = 0;
+        if (r->G > 0) {
+            const REAL* ga = r->gates_actual + (size_t)n * r->G * 4;
+            const int in_range = FN(gate_distance)(h, st, FN(drone_hz)(h, st), ga, c->track.gate_type[0]) < (REAL)c->track.visibility_range;
+            for (int k = 0; k < 3; ++k) sh[1 + k] = in_range ? ga[k] : (REAL)c->track.gates[0][k];
+        }
+        for (int k = 0; k < 3; ++k) sh[4 + k] = st[k];
     }
     for (int s = 0; s < S; ++s) {
         REAL* env = h->state + (size_t)n * M * 20;
@@ -623,6 +642,30 @@ static void FN(race_post_env)(FN(orc)* h, int n, REAL* obs, REAL* reward, uint8_
         if (!(*L & (ADRP_FLAG_ELIMINATED | ADRP_FLAG_FINISHED))) all_done = 0;
     }
     reward[n] = 0;                                                   /* :665-670 */
+    if (c->wrappers & ADRP_WRAP_REWARD) {
+        /* RewardWrapper._compute_reward (wrapper.py:121-186) on drone 0's row of this step's observation.
+         * Declared where the reference raises: info has no "task_completed" key in this fork (KeyError once the env
+         * terminates) -> drone 0's FINISHED latch; gate id == number of gates has no entry in its pose table
+         * (KeyError) -> the target is kept. */
+        REAL* sh = r->shaping + 7 * (size_t)n;
+        const REAL* o = obs + (size_t)n * M * h->O;
+        const int gate_id = (int)r->current_gate[(size_t)n * M];
+        REAL r_passed = 0, r_collision = 0, r_lab = 0;
+        if (gate_id > ((int)sh[0]) % 4) {
+            sh[0] = (REAL)gate_id;
+            if (gate_id < r->G) for (int k = 0; k < 3; ++k) sh[1 + k] = o[12 + 4 * gate_id + k];
+            r_passed = 5;
+        }
+        const int completed = (r->latch[(size_t)n * M] & ADRP_FLAG_FINISHED) != 0;
+        if (all_done && !completed) r_collision = -1;
+        if (all_done && completed) r_lab = 10;
+        const REAL dpx = sh[1] - sh[4], dpy = sh[2] - sh[5], dcx = sh[1] - o[0], dcy = sh[2] - o[1];
+        const REAL prog_xy = SQRT(dpx * dpx + dpy * dpy) - SQRT(dcx * dcx + dcy * dcy);
+        const REAL prog_z = FABS(sh[3] - sh[6]) - FABS(sh[3] - o[2]);
+        reward[n] = prog_xy + prog_z + r_passed + r_collision + r_lab;
+        for (int k = 0; k < 3; ++k) sh[4 + k] = o[k];
+    }
+    if ((c->wrappers & ADRP_WRAP_OBS) && r->current_gate[(size_t)n * M] >= 2) all_done = 1;   /* wrapper.py:60-61 */
     te[n] = (uint8_t)all_done;
     tr[n] = (uint8_t)((double)h->step_counter[n] / (double)c->pyb_freq > c->episode_len_sec);   /* :709 */
     h->step_counter[n] += S;

@@ -23,3 +23,8 @@ class Env:
 class Wrapper(Env):
     def __init__(self, env):
         self.env = env
+
+    def __getattr__(self, name):                     # gymnasium.Wrapper forwards unknown attributes to the wrapped env
+        if name.startswith("_") or name == "env":
+            raise AttributeError(name)
+        return getattr(self.env, name)

@@ -62,16 +62,22 @@ class RecordingRNG:
         return v
 
 
-def gate_pass_setpoints(cfg, steps, M):
-    """Smooth full-state setpoints: climb, fly through gate 0 along its normal, carry on to gate 1."""
+def gate_pass_setpoints(cfg, steps, M, through_gate1=False):
+    """Smooth full-state setpoints: climb, fly through gate 0 along its normal, carry on to gate 1
+    (through_gate1: around the obstacle next to it and through gate 1 as well)."""
     g0, g1 = cfg.gates[0], cfg.gates[1]
     n0 = np.array([-np.sin(g0[5]), np.cos(g0[5])])
+    n1 = np.array([-np.sin(g1[5]), np.cos(g1[5])])
     starts = [np.array(cfg.init_states[f"drone{i}"].pos) for i in range(M)]
     out = np.zeros((steps, M, 4))
     for i in range(M):
         way = [np.r_[starts[i][:2], 0.35], np.r_[1.0, 0.0, 0.45], np.r_[np.array(g0[:2]) - 0.45 * n0, 0.525],
                np.r_[np.array(g0[:2]) + 0.45 * n0, 0.525], np.r_[g1[0] - 0.3, g1[1] - 0.1, 0.9]]
         seg_t = [1.2, 2.2, 2.0, 1.4, 1.8]
+        if through_gate1:
+            way = way[:4] + [np.r_[0.15, -1.75, 0.9], np.r_[np.array(g1[:2]) - 0.45 * n1, 1.0],
+                             np.r_[np.array(g1[:2]) + 0.45 * n1, 1.0]]
+            seg_t = [1.2, 2.2, 2.0, 1.4, 1.6, 1.8, 1.6]
         t0 = 1.6 * i                                   # the second drone follows later
         for k in range(steps):
             t = max(0.0, k / 25.0 - t0)
@@ -132,7 +138,45 @@ def race_case(name, level, physics, racemode, M, steps, seed, actions=None):
           int(np.argmax(term)) if term.any() else None)
 
 
+def wrapper_case(name, level, M, steps, seed):
+    """DroneObservationWrapper(RewardWrapper(MultiRaceAviary)) as the reference composes them for training
+    (utils/wrapper.py): shaped reward of drone 0, yaw zeroed, terminated after two gates."""
+    from gym_pybullet_adrp.utils.wrapper import DroneObservationWrapper, RewardWrapper
+    cfg = munchify(json.loads(json.dumps(configs.builtin_config(level))))
+    rec = RecordingRNG(seed)
+    orig_uniform = np.random.uniform
+    np.random.uniform = rec.uniform
+    base = MultiRaceAviary(cfg, drone_model=DroneModel.CF2X, num_drones=M, physics=Physics.PYB, racemode=RaceMode.COMPARE)
+    base.np_random = rec
+    env = DroneObservationWrapper(RewardWrapper(base))
+    try:
+        obs0, _ = env.reset()
+        draws = np.array(rec.uniforms)
+        actions = gate_pass_setpoints(cfg, steps, M, through_gate1=True)
+        actions[:, :, 3] = 0.3                                   # the wrapper must zero this
+        obs = np.zeros((steps,) + obs0.shape)
+        rew, term, trunc, gate = np.zeros(steps), np.zeros(steps, bool), np.zeros(steps, bool), np.zeros((steps, M))
+        n = 0
+        for k in range(steps):
+            o, r, te, tr, _ = env.step(actions[k].copy())
+            obs[k], rew[k], term[k], trunc[k], gate[k] = o, r, te, tr, base.current_gate
+            n = k + 1
+            if te or tr:
+                break
+    finally:
+        np.random.uniform = orig_uniform
+        base.close()
+    meta = dict(env="race", level=level, physics="PYB", racemode="COMPARE", M=M, steps=n, wrappers=3)
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), meta=json.dumps(meta), draws=draws, obs0=obs0,
+                        actions=actions[:n], obs=obs[:n], reward=rew[:n], terminated=term[:n], truncated=trunc[:n],
+                        current_gate=gate[:n])
+    print(name, "steps:", n, "gates:", gate[n - 1].tolist(), "return:", rew[:n].sum(), "terminated:", term[n - 1])
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "--new":
+        wrapper_case("race_wrappers_compare_gs", "getting_started", 2, 400, 5)
+        return
     race_case("race_pyb_compete_gs", "getting_started", Physics.PYB, RaceMode.COMPETE, 2, 230, 1)
     race_case("race_pyb_compare_level3", "level3", Physics.PYB, RaceMode.COMPARE, 2, 150, 2)
     race_case("race_dyn_compete_level1", "level1", Physics.DYN, RaceMode.COMPETE, 2, 60, 3)

@@ -139,6 +139,61 @@ def test_race_batched_philox_fp64(M, racemode, physics):
     h.close(); o.close()
 
 
+@pytest.mark.parametrize("name", gc.WRAPPER_CASES)
+@pytest.mark.parametrize("precision", [_abi.F64, _abi.F32])
+def test_race_wrappers_golden(name, precision):
+    """utils/wrapper.py fused into the step (adrp_config.wrappers) against the reference's own wrapped env:
+    shaped reward of drone 0, zeroed yaw command, terminated once drone 0 has passed two gates."""
+    meta, z = gc.load(name)
+    rc, cfg = gc.race_config_for(meta, precision=precision, wrappers=meta["wrappers"])
+    h = _handle(cfg)
+    h.reset(draws=gc.place_draws(rc, z["draws"], meta["M"])[None])
+    ret = 0.0
+    for k in range(meta["steps"]):
+        obs, rew, te, tr, fl = h.step(z["actions"][k][None])
+        o = obs.cpu().numpy()[0].astype(np.float64)
+        if precision == _abi.F64:
+            assert gc.rel_err(o, z["obs"][k]) < TOL64, (name, k)
+            assert abs(float(rew[0]) - z["reward"][k]) < 1e-9, (name, k)
+            assert bool(te[0]) == bool(z["terminated"][k]) and bool(tr[0]) == bool(z["truncated"][k]), (name, k)
+            np.testing.assert_array_equal(o[:, 48], z["current_gate"][k])
+        elif k < 25:                                          # fp32: 1 s of closed-loop tracking (north_star)
+            assert np.abs(o[:, 0:3] - z["obs"][k][:, 0:3]).max() < TOL32, (name, k)
+            assert abs(float(rew[0]) - z["reward"][k]) < 2 * TOL32, (name, k)
+        ret += float(rew[0])
+    if precision == _abi.F64:
+        assert bool(te[0]) and abs(ret - z["reward"].sum()) < 1e-8
+    else:
+        assert abs(ret - z["reward"].sum()) < 0.05           # same gates passed (2 x 5) and the same way flown
+    h.close()
+
+
+def test_race_wrappers_batched_vs_oracle_fp64():
+    """Wrappers + randomisation + auto-reset over many envs: the device-side wrapper state (gate id, target, previous
+    position) follows the oracle's through in-kernel resets."""
+    N, M = 200, 2
+    rc = configs.load_config("level3")
+    rc["episode_len_sec"] = 0.8
+    cfg = _abi.make_race_config(rc, num_envs=N, num_drones=M, physics=Physics.PYB, racemode=RaceMode.COMPARE,
+                                precision=_abi.F64, auto_reset=True, seed=7, env_offset=3,
+                                wrappers=_abi.WRAP_OBS | _abi.WRAP_REWARD)
+    h, o = _handle(cfg), OracleEnv(cfg)
+    rng = np.random.default_rng(5)
+    resets = 0
+    for k in range(45):
+        a = _random_setpoints(rng, cfg, N, M, k % 21)
+        obs, rew, te, tr, fl = h.step(a)
+        obs_o, rew_o, te_o, tr_o, fl_o = o.step(a, nthreads=8)
+        assert gc.rel_err(obs.cpu().numpy(), obs_o) < TOL64, k
+        assert np.abs(rew.cpu().numpy() - rew_o).max() < 1e-9, k
+        np.testing.assert_array_equal(te.cpu().numpy(), te_o)
+        np.testing.assert_array_equal(tr.cpu().numpy(), tr_o)
+        resets += int(te_o.sum() + tr_o.sum())
+    assert resets > N                                          # every env went through at least one in-kernel reset
+    assert np.abs(rew_o).max() > 0                             # and the shaping is live
+    h.close(); o.close()
+
+
 def test_race_mellinger_formation_fp32():
     """north_star target shape: 8 CF2X per env, ground effect + drag + downwash, Mellinger per substep, no track.
     Run with the Bullet free body (PYB_GND_DRAG_DW): under the reference's semantics the Mellinger loop is unstable

@@ -85,3 +85,16 @@ def test_config_files_equal_builtin_tables():
         for key in ("random_drone_state_info", "random_drone_inertia_info", "random_gates_obstacles_info", "disturbances_info"):
             if b.get(key.replace("_info", "")):
                 assert a[key] == b[key], (name, key)
+
+
+def test_wrapper_classes_surface():
+    """utils/wrapper.py mirror: wrapping sets the kernel's epilogue bits; only race envs; attribute forwarding."""
+    from gym_pybullet_adrp_b200 import _abi, configs
+    from gym_pybullet_adrp_b200.envs import MultiRaceAviary
+    from gym_pybullet_adrp_b200.utils.wrapper import DroneObservationWrapper, RewardWrapper
+    base = MultiRaceAviary(configs.load_config("twogates"), num_envs=8)
+    env = DroneObservationWrapper(RewardWrapper(base))
+    assert env.unwrapped is base and env.NUM_DRONES == 2
+    assert base._make_config().wrappers == (_abi.WRAP_OBS | _abi.WRAP_REWARD)
+    with pytest.raises(TypeError, match="MultiRaceAviary"):
+        RewardWrapper(HoverAviary())

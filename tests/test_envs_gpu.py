@@ -106,3 +106,46 @@ def test_multi_race_aviary_matches_reference_run():
     with pytest.raises(NotImplementedError):
         env.step([("fst", ())] * 2)
     env.close()
+
+
+def test_wrapper_classes_match_reference_run():
+    """DroneObservationWrapper(RewardWrapper(MultiRaceAviary)) -- the reference's class names, fused in the kernel."""
+    from gym_pybullet_adrp_b200.utils.wrapper import DroneObservationWrapper, RewardWrapper
+    meta, z = gc.load("race_wrappers_compare_gs")
+    rc = configs.load_config(meta["level"])
+    env = DroneObservationWrapper(RewardWrapper(MultiRaceAviary(rc, num_drones=meta["M"], physics=Physics.PYB,
+                                                                racemode=RaceMode.COMPARE, precision="fp64")))
+    obs, info = env.reset(draws=gc.place_draws(rc, z["draws"], meta["M"])[None])
+    ret = 0.0
+    for k in range(meta["steps"]):
+        obs, reward, terminated, truncated, info = env.step(z["actions"][k])
+        assert gc.rel_err(obs, z["obs"][k]) < 1e-9, k
+        assert abs(reward - z["reward"][k]) < 1e-9 and terminated == bool(z["terminated"][k]), k
+        ret += reward
+    assert terminated and env.current_gate[0] == 2 and abs(ret - z["reward"].sum()) < 1e-8
+    with pytest.raises(RuntimeError, match="before its first reset"):
+        RewardWrapper(env.unwrapped)
+    env.close()
+
+
+def test_torch_vec_env_rollout():
+    """SB3-style rollout loop on device tensors: shapes, done bookkeeping, auto-reset keeps every env alive."""
+    import torch
+    from gym_pybullet_adrp_b200.vec_env import TorchVecEnv
+    N = 64
+    env = HoverAviary(physics=Physics.PYB, act=ActionType.RPM, num_envs=N, auto_reset=True)
+    env.EPISODE_LEN_SEC = 1.0
+    venv = TorchVecEnv(env)
+    obs = venv.reset()
+    assert obs.shape == (N, int(np.prod(env.observation_space.shape))) and obs.is_cuda
+    g = torch.Generator(device="cuda").manual_seed(0)
+    finished = torch.zeros(N, dtype=torch.int64, device="cuda")
+    for k in range(80):
+        actions = 0.2 * (2 * torch.rand((N,) + env.action_space.shape, device="cuda", generator=g) - 1)
+        obs, rewards, dones, infos = venv.step(actions)
+        assert rewards.shape == (N,) and dones.shape == (N,) and dones.dtype == torch.bool
+        finished += dones
+        assert torch.all(infos["episode_length"][dones] > 0)
+    assert int(finished.min()) >= 1 and torch.isfinite(obs).all()      # 80 steps at 30 Hz > 1 s episodes: everyone reset
+    assert int(venv.episode_lengths.max()) <= 31
+    venv.close()

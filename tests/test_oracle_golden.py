@@ -122,6 +122,26 @@ def test_race_env_fp64(name):
         assert rew[0] == 0
 
 
+@pytest.mark.parametrize("name", gc.WRAPPER_CASES)
+def test_race_wrappers_fp64(name):
+    """utils/wrapper.py as run by the reference on its own env: shaped reward of drone 0 (gate progress, +5 per gate),
+    zeroed yaw command, terminated once drone 0 has passed two gates."""
+    meta, z = gc.load(name)
+    rc, cfg = gc.race_config_for(meta, wrappers=meta["wrappers"])
+    env = OracleEnv(cfg)
+    env.reset(draws=gc.place_draws(rc, z["draws"], meta["M"])[None])
+    ret = 0.0
+    for k in range(meta["steps"]):
+        obs, rew, te, tr, fl = env.step(z["actions"][k][None])
+        assert gc.rel_err(obs[0], z["obs"][k]) < TOL64, (name, k)
+        assert abs(rew[0] - z["reward"][k]) < 1e-9, (name, k, rew[0], z["reward"][k])
+        assert bool(te[0]) == bool(z["terminated"][k]) and bool(tr[0]) == bool(z["truncated"][k]), (name, k)
+        np.testing.assert_array_equal(obs[0][:, 48], z["current_gate"][k])
+        ret += rew[0]
+    assert bool(z["terminated"][-1]) and z["current_gate"][-1][0] == 2      # the recording ends on the wrapper's condition
+    assert abs(ret - z["reward"].sum()) < 1e-8
+
+
 def test_mellinger_schedule_known_answer():
     """the float64 sub-rate schedule of MellingerControl._step_controller (:395-411),
     first 120 ticks, computed with the reference's own expressions; the oracle's integer-stamp form
