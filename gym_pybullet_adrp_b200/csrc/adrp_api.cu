@@ -70,6 +70,7 @@ int action_dim(int act)
 {
     switch (act) {
     case ADRP_ACT_RPM_RAW: case ADRP_ACT_RPM: case ADRP_ACT_VEL: case ADRP_ACT_MEL: return 4;
+    case ADRP_ACT_MEL_FULL: return 13;
     case ADRP_ACT_PID: return 3;
     case ADRP_ACT_ONE_D_RPM: case ADRP_ACT_ONE_D_PID: return 1;
     case ADRP_ACT_PID_FULL: return 12;
@@ -336,7 +337,7 @@ int validate(const adrp_config* c)
     if (c->ctrl_freq < 1 || c->pyb_freq % c->ctrl_freq != 0) { g_create_error = "[ERROR] in BaseAviary.__init__(), pyb_freq is not divisible by env_freq."; return ADRP_EINVAL; }
     if (c->precision != ADRP_F32 && c->precision != ADRP_F64) { g_create_error = "unknown precision"; return ADRP_EINVAL; }
     if (action_dim(c->action_type) == 0) { g_create_error = "unknown action_type"; return ADRP_EINVAL; }
-    if ((c->env_kind == ADRP_ENV_RACE) != (c->action_type == ADRP_ACT_MEL)) { g_create_error = "ADRP_ACT_MEL (Mellinger full-state setpoints) is the race env's action type, and its only one"; return ADRP_EINVAL; }
+    if ((c->env_kind == ADRP_ENV_RACE) != (c->action_type == ADRP_ACT_MEL || c->action_type == ADRP_ACT_MEL_FULL)) { g_create_error = "ADRP_ACT_MEL / ADRP_ACT_MEL_FULL (Mellinger full-state setpoints) are the race env's action types, and its only ones"; return ADRP_EINVAL; }
     if (c->wrappers & ~(ADRP_WRAP_OBS | ADRP_WRAP_REWARD)) { g_create_error = "unknown bit in wrappers"; return ADRP_EINVAL; }
     if (c->wrappers && c->env_kind != ADRP_ENV_RACE) { g_create_error = "wrappers (utils/wrapper.py) apply to the race env"; return ADRP_EINVAL; }
     if (c->env_kind == ADRP_ENV_RACE && (c->track.num_gates < 0 || c->track.num_gates > ADRP_MAX_GATES || c->track.num_obstacles < 0 || c->track.num_obstacles > ADRP_MAX_OBSTACLES)) { g_create_error = "too many gates / obstacles"; return ADRP_EINVAL; }

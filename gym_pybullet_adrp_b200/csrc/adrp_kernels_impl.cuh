@@ -84,18 +84,19 @@ template <typename T>
 using RaceStepFn = void (*)(KParams<T>, RaceParams<T>, KBuffers<T>, RaceBuffers<T>, const T*, const T*, T*, T*, uint8_t*,
                             uint8_t*, uint8_t*);
 template <typename T>
-inline RaceStepFn<T> race_step_fn(int mpad)
+inline RaceStepFn<T> race_step_fn(int mpad, bool full)
 {
+    if (full) return race_step_kernel<T, 0, true>;           // (Command.FULLSTATE, args) actions: scripted controllers
     if (M<T>::fast) {
         switch (mpad) {
-            case 1: return race_step_kernel<T, 1>;
-            case 2: return race_step_kernel<T, 2>;
-            case 4: return race_step_kernel<T, 4>;
-            case 8: return race_step_kernel<T, 8>;
+            case 1: return race_step_kernel<T, 1, false>;
+            case 2: return race_step_kernel<T, 2, false>;
+            case 4: return race_step_kernel<T, 4, false>;
+            case 8: return race_step_kernel<T, 8, false>;
             default: break;
         }
     }
-    return race_step_kernel<T, 0>;
+    return race_step_kernel<T, 0, false>;
 }
 
 template <typename T>
@@ -103,7 +104,7 @@ cudaError_t Launch<T>::race_prepare(const RaceParams<T>& RP, const KParams<T>& P
 {
     const size_t bytes = race_smem_bytes(P, RP);
     if (bytes <= 48 * 1024) return cudaSuccess;
-    cudaError_t e = cudaFuncSetAttribute(race_step_fn<T>(P.Mpad), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    cudaError_t e = cudaFuncSetAttribute(race_step_fn<T>(P.Mpad, P.action_type == ADRP_ACT_MEL_FULL), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(race_reset_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
 }
@@ -121,7 +122,7 @@ cudaError_t Launch<T>::race_step(const KParams<T>& P, const RaceParams<T>& RP, c
                                  const T* action, const T* noise, T* obs, T* reward, uint8_t* te, uint8_t* tr,
                                  uint8_t* fl, cudaStream_t s)
 {
-    race_step_fn<T>(P.Mpad)<<<grid_for((long long)(P.env_end - P.env_begin) * P.Mpad), kBlock, race_smem_bytes(P, RP), s>>>(P, RP, b, rb, action, noise, obs, reward, te, tr, fl);
+    race_step_fn<T>(P.Mpad, P.action_type == ADRP_ACT_MEL_FULL)<<<grid_for((long long)(P.env_end - P.env_begin) * P.Mpad), kBlock, race_smem_bytes(P, RP), s>>>(P, RP, b, rb, action, noise, obs, reward, te, tr, fl);
     return cudaGetLastError();
 }
 

@@ -46,7 +46,9 @@ struct Mel {
     int tick, tumble, last_att, error;
 };
 
-struct MelSetpoint { float pos[3], qz, qw; };   // full-state command: vel = acc = rates = 0, yaw-only quaternion (:510-543)
+// Full-state command (MellingerControl._sendFullStateCmd, :510-543): yaw-only quaternion; vel / acc / attitude rates
+// (deg/s) are zero for ndarray actions (MultiRaceAviary.py:190-195) and literal zeros in those kernels.
+struct MelSetpoint { float pos[3], qz, qw, vel[3], acc[3], rate_deg[3]; };
 
 __device__ __forceinline__ float fw_clamp(float v, float lo, float hi) { return v < lo ? lo : (v > hi ? hi : v); }
 template <typename T> __device__ __forceinline__ float fw_clampT(float v, float lo, float hi)
@@ -79,16 +81,15 @@ __device__ __forceinline__ void fw_mellinger(MelFw& m, const MelSetpoint& sp, fl
     const float kR_z = 60000.0f, kw_z = 12000.0f, ki_m_z = 500.0f, i_range_m_z = 1500.0f;
     const float kd_omega_rp = 200.0f, GRAVITY_MAGNITUDE = 9.81f;
     const float dt = (float)(1.0f / 500.0f);
-    const float sp_vel = 0.0f, sp_acc = 0.0f, sp_rate_deg = 0.0f;
     float r_error[3], v_error[3], tt[3];
 #pragma unroll
-    for (int k = 0; k < 3; ++k) { r_error[k] = sp.pos[k] - pos[k]; v_error[k] = sp_vel - vel[k]; }
+    for (int k = 0; k < 3; ++k) { r_error[k] = sp.pos[k] - pos[k]; v_error[k] = sp.vel[k] - vel[k]; }
     m.i_error_z += r_error[2] * dt; m.i_error_z = fw_clampT<T>(m.i_error_z, -i_range_z, i_range_z);
     m.i_error_x += r_error[0] * dt; m.i_error_x = fw_clampT<T>(m.i_error_x, -i_range_xy, i_range_xy);
     m.i_error_y += r_error[1] * dt; m.i_error_y = fw_clampT<T>(m.i_error_y, -i_range_xy, i_range_xy);
-    tt[0] = mass * sp_acc + kp_xy * r_error[0] + kd_xy * v_error[0] + ki_xy * m.i_error_x;
-    tt[1] = mass * sp_acc + kp_xy * r_error[1] + kd_xy * v_error[1] + ki_xy * m.i_error_y;
-    tt[2] = mass * (sp_acc + GRAVITY_MAGNITUDE) + kp_z * r_error[2] + kd_z * v_error[2] + ki_z * m.i_error_z;
+    tt[0] = mass * sp.acc[0] + kp_xy * r_error[0] + kd_xy * v_error[0] + ki_xy * m.i_error_x;
+    tt[1] = mass * sp.acc[1] + kp_xy * r_error[1] + kd_xy * v_error[1] + ki_xy * m.i_error_y;
+    tt[2] = mass * (sp.acc[2] + GRAVITY_MAGNITUDE) + kp_z * r_error[2] + kd_z * v_error[2] + ki_z * m.i_error_z;
     // desired yaw from the setpoint quaternion (0, 0, qz, qw), in degrees
     const float sx = 0.0f, sy = 0.0f, sz = sp.qz, sw = sp.qw;
     // (fp32 product build: cos / sin of that angle are the atan2 arguments themselves, see below)
@@ -125,15 +126,15 @@ __device__ __forceinline__ void fw_mellinger(MelFw& m, const MelSetpoint& sp, fl
     e21 += zd2 * R21 - R22 * yd2; e02 += xd2 * R22 - R20 * zd2; e10 += yd2 * R20 - R21 * xd2;
     const float eR0 = e21, eR1 = -e02, eR2 = e10;
     const float rate_roll = fw_radians(gyro_deg[0]), rate_pitch = -fw_radians(gyro_deg[1]), rate_yaw = fw_radians(gyro_deg[2]);
-    const float ew0 = fw_radians(sp_rate_deg) - rate_roll, ew1 = -fw_radians(sp_rate_deg) - rate_pitch,
-                ew2 = fw_radians(sp_rate_deg) - rate_yaw;
-    float err_d_roll = (fw_radians(sp_rate_deg) - m.prev_setpoint_omega_roll) - (rate_roll - m.prev_omega_roll);
-    float err_d_pitch = -(fw_radians(sp_rate_deg) - m.prev_setpoint_omega_pitch) - (rate_pitch - m.prev_omega_pitch);
+    const float ew0 = fw_radians(sp.rate_deg[0]) - rate_roll, ew1 = -fw_radians(sp.rate_deg[1]) - rate_pitch,
+                ew2 = fw_radians(sp.rate_deg[2]) - rate_yaw;
+    float err_d_roll = (fw_radians(sp.rate_deg[0]) - m.prev_setpoint_omega_roll) - (rate_roll - m.prev_omega_roll);
+    float err_d_pitch = -(fw_radians(sp.rate_deg[1]) - m.prev_setpoint_omega_pitch) - (rate_pitch - m.prev_omega_pitch);
     if (M<T>::fast) { err_d_roll *= 500.0f; err_d_pitch *= 500.0f; }
     else { err_d_roll = err_d_roll / dt; err_d_pitch = err_d_pitch / dt; }
     m.prev_omega_roll = rate_roll; m.prev_omega_pitch = rate_pitch;
-    m.prev_setpoint_omega_roll = fw_radians(sp_rate_deg);
-    m.prev_setpoint_omega_pitch = fw_radians(sp_rate_deg);
+    m.prev_setpoint_omega_roll = fw_radians(sp.rate_deg[0]);
+    m.prev_setpoint_omega_pitch = fw_radians(sp.rate_deg[1]);
     m.i_error_m_x += (-eR0) * dt; m.i_error_m_x = fw_clampT<T>(m.i_error_m_x, -i_range_m_xy, i_range_m_xy);
     m.i_error_m_y += (-eR1) * dt; m.i_error_m_y = fw_clampT<T>(m.i_error_m_y, -i_range_m_xy, i_range_m_xy);
     m.i_error_m_z += (-eR2) * dt; m.i_error_m_z = fw_clampT<T>(m.i_error_m_z, -i_range_m_z, i_range_m_z);

@@ -51,7 +51,8 @@ race_reset_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ 
 
 // MultiRaceAviary.step (:171-270).  noise: NULL or (N, M, S, 7) = [wind force xyz (N), motor thrust noise x4 (N)].
 // MP: lanes per env at compile time (unrolled neighbour loops), 0 = read from the params.
-template <typename T, int MP>
+// FULL: 13-float (Command.FULLSTATE, args) actions (ADRP_ACT_MEL_FULL) instead of [x, y, z, yaw].
+template <typename T, int MP, bool FULL>
 __global__ void __launch_bounds__(kBlock)
 race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ RaceParams<T> RP, const KBuffers<T> b,
                  const RaceBuffers<T> rb, const T* __restrict__ action, const T* __restrict__ noise, T* __restrict__ obs,
@@ -99,12 +100,19 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
     const bool eliminated = (latch & ADRP_FLAG_ELIMINATED) != 0;
 
     // ---- ndarray action -> FULLSTATE(pos, 0, 0, yaw, 0, step_counter) (:190-202)
-    MelSetpoint sp = {{0.0f, 0.0f, 0.0f}, 0.0f, 1.0f};
+    MelSetpoint sp = {{0.0f, 0.0f, 0.0f}, 0.0f, 1.0f, {0.0f, 0.0f, 0.0f}, {0.0f, 0.0f, 0.0f}, {0.0f, 0.0f, 0.0f}};
     if (valid && !eliminated) {
-        const T* a = action + od * 4;
+        const T* a = action + od * (FULL ? 13 : 4);
         sp.pos[0] = (float)a[0]; sp.pos[1] = (float)a[1]; sp.pos[2] = (float)a[2];
+        if (FULL) {                                           // _sendFullStateCmd (MellingerControl.py:510-527)
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                sp.vel[k] = (float)a[3 + k]; sp.acc[k] = (float)a[6 + k];
+                sp.rate_deg[k] = (float)(a[10 + k] * (T)(180.0 / 3.14159265358979323846));
+            }
+        }
         T sy, cy;
-        const T yaw = (RP.wrappers & ADRP_WRAP_OBS) ? T(0) : a[3];   // DroneObservationWrapper.step (wrapper.py:52-57)
+        const T yaw = (RP.wrappers & ADRP_WRAP_OBS) ? T(0) : a[FULL ? 9 : 3];   // DroneObservationWrapper.step (wrapper.py:52-57)
         M<T>::sincos(yaw / T(2), &sy, &cy);                   // utils.get_quaternion_from_euler(0, 0, yaw)
         sp.qz = (float)sy; sp.qw = (float)cy;
     }

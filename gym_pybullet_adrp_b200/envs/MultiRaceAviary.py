@@ -11,7 +11,7 @@ import numpy as np
 
 from .. import _abi
 from ..utils.constants import CTRL_FREQ, FIRMWARE_FREQ
-from ..utils.enums import ActionType, DroneModel, ObservationType, Physics, RaceMode
+from ..utils.enums import ActionType, Command, DroneModel, ObservationType, Physics, RaceMode
 from ._spaces import Box
 from .BaseAviary import BaseAviary
 
@@ -38,6 +38,11 @@ class MultiRaceAviary(BaseAviary):
         init_rpys = np.array([race_config["init_states"][d]["rpy"] for d in names], dtype=float) * np.pi / 180   # :95
         self._physics_mask = batch.pop("physics_mask", None)
         self._wrappers = int(batch.pop("wrappers", 0))       # _abi.WRAP_* (utils/wrapper.py fused into the step kernel)
+        # (Command, args) tuple actions need the 13-float FULLSTATE rows (ADRP_ACT_MEL_FULL); the batched default is
+        # the 4-float [x, y, z, yaw] row the reference's ndarray path uses (:190-195)
+        full = batch.pop("full_state_actions", None)
+        self._full = (batch.get("num_envs", 1) == 1) if full is None else bool(full)
+        self._last_cmd = None
         super().__init__(drone_model=drone_model, num_drones=num_drones, initial_xyzs=init_xyzs, initial_rpys=init_rpys,
                          physics=physics, pyb_freq=pyb_freq, ctrl_freq=ctrl_freq, gui=gui, record=record, **batch)
 
@@ -47,7 +52,7 @@ class MultiRaceAviary(BaseAviary):
                                      ctrl_freq=self.CTRL_FREQ, racemode=self.racemode, precision=self.PRECISION,
                                      device=self.DEVICE, seed=self._seed or None, env_offset=self._env_offset,
                                      auto_reset=self._auto_reset, physics_mask=self._physics_mask,
-                                     wrappers=self._wrappers)
+                                     wrappers=self._wrappers, full_state_actions=self._full)
 
     # ------------------------------------------------------------------ spaces (:284-343)
     def _actionSpace(self):
@@ -73,12 +78,44 @@ class MultiRaceAviary(BaseAviary):
         self.step_counter = 0
         return self._out_obs(obs), self._computeInfo()
 
+    def _rows_from_commands(self, action):
+        """[(Command, args)] per drone -> (NUM_DRONES, 13) FULLSTATE rows (MultiRaceAviary.py:198-205)."""
+        if not self._full:
+            raise ValueError("(Command, args) actions need full_state_actions=True (13-float FULLSTATE rows)")
+        rows = np.zeros((self.NUM_DRONES, 13))
+        for i, (cmd, args) in enumerate(action):
+            if cmd == Command.FULLSTATE:                           # MellingerControl.sendFullStateCmd (:492-543)
+                pos, vel, acc, yaw, rpy_rate = args[:5]
+                rows[i] = np.r_[np.asarray(pos, float), np.asarray(vel, float), np.asarray(acc, float), float(yaw),
+                                np.asarray(rpy_rate, float)]
+            elif cmd in (Command.NONE, Command.STOP) and self._last_cmd is not None:
+                rows[i] = self._last_cmd[i]                        # no new command: the firmware keeps its setpoint
+            elif cmd in (Command.NONE, Command.STOP):
+                raise ValueError("Command.NONE before any FULLSTATE command: the firmware's power-on setpoint is not restated")
+            else:
+                # TAKEOFF / LAND / GOTO / NOTIFY run pycffirmware's high-level commander (crtpCommanderHighLevel*), which
+                # is not in the reference tree and whose planner is not restated (DESIGN.md section 9)
+                raise NotImplementedError(f"{cmd}: the firmware's high-level commander planner is not on this path")
+        self._last_cmd = rows.copy()
+        return rows
+
     def step(self, action, noise=None):
         """MultiRaceAviary.step (:171-270).  ``action``: ``(NUM_DRONES, 4)`` full-state setpoints [x, y, z, yaw]
-        (``(num_envs, NUM_DRONES, 4)`` when batched).  ``(Command, args)`` tuples need the firmware's high-level
-        commander, which is not on this path."""
-        if isinstance(action, (list, tuple)) and len(action) and isinstance(action[0], (list, tuple)):
-            raise NotImplementedError("(Command, args) actions need the high-level commander planner (next row, DESIGN.md)")
+        (``(num_envs, NUM_DRONES, 4)`` when batched), ``(..., 13)`` rows [pos, vel, acc, yaw, rpy_rates] with
+        ``full_state_actions=True``, or -- single env -- the reference's list of ``(Command.FULLSTATE, args)`` tuples."""
+        if isinstance(action, (list, tuple)) and len(action) and isinstance(action[0], (list, tuple)) \
+                and len(action[0]) == 2 and isinstance(action[0][0], Command):
+            if not self._single:
+                raise ValueError("(Command, args) tuples are the single-env interface; pass (num_envs, NUM_DRONES, 13) rows")
+            action = self._rows_from_commands(action)
+        elif self._full:
+            a = np.asarray(action.cpu() if hasattr(action, "cpu") else action, dtype=float)
+            if a.shape[-1] == 4:                                   # ndarray path: FULLSTATE(pos, 0, 0, yaw, 0) (:190-195)
+                full = np.zeros(a.shape[:-1] + (13,))
+                full[..., 0:3], full[..., 9] = a[..., 0:3], a[..., 3]
+                action = full
+            if self._single:
+                self._last_cmd = np.asarray(action, float).reshape(self.NUM_DRONES, 13).copy()
         h = self.handle
         obs, reward, terminated, truncated, self._last_flags = h.step(self._in_action(action), noise=noise)
         self.step_counter += self.PYB_STEPS_PER_CTRL

@@ -47,8 +47,10 @@ enum adrp_action_type {          /* utils/enums.py:40-47 + CtrlAviary */
     ADRP_ACT_ONE_D_PID = 4,      /* pos + 0.1*[0,0,a] -> DSLPIDControl     (BaseRLAviary.py:226-235) */
     ADRP_ACT_VEL = 5,            /* velocity command -> DSLPIDControl      (BaseRLAviary.py:208-223) */
     ADRP_ACT_MEL = 6,            /* [x,y,z,yaw] full-state setpoint -> Mellinger per substep (MultiRaceAviary.py:190-254) */
-    ADRP_ACT_PID_FULL = 7        /* [target_pos3, target_rpy3, target_vel3, target_rates3] -> DSLPIDControl.computeControl
+    ADRP_ACT_PID_FULL = 7,       /* [target_pos3, target_rpy3, target_vel3, target_rates3] -> DSLPIDControl.computeControl
                                     (control/DSLPIDControl.py:82-145), the examples/pid.py:138-147 driver loop fused */
+    ADRP_ACT_MEL_FULL = 8        /* (Command.FULLSTATE, args) tuples (MultiRaceAviary.py:198-205; MellingerControl.sendFullStateCmd,
+                                    :510-543): [pos3, vel3, acc3, yaw, rpy_rates3 (rad/s)] -> Mellinger per substep */
 };
 
 enum adrp_env_kind {

@@ -536,9 +536,15 @@ static void FN(race_step_env)(FN(orc)* h, int n, const REAL* action, const REAL*
     for (int i = 0; i < M; ++i) {
         FN(mel_state)* m = r->mel + (size_t)n * M + i;
         if (r->latch[(size_t)n * M + i] & ADRP_FLAG_ELIMINATED) continue;
-        const REAL* a = action + ((size_t)n * M + i) * 4;
+        const int full = c->action_type == ADRP_ACT_MEL_FULL;         /* (Command.FULLSTATE, (pos, vel, acc, yaw, rpy_rate, t)) */
+        const REAL* a = action + ((size_t)n * M + i) * h->A;
         for (int k = 0; k < 3; ++k) { m->sp_pos[k] = (float)a[k]; m->sp_vel[k] = 0; m->sp_acc[k] = 0; m->sp_rate_deg[k] = 0; }
-        REAL yaw = (c->wrappers & ADRP_WRAP_OBS) ? (REAL)0 : a[3];   /* wrapper.py:52-57; get_quaternion_from_euler(0, 0, yaw) (:525) */
+        if (full)                                                    /* _sendFullStateCmd (MellingerControl.py:510-527) */
+            for (int k = 0; k < 3; ++k) {
+                m->sp_vel[k] = (float)a[3 + k]; m->sp_acc[k] = (float)a[6 + k];
+                m->sp_rate_deg[k] = (float)(a[10 + k] * (REAL)(180.0 / 3.14159265358979323846));   /* RAD_TO_DEG */
+            }
+        REAL yaw = (c->wrappers & ADRP_WRAP_OBS) ? (REAL)0 : a[full ? 9 : 3];   /* wrapper.py:52-57; get_quaternion_from_euler(0, 0, yaw) (:525) */
         m->sp_quat[0] = (float)(SIN((REAL)0) * COS((REAL)0) * COS(yaw / 2) - COS((REAL)0) * SIN((REAL)0) * SIN(yaw / 2));
         m->sp_quat[1] = (float)(COS((REAL)0) * SIN((REAL)0) * COS(yaw / 2) + SIN((REAL)0) * COS((REAL)0) * SIN(yaw / 2));
         m->sp_quat[2] = (float)(COS((REAL)0) * COS((REAL)0) * SIN(yaw / 2) - SIN((REAL)0) * SIN((REAL)0) * COS(yaw / 2));

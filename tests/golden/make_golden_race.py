@@ -173,7 +173,47 @@ def wrapper_case(name, level, M, steps, seed):
     print(name, "steps:", n, "gates:", gate[n - 1].tolist(), "return:", rew[:n].sum(), "terminated:", term[n - 1])
 
 
+def fullstate_case(name, level, M, steps, seed):
+    """(Command.FULLSTATE, (pos, vel, acc, yaw, rpy_rate, t)) tuples as HardCodedController.predict sends them
+    (user_controller/HardCodedController.py:166-176): MultiRaceAviary.step (:198-205) -> MellingerControl.sendFullStateCmd
+    (:510-543) with non-zero velocity / acceleration / yaw / body-rate setpoints."""
+    from gym_pybullet_adrp.utils.enums import Command
+    cfg = munchify(json.loads(json.dumps(configs.builtin_config(level))))
+    rec = RecordingRNG(seed)
+    orig_uniform = np.random.uniform
+    np.random.uniform = rec.uniform
+    env = MultiRaceAviary(cfg, drone_model=DroneModel.CF2X, num_drones=M, physics=Physics.PYB, racemode=RaceMode.COMPARE)
+    env.np_random = rec
+    try:
+        obs0, _ = env.reset()
+        draws = np.array(rec.uniforms)
+        pos = gate_pass_setpoints(cfg, steps + 1, M)[:, :, :3]
+        act = np.zeros((steps, M, 13))
+        act[:, :, 0:3] = pos[:-1]
+        act[:, :, 3:6] = (pos[1:] - pos[:-1]) * 25.0                    # feed-forward velocity of the setpoint path
+        act[:, :, 6:9] = 0.5                                            # HardCodedController sends ones(3) * 0.5
+        act[:, :, 9] = 0.4 * np.sin(np.arange(steps) / 20.0)[:, None]   # yaw
+        act[:, :, 10:13] = 0.05 * np.cos(np.arange(steps) / 15.0)[:, None, None] * np.array([1.0, -1.0, 0.5])
+        obs = np.zeros((steps,) + obs0.shape)
+        term, trunc, gate = np.zeros(steps, bool), np.zeros(steps, bool), np.zeros((steps, M))
+        for k in range(steps):
+            cmds = [(Command.FULLSTATE, [act[k, i, 0:3].copy(), act[k, i, 3:6].copy(), act[k, i, 6:9].copy(), float(act[k, i, 9]),
+                                         act[k, i, 10:13].copy(), k / 25.0]) for i in range(M)]
+            o, r, te, tr, _ = env.step(cmds)
+            obs[k], term[k], trunc[k], gate[k] = o, te, tr, env.current_gate
+    finally:
+        np.random.uniform = orig_uniform
+        env.close()
+    meta = dict(env="race", level=level, physics="PYB", racemode="COMPARE", M=M, steps=steps, full_state_actions=True)
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), meta=json.dumps(meta), draws=draws, obs0=obs0, actions=act,
+                        obs=obs, terminated=term, truncated=trunc, current_gate=gate)
+    print(name, "gates:", gate[-1].tolist(), "terminated:", term[-1])
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "--fullstate":
+        fullstate_case("race_fullstate_compare_gs", "getting_started", 2, 200, 6)
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "--new":
         wrapper_case("race_wrappers_compare_gs", "getting_started", 2, 400, 5)
         return

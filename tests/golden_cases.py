@@ -55,6 +55,7 @@ def rel_err(a, b, floor=1.0):
     a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
     return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), floor)))
 
+FULLSTATE_CASES = ["race_fullstate_compare_gs"]          # (Command.FULLSTATE, args) tuples with vel / acc / yaw / rates
 WRAPPER_CASES = ["race_wrappers_compare_gs"]             # DroneObservationWrapper(RewardWrapper(MultiRaceAviary))
 RACE_CASES = ["race_pyb_compete_gs", "race_pyb_compare_level3", "race_dyn_compete_level1", "race_pyb_all_compete_level3"]
 

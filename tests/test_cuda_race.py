@@ -139,6 +139,28 @@ def test_race_batched_philox_fp64(M, racemode, physics):
     h.close(); o.close()
 
 
+@pytest.mark.parametrize("name", gc.FULLSTATE_CASES)
+@pytest.mark.parametrize("precision", [_abi.F64, _abi.F32])
+def test_race_fullstate_commands_golden(name, precision):
+    """ADRP_ACT_MEL_FULL ((Command.FULLSTATE, args) tuples: velocity / acceleration / yaw / body-rate setpoints)
+    against the reference's own run."""
+    meta, z = gc.load(name)
+    rc, cfg = gc.race_config_for(meta, precision=precision, full_state_actions=True)
+    h = _handle(cfg)
+    assert h.A == 13
+    h.reset(draws=gc.place_draws(rc, z["draws"], meta["M"])[None])
+    for k in range(meta["steps"] if precision == _abi.F64 else 25):
+        obs, rew, te, tr, fl = h.step(z["actions"][k][None])
+        o = obs.cpu().numpy()[0].astype(np.float64)
+        if precision == _abi.F64:
+            assert gc.rel_err(o, z["obs"][k]) < TOL64, (name, k)
+            np.testing.assert_array_equal(o[:, 48], z["current_gate"][k])
+        else:
+            assert np.abs(o[:, 0:3] - z["obs"][k][:, 0:3]).max() < TOL32, (name, k)
+            assert _ang_diff(o[:, 3:6], z["obs"][k][:, 3:6]).max() < TOL32, (name, k)
+    h.close()
+
+
 @pytest.mark.parametrize("name", gc.WRAPPER_CASES)
 @pytest.mark.parametrize("precision", [_abi.F64, _abi.F32])
 def test_race_wrappers_golden(name, precision):

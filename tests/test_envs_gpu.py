@@ -6,7 +6,7 @@ import pytest
 from gym_pybullet_adrp_b200 import configs
 from gym_pybullet_adrp_b200.control import DSLPIDControl
 from gym_pybullet_adrp_b200.envs import CtrlAviary, HoverAviary, MultiHoverAviary, MultiRaceAviary, VelocityAviary
-from gym_pybullet_adrp_b200.utils.enums import ActionType, DroneModel, Physics, RaceMode
+from gym_pybullet_adrp_b200.utils.enums import ActionType, Command, DroneModel, Physics, RaceMode
 from tests import golden_cases as gc
 
 pytestmark = pytest.mark.gpu
@@ -103,9 +103,32 @@ def test_multi_race_aviary_matches_reference_run():
         np.testing.assert_array_equal(env.drones_eliminated, z["eliminated"][k])
         np.testing.assert_array_equal(env.current_gate, z["current_gate"][k])
         assert reward == 0 and terminated == bool(z["terminated"][k]) and truncated == bool(z["truncated"][k])
-    with pytest.raises(NotImplementedError):
-        env.step([("fst", ())] * 2)
+    with pytest.raises(NotImplementedError, match="high-level commander"):
+        env.step([(Command.TAKEOFF, [0.3, 2])] * 2)                # the planner is not restated
     env.close()
+
+
+def test_multi_race_aviary_command_tuples_match_reference_run():
+    """HardCodedController-style actions: a list of (Command.FULLSTATE, [pos, vel, acc, yaw, rpy_rate, t]) per drone."""
+    meta, z = gc.load("race_fullstate_compare_gs")
+    rc = configs.load_config(meta["level"])
+    env = MultiRaceAviary(rc, num_drones=meta["M"], physics=Physics.PYB, racemode=RaceMode.COMPARE, precision="fp64")
+    env.reset(draws=gc.place_draws(rc, z["draws"], meta["M"])[None])
+    a = z["actions"]
+    for k in range(60):
+        cmds = [(Command.FULLSTATE, [a[k, i, 0:3], a[k, i, 3:6], a[k, i, 6:9], a[k, i, 9], a[k, i, 10:13], k / 25.0])
+                for i in range(meta["M"])]
+        obs, reward, terminated, truncated, info = env.step(cmds)
+        assert gc.rel_err(obs, z["obs"][k]) < 1e-9, k
+    obs_none, *_ = env.step([(Command.NONE, [])] * meta["M"])           # no new command: the last setpoint stays
+    env.close()
+    env2 = MultiRaceAviary(rc, num_drones=meta["M"], physics=Physics.PYB, racemode=RaceMode.COMPARE, precision="fp64")
+    env2.reset(draws=gc.place_draws(rc, z["draws"], meta["M"])[None])
+    for k in range(60):
+        env2.step(a[k])                                                  # (M, 13) rows, same thing
+    obs_rep, *_ = env2.step(a[59])
+    np.testing.assert_array_equal(obs_none, obs_rep)
+    env2.close()
 
 
 def test_wrapper_classes_match_reference_run():

@@ -122,6 +122,22 @@ def test_race_env_fp64(name):
         assert rew[0] == 0
 
 
+@pytest.mark.parametrize("name", gc.FULLSTATE_CASES)
+def test_race_fullstate_commands_fp64(name):
+    """(Command.FULLSTATE, (pos, vel, acc, yaw, rpy_rate, t)) tuples through the reference's MultiRaceAviary.step and
+    MellingerControl.sendFullStateCmd: ADRP_ACT_MEL_FULL rows [pos3, vel3, acc3, yaw, rates3]."""
+    meta, z = gc.load(name)
+    rc, cfg = gc.race_config_for(meta, full_state_actions=True)
+    env = OracleEnv(cfg)
+    env.reset(draws=gc.place_draws(rc, z["draws"], meta["M"])[None])
+    for k in range(meta["steps"]):
+        obs, rew, te, tr, fl = env.step(z["actions"][k][None])
+        assert gc.rel_err(obs[0], z["obs"][k]) < TOL64, (name, k)
+        np.testing.assert_array_equal(obs[0][:, 48], z["current_gate"][k])
+        assert bool(te[0]) == bool(z["terminated"][k]) and bool(tr[0]) == bool(z["truncated"][k])
+    assert z["current_gate"][-1].max() >= 1                      # the recorded flight does pass a gate
+
+
 @pytest.mark.parametrize("name", gc.WRAPPER_CASES)
 def test_race_wrappers_fp64(name):
     """utils/wrapper.py as run by the reference on its own env: shaped reward of drone 0 (gate progress, +5 per gate),
