@@ -98,3 +98,29 @@ def test_wrapper_classes_surface():
     assert base._make_config().wrappers == (_abi.WRAP_OBS | _abi.WRAP_REWARD)
     with pytest.raises(TypeError, match="MultiRaceAviary"):
         RewardWrapper(HoverAviary())
+
+
+def test_eval_driver_host_pieces(tmp_path):
+    """scripts/sim.py helpers that need no GPU: Logger layout (utils/logger.py:100-113), load_controller, action rows."""
+    import os
+    from gym_pybullet_adrp_b200.scripts import sim
+    from gym_pybullet_adrp_b200.utils.enums import Command
+    from gym_pybullet_adrp_b200.utils.logger import Logger
+    from gym_pybullet_adrp_b200.utils.utils import load_controller, map2pi
+    log = Logger(logging_freq_hz=25, output_folder=str(tmp_path), num_drones=2)
+    for k in range(3):
+        for i in range(2):
+            log.log(i, k / 25, np.arange(20.0) + 100 * i)
+    z = np.load(log.save())
+    assert z["timestamps"].shape == (2, 3) and z["states"].shape == (2, 16, 3) and z["controls"].shape == (2, 12, 3)
+    # pos, vel, rpy, ang_vel, rpm out of the 20-float state row [pos3 quat4 rpy3 vel3 ang_vel3 rpm4]
+    np.testing.assert_array_equal(z["states"][1, :, 2], 100 + np.r_[0:3, 10:13, 7:10, 13:20])
+    here = os.path.dirname(os.path.abspath(sim.__file__))
+    cls = load_controller(os.path.join(here, "..", "user_controller", "HoverController.py"))
+    assert cls(1).predict(None).tolist() == [1.5, 0.5, 2, 0]
+    row = sim._row((Command.FULLSTATE, [[1, 2, 3], [4, 5, 6], [7, 8, 9], 0.25, [0.1, 0.2, 0.3], 0.0]))
+    assert row.tolist() == [1, 2, 3, 4, 5, 6, 7, 8, 9, 0.25, 0.1, 0.2, 0.3]
+    assert sim._row(np.array([1.0, 2.0, 3.0, 0.5])).tolist() == [1, 2, 3] + [0] * 6 + [0.5, 0, 0, 0]
+    with pytest.raises(NotImplementedError):
+        sim._row((Command.TAKEOFF, [0.3, 2]))
+    assert abs(map2pi(3 * np.pi / 2) + np.pi / 2) < 1e-12

@@ -172,3 +172,33 @@ def test_torch_vec_env_rollout():
     assert int(finished.min()) >= 1 and torch.isfinite(obs).all()      # 80 steps at 30 Hz > 1 s episodes: everyone reset
     assert int(venv.episode_lengths.max()) <= 31
     venv.close()
+
+
+def test_batched_eval_driver(tmp_path):
+    """scripts/sim.py:18-107 over parallel runs: per-agent host controllers and the on-device predict_batch give the
+    same episode times; the flight of one run lands in the reference Logger's .npy layout."""
+    import glob
+    from gym_pybullet_adrp_b200.scripts.sim import simulate
+    from gym_pybullet_adrp_b200.user_controller import HoverController
+    rc = configs.load_config("getting_started")
+    rc["episode_len_sec"] = 1.2
+
+    class HostOnlyHover(HoverController):                     # no predict_batch: forces the per-agent path
+        predict_batch = None
+    del HostOnlyHover.predict_batch
+
+    class PerAgent(HoverController.__mro__[1]):
+        def predict(self, obs, reward=None, done=None, info=None, ep_time=None):
+            return np.array([1.5, 0.5, 1 + self.drone_id, 0])
+
+    t_host = simulate(rc, PerAgent, n_runs=3, n_drones=2, precision="fp64", log_env=1, output_folder=str(tmp_path))
+    t_dev = simulate(rc, HoverController, n_runs=3, n_drones=2, precision="fp64")
+    assert t_host == t_dev and len(t_host) == 3
+    # hovering towards the setpoint: the runs end by truncation, in the first env step k with k * 20 / 500 > 1.2 s
+    # (k = 31); like the reference the driver counts time in the CONFIG's ctrl_freq (sim.py:79), 30 Hz here
+    assert all(abs(t - 31 / rc["ctrl_freq"]) < 1e-12 for t in t_host)
+    files = glob.glob(str(tmp_path / "save-flight-*.npy"))
+    assert len(files) == 1
+    z = np.load(files[0])
+    assert z["states"].shape[0] == 2 and z["states"].shape[1] == 16 and z["states"].shape[2] >= 29
+    assert z["states"][0, 2, -1] > z["states"][0, 2, 0]        # it climbed
