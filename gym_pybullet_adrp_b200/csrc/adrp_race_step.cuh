@@ -34,19 +34,24 @@ race_reset_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ 
     }
     if (!obs) return;
     __syncthreads();                                           // track written above is read back below
-    if (valid && !mine) load_drone(b, P.Dpad, t, d);
-    if (!valid) init_drone(P, 0, d);
     const long long env0 = (long long)blockIdx.x * EPB;
     for (int idx = threadIdx.x; idx < RP.TF * EPB; idx += kBlock) {
         const int f = idx / EPB, el = idx - f * EPB;
         trk[idx] = env0 + el < P.N ? rb.track[(long long)f * P.N + env0 + el] : T(0);
     }
     __syncthreads();
+    // MultiRaceAviary.reset (:143-144): the returned observation comes from BaseAviary.reset, BEFORE
+    // _drone_init randomises the drones -- the nominal INIT_XYZS / INIT_RPYS (config rpy * pi/180, :95) at rest, seen
+    // against the already randomised track
+    const int id = valid ? i : 0;
+    d.p = {P.init_xyz[id][0], P.init_xyz[id][1], P.init_xyz[id][2]};
+    d.q = canon_quat(quat_from_rpy(V3<T>{RP.mel_prev_rpy[id][0], RP.mel_prev_rpy[id][1], RP.mel_prev_rpy[id][2]}));
+    d.v = d.w = d.rt = {T(0), T(0), T(0)};
     const V3<T> rpy = euler_rpy(d.q);
     const T hz = drone_half_height(P.coll_r, P.coll_h, rotmat(d.q).m22);
     T* o = obs + (valid ? env * P.M + i : 0) * P.O;
     const bool wr = mine;
-    race_write_obs(P, RP, trk, EPB, e, d, rpy, hz, wr ? (rb.gate_latch[t] & 0xffff) : 0, i, lane - i, wr, o);
+    race_write_obs(P, RP, trk, EPB, e, d, rpy, hz, 0, i, lane - i, wr, o);
 }
 
 // MultiRaceAviary.step (:171-270).  noise: NULL or (N, M, S, 7) = [wind force xyz (N), motor thrust noise x4 (N)].

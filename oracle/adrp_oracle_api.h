@@ -49,7 +49,26 @@ static void FN(reset)(FN(orc)* h, const uint8_t* mask, const REAL* draws, REAL* 
     if (obs)
         for (int n = 0; n < h->N; ++n) {
             if (mask && !mask[n]) continue;
-            if (h->race) FN(race_write_obs)(h, n, obs); else FN(write_obs)(h, n, obs);
+            if (!h->race) { FN(write_obs)(h, n, obs); continue; }
+            /* MultiRaceAviary.reset (:143-144): initial_obs comes from BaseAviary.reset, BEFORE _drone_init
+             * randomises the drones -- nominal INIT_XYZS / INIT_RPYS (= config rpy * pi/180, :95) at rest, seen against
+             * the already randomised track. */
+            REAL keep[ADRP_MAX_DRONES * 20];
+            REAL* env = h->state + (size_t)n * h->M * 20;
+            memcpy(keep, env, sizeof(REAL) * 20 * h->M);
+            for (int i = 0; i < h->M; ++i) {
+                REAL* st = env + 20 * i;
+                REAL e[3];
+                for (int k = 0; k < 20; ++k) st[k] = 0;
+                for (int k = 0; k < 3; ++k) {
+                    st[k] = (REAL)h->cfg.init_xyz[i][k];
+                    e[k] = (REAL)(h->cfg.init_rpy[i][k] * (3.14159265358979323846 / 180.0));
+                }
+                FN(quat_from_euler)(e, st + 3);
+                FN(pose_round_trip)(st + 3);
+            }
+            FN(race_write_obs)(h, n, obs);
+            memcpy(env, keep, sizeof(REAL) * 20 * h->M);
         }
 }
 

@@ -33,7 +33,8 @@ def test_race_golden_fp64(name):
     meta, z = gc.load(name)
     rc, cfg = gc.race_config_for(meta, precision=_abi.F64)
     h = _handle(cfg)
-    h.reset(draws=gc.place_draws(rc, z["draws"], meta["M"])[None])
+    obs0 = h.reset(draws=gc.place_draws(rc, z["draws"], meta["M"])[None]).cpu().numpy()
+    assert gc.rel_err(obs0[0], z["obs0"]) < TOL64                   # nominal pose, randomised track
     st = h.get_state().cpu().numpy()[0]
     assert np.abs(st[:, 0:7] - z["state0"][:, 0:7]).max() < 1e-12
     worst = 0.0

@@ -106,7 +106,8 @@ def test_race_env_fp64(name):
     meta, z = gc.load(name)
     rc, cfg = gc.race_config_for(meta)
     env = OracleEnv(cfg)
-    env.reset(draws=gc.place_draws(rc, z["draws"], meta["M"])[None])
+    obs0 = env.reset(draws=gc.place_draws(rc, z["draws"], meta["M"])[None])
+    assert gc.rel_err(obs0[0], z["obs0"]) < TOL64                   # nominal pose, randomised track
     st = env.get_state()[0]
     assert np.abs(st[:, 0:7] - z["state0"][:, 0:7]).max() < 1e-12
     worst = 0.0
