@@ -192,6 +192,57 @@ def test_batched_vs_oracle(physics, precision, tol):
     h.close(); o.close()
 
 
+@pytest.mark.parametrize("precision,tol", [(_abi.F64, 1e-9), (_abi.F32, 2e-4)])
+@pytest.mark.parametrize("M", [2, 5, 8, 16, 17, 32])
+@pytest.mark.parametrize("physics", [Physics.PYB_DW, Physics.DYN_GND_DRAG_DW])
+def test_downwash_lane_widths(M, physics, precision, tol):
+    """Every lanes-per-env specialisation (2 .. 32, padded and full) with a LIVE downwash term: a vertical stack with
+    centimetre lateral offsets, so each drone feels several drones above it (0.02 - 0.05 N each, weight 0.34 N).
+    The fp32 build evaluates every unordered pair once and hands the share back over a shuffle; the oracle loops
+    over ordered pairs like the reference (:805-811)."""
+    N = 19
+    rng = np.random.default_rng(M)
+    xyz = [[0.05 * (i % 3), 0.04 * (i % 2), 0.3 + 0.9 * i] for i in range(M)]
+    cfg = _abi.make_config(num_envs=N, num_drones=M, physics=physics, pyb_freq=240, ctrl_freq=48,
+                           action_type=_abi.ACT_RPM_RAW, env_kind=_abi.ENV_CTRL, precision=precision, initial_xyzs=xyz)
+    h, o = _handle(cfg), OracleEnv(cfg)
+    h.reset(); o.reset()
+    st = o.get_state().astype(np.float64)
+    st[:, :, 0:2] += rng.uniform(-0.02, 0.02, (N, M, 2))
+    st[:, :, 2] += rng.uniform(-0.1, 0.1, (N, M))
+    h.set_state(st); o.set_state(st)
+    hover = float(np.sqrt(9.8 * 0.03454 / (4 * 3.16e-10)))
+    z0 = o.get_state()[:, :, 2].copy()
+    for k in range(12):
+        a = hover * (1 + 0.003 * rng.uniform(-1, 1, (N, M, 4)))
+        og = h.step(a)[0].cpu().numpy()
+        oc = o.step(a, nthreads=4)[0]
+        assert gc.rel_err(og, oc) < tol, (M, physics, k, gc.rel_err(og, oc))
+    # the term is live: on average the lowest drone has sunk by centimetres relative to the top one (no downwash there)
+    dz = o.get_state()[:, :, 2] - z0
+    assert dz[:, 0].mean() < dz[:, M - 1].mean() - 5e-3
+    h.close(); o.close()
+
+
+@pytest.mark.parametrize("N,M", [(1, 1), (1, 3), (2, 32), (131, 1)])
+def test_ragged_batch_shapes(N, M):
+    """Batches that do not fill a warp or a thread block: one env, one drone, a full warp per env, odd env counts."""
+    rng = np.random.default_rng(N * 100 + M)
+    xyz = [[1.3 * (i % 6), 1.3 * (i // 6), 0.5 + 0.01 * i] for i in range(M)]
+    cfg = _abi.make_config(num_envs=N, num_drones=M, physics=Physics.PYB_GND_DRAG_DW, pyb_freq=240, ctrl_freq=30,
+                           action_type=_abi.ACT_RPM_RAW, env_kind=_abi.ENV_CTRL, precision=_abi.F64, initial_xyzs=xyz)
+    h, o = _handle(cfg), OracleEnv(cfg)
+    h.reset(); o.reset()
+    hover = float(np.sqrt(9.8 * 0.03454 / (4 * 3.16e-10)))
+    for k in range(6):
+        a = hover * (1 + 0.01 * rng.uniform(-1, 1, (N, M, 4)))
+        obs, rew, te, tr, fl = h.step(a)
+        oc = o.step(a)[0]
+        assert obs.shape == (N, M, 20) and rew.shape == (N,) and fl.shape == (N, M)
+        assert gc.rel_err(obs.cpu().numpy(), oc) < TOL64, (N, M, k)
+    h.close(); o.close()
+
+
 def test_host_path_matches_device_path():
     cfg = _abi.make_config(num_envs=33, num_drones=2, physics=Physics.PYB, pyb_freq=240, ctrl_freq=48,
                            action_type=_abi.ACT_RPM_RAW, env_kind=_abi.ENV_CTRL, precision=_abi.F32)

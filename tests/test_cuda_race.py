@@ -264,6 +264,37 @@ def test_race_reset_mask_and_obs():
     h.close(); o.close()
 
 
+@pytest.mark.parametrize("G,NO,N,M", [(8, 8, 21, 2), (1, 0, 1, 1), (0, 0, 3, 2), (4, 4, 5, 7)])
+def test_race_track_sizes_and_ragged_batches(G, NO, N, M):
+    """Maximum track (ADRP_MAX_GATES / ADRP_MAX_OBSTACLES), a single gate, no track at all (the reference returns an
+    all-zero observation without gates, MultiRaceAviary.py:598-600 -- here the kinematic part is kept), one env of
+    one drone, seven drones per env (padded lanes)."""
+    rc = configs.load_config("level3")
+    g0 = [list(map(float, g)) for g in rc["gates"]]
+    o0 = [list(map(float, b)) for b in rc["obstacles"]]
+    gates = [[g0[k % 4][0] + 0.3 * (k // 4), g0[k % 4][1] - 0.4 * (k // 4), g0[k % 4][2], 0, 0, g0[k % 4][5] + 0.2 * (k // 4), g0[k % 4][6]]
+             for k in range(G)]
+    obst = [[o0[k % 4][0] - 0.35 * (k // 4), o0[k % 4][1] + 0.45 * (k // 4), o0[k % 4][2], 0, 0, 0] for k in range(NO)]
+    rc["gates"], rc["obstacles"] = gates, obst
+    for i in range(M):
+        rc["init_states"][f"drone{i}"] = configs.configify({"pos": [0.9 + 0.35 * (i % 4), 0.9 + 0.35 * (i // 4), 0.05],
+                                                           "vel": [0, 0, 0], "rpy": [0, 0, 0], "pqr": [0, 0, 0]})
+    cfg = _abi.make_race_config(rc, num_envs=N, num_drones=M, physics=Physics.PYB, racemode=RaceMode.COMPETE,
+                                precision=_abi.F64, seed=9)
+    h, o = _handle(cfg), OracleEnv(cfg)
+    assert h.O == 12 + 5 * G + 4 * NO + 1 + 6 * (M - 1)
+    np.testing.assert_allclose(h.reset().cpu().numpy(), o.reset(), rtol=0, atol=1e-12)
+    rng = np.random.default_rng(G + NO)
+    for k in range(12):
+        a = _random_setpoints(rng, cfg, N, M, k)
+        obs, rew, te, tr, fl = h.step(a)
+        obs_o, rew_o, te_o, tr_o, fl_o = o.step(a)
+        assert gc.rel_err(obs.cpu().numpy(), obs_o) < TOL64, (G, NO, k)
+        np.testing.assert_array_equal(fl.cpu().numpy(), fl_o)
+        np.testing.assert_array_equal(te.cpu().numpy(), te_o)
+    h.close(); o.close()
+
+
 def test_race_rejects_wrong_action_type():
     from gym_pybullet_adrp_b200 import _lib
     cfg = _abi.make_config(num_envs=2, action_type=_abi.ACT_MEL, env_kind=_abi.ENV_CTRL)
