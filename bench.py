@@ -135,8 +135,29 @@ def algorithmic_bytes_per_drone_step(wl, O, A, M):
     return per_drone + per_env / M
 
 
-# algorithmic flops per substep-update (reading estimates, +-20 %)
+# algorithmic work of the restated path.  MECHANICAL COUNT of the frozen oracle (oracle/flopcount.py:
+# the oracle's own statements compiled with counting arithmetic types, run on these workloads):
+#   (flops per substep-update, SFU ops per substep-update, flops per control step, SFU ops per control step)
+# flops = add + sub + mul + compare (a multiply-add counts 2); SFU = div, sqrt, sin/cos, atan2, asin, exp, log.
+# tests/test_oracle_golden.py::test_flop_table_is_the_mechanical_count keeps this table equal to the counter's output.
+MECHANICAL_OPS = {
+    "c5": (480.0, 46.5, 32.0, 3.0),
+    "c4": (570.0, 54.5, 32.0, 3.0),
+    "c2": (428.0, 25.0, 80.0, 7.0),
+    "c3": (825.1, 89.8, 2782.9, 306.2),
+    "c5m": (1000.3, 118.5, 125.6, 38.1),
+}
+
+
 def algorithmic_flops_per_substep(wl):
+    """flops per substep-update including the per-control-step part spread over the S substeps."""
+    S = WORKLOADS[wl][3] // WORKLOADS[wl][4]
+    sub, _, step, _ = MECHANICAL_OPS[wl]
+    return sub + step / S
+
+
+def reading_estimate_flops_per_substep(wl):
+    """SURVEY 8(d)'s reading estimate (+-20 %), kept beside the mechanical count for the record."""
     N, M, physics, pyb, ctrl, kind, act, _ = WORKLOADS[wl]
     phy = _abi.PHYSICS_MASK[physics]
     fl = 160 if phy & _abi.PHY_DYN else 200
@@ -376,6 +397,8 @@ def main():
                          "kernel_ms": kernel_ms, "algorithmic_bytes_per_drone_step": bpd},
             "fp32_roofline": {"achieved": fp32_ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": fp32_ach / fp32_peak if fp32_ach else None,
                               "algorithmic_flops_per_substep_update": fps,
+                              "sfu_ops_per_substep_update": MECHANICAL_OPS[wl][1] + MECHANICAL_OPS[wl][3] / S,
+                              "count": "mechanical (oracle/flopcount.py); SURVEY reading estimate: %d" % reading_estimate_flops_per_substep(wl),
                               "peak_source": "measured live: adrp_fp32_peak_tflops (16 FMA chains per thread)"},
             "e2e": {"value": e2e_value, "unit": "drone-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps},

@@ -182,3 +182,22 @@ def test_mellinger_schedule_known_answer():
         else:
             fired += "1"
     assert all((a == "1") == (b == "1") for a, b in zip(want, fired))
+
+
+def test_flop_table_is_the_mechanical_count():
+    """bench.py's roofline numerators are the mechanical operation count of the oracle (oracle/flopcount.py: the same
+    statements compiled with counting arithmetic types), not reading estimates."""
+    import json, os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    subprocess.run(["make", "-s", "-C", os.path.join(root, "oracle"), "liboracle_count.so"], check=True)
+    out = subprocess.run([sys.executable, os.path.join(root, "oracle", "flopcount.py"), "--json"], check=True,
+                         capture_output=True, text=True).stdout
+    rows = json.loads(out)
+    sys.path.insert(0, root)
+    import bench
+    key = {"c5": "C5:", "c4": "C4:", "c2": "C2:", "c3": "C3:", "c5m": "C5M:"}
+    for wl, (sub_f, sub_s, step_f, step_s) in bench.MECHANICAL_OPS.items():
+        r = next(v for k, v in rows.items() if k.startswith(key[wl]))
+        got = (r["per_substep_update"]["flops"], r["per_substep_update"]["sfu"], r["per_control_step"]["flops"], r["per_control_step"]["sfu"])
+        for g, w in zip(got, (sub_f, sub_s, step_f, step_s)):
+            assert abs(g - w) <= 0.01 * max(abs(w), 10.0), (wl, got)
