@@ -105,7 +105,7 @@ void derive_params(const adrp_config& c, KParams<T>& P)
     P.physics = c.physics; P.drone_model = c.drone_model; P.action_type = c.action_type; P.env_kind = c.env_kind;
     P.race_mode = c.race_mode; P.auto_reset = c.auto_reset; P.pid_model = c.dslpid_model;
     P.Dpad = (long long)P.N * P.Mpad;
-    P.env_begin = 0; P.env_end = P.N;
+    P.env_begin = 0; P.env_end = P.N; P.obs_vec = 0; P.act_vec = 0;
     P.pyb_freq = c.pyb_freq;
     // step_counter / PYB_FREQ > EPISODE_LEN_SEC, evaluated like Python does (double division)
     int ts = 0;
@@ -289,6 +289,8 @@ int do_step(Handle<T>* h, const T* action, const T* noise, T* obs, T* reward, ui
 {
     KParams<T> P = h->P;
     P.env_begin = env_begin; P.env_end = env_end < 0 ? P.N : env_end;
+    P.obs_vec = sizeof(T) == 4 && (P.O % 4) == 0 && (P.A == 4 || P.env_kind == ADRP_ENV_CTRL) && ((uintptr_t)obs & 15) == 0;
+    P.act_vec = sizeof(T) == 4 && P.A == 4 && ((uintptr_t)action & 15) == 0;
     if (h->profiling) {
         if (h->ev_pending) {          // harvest the previous launch's time before re-recording the events
             float ms = 0;

@@ -19,6 +19,8 @@ struct KParams {
     int physics, drone_model, action_type, env_kind, race_mode, auto_reset, pid_model;
     long long Dpad;                       // N * Mpad
     int env_begin, env_end;               // env range of THIS launch (chunked host path); the whole shard otherwise
+    int obs_vec;                          // this launch may write observation rows with 16-byte stores (fp32, rows and base 16 B aligned)
+    int act_vec;                          // ... and read 4-float action rows with one 16-byte load
     int pyb_freq;
     int trunc_steps;                      // smallest step_counter with step_counter/PYB_FREQ > EPISODE_LEN_SEC
     // BaseAviary constants (envs/BaseAviary.py:74-128)

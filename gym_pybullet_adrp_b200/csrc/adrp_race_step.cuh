@@ -108,7 +108,13 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
     MelSetpoint sp = {{0.0f, 0.0f, 0.0f}, 0.0f, 1.0f, {0.0f, 0.0f, 0.0f}, {0.0f, 0.0f, 0.0f}, {0.0f, 0.0f, 0.0f}};
     if (valid && !eliminated) {
         const T* a = action + od * (FULL ? 13 : 4);
-        sp.pos[0] = (float)a[0]; sp.pos[1] = (float)a[1]; sp.pos[2] = (float)a[2];
+        T a_yaw;
+        if (M<T>::fast && !FULL && P.act_vec) {               // one 16-byte load per drone instead of four strided ones
+            const float4 a4 = *reinterpret_cast<const float4*>(a);
+            sp.pos[0] = a4.x; sp.pos[1] = a4.y; sp.pos[2] = a4.z; a_yaw = (T)a4.w;
+        } else {
+            sp.pos[0] = (float)a[0]; sp.pos[1] = (float)a[1]; sp.pos[2] = (float)a[2]; a_yaw = a[FULL ? 9 : 3];
+        }
         if (FULL) {                                           // _sendFullStateCmd (MellingerControl.py:510-527)
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
@@ -117,7 +123,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
             }
         }
         T sy, cy;
-        const T yaw = (RP.wrappers & ADRP_WRAP_OBS) ? T(0) : a[FULL ? 9 : 3];   // DroneObservationWrapper.step (wrapper.py:52-57)
+        const T yaw = (RP.wrappers & ADRP_WRAP_OBS) ? T(0) : a_yaw;          // DroneObservationWrapper.step (wrapper.py:52-57)
         M<T>::sincos(yaw / T(2), &sy, &cy);                   // utils.get_quaternion_from_euler(0, 0, yaw)
         sp.qz = (float)sy; sp.qw = (float)cy;
     }

@@ -91,8 +91,13 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
     const T* a = action + od * P.A;
     constexpr int AMAX = ACTC == 0 ? 4 : 12;             // RPM-type actions have at most 4 components
     T act_in[AMAX];
+    if (M<T>::fast && P.act_vec && AMAX == 4) {               // one 16-byte load per drone instead of four strided ones
+        const float4 a4 = valid ? *reinterpret_cast<const float4*>(a) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        act_in[0] = (T)a4.x; act_in[1] = (T)a4.y; act_in[2] = (T)a4.z; act_in[3] = (T)a4.w;
+    } else {
 #pragma unroll
-    for (int k = 0; k < AMAX; ++k) act_in[k] = (valid && k < P.A) ? a[k] : T(0);
+        for (int k = 0; k < AMAX; ++k) act_in[k] = (valid && k < P.A) ? a[k] : T(0);
+    }
     PidState<T> pc;
     if (ACTC == 0) {
         if (P.action_type == ADRP_ACT_RPM_RAW) {
@@ -170,8 +175,18 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
     const V3<T> rpy = euler_rpy(d.q);
     T* o = obs + od * P.O;
     int head = 0;
+    // fp32 build: rows whose length is a multiple of 4 floats go out as 16-byte stores (a warp's scalar store of one
+    // column touches 32 sectors for 128 useful bytes; the float4 form moves 4x the payload per sector access)
+    const bool vec = M<T>::fast && P.obs_vec;
     if (P.env_kind == ADRP_ENV_CTRL) {
-        if (valid) {
+        if (valid && vec) {
+            float4* o4 = reinterpret_cast<float4*>(o);
+            o4[0] = make_float4((float)d.p.x, (float)d.p.y, (float)d.p.z, (float)d.q.x);
+            o4[1] = make_float4((float)d.q.y, (float)d.q.z, (float)d.q.w, (float)rpy.x);
+            o4[2] = make_float4((float)rpy.y, (float)rpy.z, (float)d.v.x, (float)d.v.y);
+            o4[3] = make_float4((float)d.v.z, (float)d.w.x, (float)d.w.y, (float)d.w.z);
+            o4[4] = make_float4((float)d.last_rpm[0], (float)d.last_rpm[1], (float)d.last_rpm[2], (float)d.last_rpm[3]);
+        } else if (valid) {
             o[0] = d.p.x; o[1] = d.p.y; o[2] = d.p.z; o[3] = d.q.x; o[4] = d.q.y; o[5] = d.q.z; o[6] = d.q.w;
             o[7] = rpy.x; o[8] = rpy.y; o[9] = rpy.z; o[10] = d.v.x; o[11] = d.v.y; o[12] = d.v.z;
             o[13] = d.w.x; o[14] = d.w.y; o[15] = d.w.z;
@@ -179,8 +194,15 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
             for (int k = 0; k < 4; ++k) o[16 + k] = d.last_rpm[k];
         }
     } else if (valid) {
-        o[0] = d.p.x; o[1] = d.p.y; o[2] = d.p.z; o[3] = rpy.x; o[4] = rpy.y; o[5] = rpy.z;
-        o[6] = d.v.x; o[7] = d.v.y; o[8] = d.v.z; o[9] = d.w.x; o[10] = d.w.y; o[11] = d.w.z;
+        if (vec) {
+            float4* o4 = reinterpret_cast<float4*>(o);
+            o4[0] = make_float4((float)d.p.x, (float)d.p.y, (float)d.p.z, (float)rpy.x);
+            o4[1] = make_float4((float)rpy.y, (float)rpy.z, (float)d.v.x, (float)d.v.y);
+            o4[2] = make_float4((float)d.v.z, (float)d.w.x, (float)d.w.y, (float)d.w.z);
+        } else {
+            o[0] = d.p.x; o[1] = d.p.y; o[2] = d.p.z; o[3] = rpy.x; o[4] = rpy.y; o[5] = rpy.z;
+            o[6] = d.v.x; o[7] = d.v.y; o[8] = d.v.z; o[9] = d.w.x; o[10] = d.w.y; o[11] = d.w.z;
+        }
         // action buffer (deque(maxlen=ctrl_freq//2), BaseRLAviary.py:66-67,187): the newest action
         // overwrites the oldest ring slot; the observation lists the slots oldest -> newest
         head = b.ring_head[env];
@@ -188,10 +210,20 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
         for (int k = 0; k < AMAX; ++k)
             if (k < P.A) st(b.ring, D, head * P.A + k, t, act_in[k]);
         const int nh = head + 1 == P.B ? 0 : head + 1;
-        for (int j = 0; j < P.B; ++j) {
-            int slot = nh + j;
-            if (slot >= P.B) slot -= P.B;
-            for (int k = 0; k < P.A; ++k) o[12 + j * P.A + k] = ld(b.ring, D, slot * P.A + k, t);
+        if (vec) {                                             // P.A == 4: one 16-byte store per ring slot
+            float4* o4 = reinterpret_cast<float4*>(o) + 3;
+            for (int j = 0; j < P.B; ++j) {
+                int slot = nh + j;
+                if (slot >= P.B) slot -= P.B;
+                o4[j] = make_float4((float)ld(b.ring, D, slot * 4, t), (float)ld(b.ring, D, slot * 4 + 1, t),
+                                    (float)ld(b.ring, D, slot * 4 + 2, t), (float)ld(b.ring, D, slot * 4 + 3, t));
+            }
+        } else {
+            for (int j = 0; j < P.B; ++j) {
+                int slot = nh + j;
+                if (slot >= P.B) slot -= P.B;
+                for (int k = 0; k < P.A; ++k) o[12 + j * P.A + k] = ld(b.ring, D, slot * P.A + k, t);
+            }
         }
         head = nh;
     }
