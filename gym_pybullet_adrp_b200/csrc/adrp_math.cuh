@@ -116,6 +116,11 @@ template <> struct M<double> {
 __device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
 __device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
 
+// Value barrier: the compiler may not assume anything about v afterwards (keeps a rarely needed recomputation inside
+// its branch instead of being merged with, and hoisted next to, the hot path's common subexpressions).
+__device__ __forceinline__ void opaque(float& v) { asm volatile("" : "+f"(v)); }
+__device__ __forceinline__ void opaque(double& v) { asm volatile("" : "+d"(v)); }
+
 template <typename T> __device__ __forceinline__ T clampT(T v, T lo, T hi) { return v < lo ? lo : (v > hi ? hi : v); }
 
 template <typename T> struct V3 { T x, y, z; };

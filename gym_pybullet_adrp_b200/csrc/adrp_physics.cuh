@@ -36,8 +36,7 @@ __device__ __forceinline__ void ground_effect(const KParams<T>& P, const Drone<T
         for (int i = 0; i < 4; ++i) {
             T h = d.p.z + R.m20 * P.prop_x[i] + R.m21 * P.prop_y[i];
             h = M<T>::fmax(h, P.gnd_eff_h_clip);
-            const T r = P.qr4 * M<T>::rcp(h);
-            gnd[i] = on ? mul_rn(rpm2kf[i] * P.gnd_eff_coeff, r * r) : T(0);
+            gnd[i] = on ? mul_rn(rpm2kf[i] * (P.gnd_eff_coeff * P.qr4 * P.qr4), M<T>::rcp(h * h)) : T(0);
         }
         return;
     }
@@ -62,6 +61,12 @@ __device__ __forceinline__ V3<T> drag_force(const KParams<T>& P, const Drone<T>&
         sum = (T(2) * T(3.141592653589793) * d.last_rpm[0] / T(60) + T(2) * T(3.141592653589793) * d.last_rpm[1] / T(60)) +
               T(2) * T(3.141592653589793) * d.last_rpm[2] / T(60) + T(2) * T(3.141592653589793) * d.last_rpm[3] / T(60);
     }
+    return {-P.drag_xy * sum * d.v.x, -P.drag_xy * sum * d.v.y, -P.drag_z * sum * d.v.z};
+}
+
+template <typename T>
+__device__ __forceinline__ V3<T> drag_force_sum(const KParams<T>& P, const Drone<T>& d, T sum)
+{
     return {-P.drag_xy * sum * d.v.x, -P.drag_xy * sum * d.v.y, -P.drag_z * sum * d.v.z};
 }
 
@@ -207,7 +212,11 @@ __device__ __forceinline__ void dyn_substep(const KParams<T>& P, Drone<T>& d, co
         // the pose round trip through Bullet only renormalises and fixes the sign: _integrateQ is linear in q and
         // every consumer inside the loop normalises by |q|^2, so the product build applies it once per control
         // step (step kernel epilogue); the world rates are needed after the last substep only
-        if (last) d.w = mul(rotmat_loop(q), d.rt);        // (the loop itself reads the third row / column of R only)
+        if (last) {                                        // (the loop itself reads the third row / column of R only)
+            Q4<T> ql = q;
+            opaque(ql.x); opaque(ql.y); opaque(ql.z); opaque(ql.w);
+            d.w = mul(rotmat_loop(ql), d.rt);
+        }
         return;
     }
     const T wn = M<T>::sqrt(wn2);

@@ -144,6 +144,8 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
     T f0[4], tq[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) { f0[k] = mul_rn(rpm[k] * rpm[k], P.kf); tq[k] = mul_rn(rpm[k] * rpm[k], P.km); }
+    const T drag_sum_prev = T(0.10471975511965977) * ((d.last_rpm[0] + d.last_rpm[1]) + (d.last_rpm[2] + d.last_rpm[3]));   // 2 pi / 60
+    const T drag_sum_cur = T(0.10471975511965977) * ((rpm[0] + rpm[1]) + (rpm[2] + rpm[3]));
     for (int s = 0; s < P.S; ++s) {
         const Mat3<T> R = rotmat_loop(d.q);
         T f[4] = {f0[0], f0[1], f0[2], f0[3]};
@@ -154,7 +156,10 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
             for (int k = 0; k < 4; ++k) f[k] += gnd[k];
         }
         V3<T> fext = {T(0), T(0), T(0)};
-        if (phy & ADRP_PHY_DRAG) fext = drag_force(P, d);   // last_clipped_action: the previous step's RPM during the first substep (:363,:376)
+        if (phy & ADRP_PHY_DRAG) {                         // last_clipped_action: the previous step's RPM during the first substep (:363,:376)
+            if (M<T>::fast) fext = drag_force_sum(P, d, s == 0 ? drag_sum_prev : drag_sum_cur);
+            else fext = drag_force(P, d);
+        }
         T dw = T(0);
         if (phy & ADRP_PHY_DW) dw = downwash<T, MP>(P, d.p, lane_base, valid);
         if (phy & ADRP_PHY_DYN) {
@@ -166,13 +171,21 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
                               tq[0] - tq[1] + tq[2] - tq[3]};                   // :703
             pyb_substep(P, phy, d, R, fz, tb, fext, P.pyb_mass, P.pyb_jx, P.pyb_jy, P.pyb_jz);
         }
+        if (!M<T>::fast) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) d.last_rpm[k] = rpm[k];                      // :376
+            for (int k = 0; k < 4; ++k) d.last_rpm[k] = rpm[k];                  // :376
+        }
+    }
+    if (M<T>::fast) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) d.last_rpm[k] = rpm[k];                      // :376 (S >= 1)
     }
     if (M<T>::fast) d.q = canon_quat_loop(d.q);          // once per control step in the product build (adrp_physics.cuh)
 
-    // ---- observation (CtrlAviary.py:106-117; BaseRLAviary.py:284-322)
-    const V3<T> rpy = euler_rpy(d.q);
+    // ---- observation (CtrlAviary.py:106-117; BaseRLAviary.py:284-322).  CtrlAviary has no flag that depends on the
+    // Euler angles, so the product build may use the loop's polynomial atan2 there (1 ulp); the RL aviaries threshold
+    // |roll|, |pitch| and keep libm, so that their flags stay a bit-exact function of the stored state
+    const V3<T> rpy = P.env_kind == ADRP_ENV_CTRL ? euler_rpy_loop(d.q) : euler_rpy(d.q);
     T* o = obs + od * P.O;
     int head = 0;
     // fp32 build: rows whose length is a multiple of 4 floats go out as 16-byte stores (a warp's scalar store of one
