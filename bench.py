@@ -189,33 +189,52 @@ def ncu_traffic_bytes(wl, n_envs):
 
 
 class ClockSampler(threading.Thread):
+    """Polls NVML (SM clock + throttle reasons) for the duration of the timed region.  NVML is initialised in the
+    constructor (before the region starts) and polled every millisecond, so that even a 20 ms region is sampled."""
+
+    NAMES = {"nvmlClocksThrottleReasonHwSlowdown": "hw_slowdown",
+             "nvmlClocksThrottleReasonHwThermalSlowdown": "hw_thermal_slowdown",
+             "nvmlClocksThrottleReasonSwThermalSlowdown": "sw_thermal_slowdown",
+             "nvmlClocksThrottleReasonSwPowerCap": "sw_power_cap"}
+
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.stop_flag, self.samples, self.reasons, self.max_mhz = index, False, [], set(), None
-
-    def run(self):
+        self.stop_flag, self.samples, self.reasons, self.max_mhz = False, [], set(), None
+        self.nv = self.h = None
         try:
             import pynvml as nv
             nv.nvmlInit()
-            h = nv.nvmlDeviceGetHandleByIndex(self.index)
-            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
-            names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
-                     nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
-                     nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
-                     nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+            # LOCAL_RANK indexes CUDA_VISIBLE_DEVICES; NVML enumerates the whole box
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            phys = vis.split(",")[index] if vis else str(index)
+            self.h = nv.nvmlDeviceGetHandleByIndex(int(phys)) if phys.isdigit() else nv.nvmlDeviceGetHandleByUUID(phys)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
+            self.names = {getattr(nv, k): v for k, v in self.NAMES.items()}
+            self.nv = nv
+        except Exception as e:  # noqa: BLE001
+            self.reasons.add(f"nvml_unavailable:{type(e).__name__}")
+
+    def poll(self):
+        nv, h = self.nv, self.h
+        self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+        r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+        for bit, name in self.names.items():
+            if r & bit:
+                self.reasons.add(name)
+
+    def run(self):
+        if self.nv is None:
+            return
+        try:
             while not self.stop_flag:
-                self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
-                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
-                for bit, name in names.items():
-                    if r & bit:
-                        self.reasons.add(name)
-                time.sleep(0.02)
+                self.poll()
+                time.sleep(0.001)
         except Exception as e:  # noqa: BLE001
             self.reasons.add(f"nvml_unavailable:{type(e).__name__}")
 
     def result(self):
         return {"sm_mhz": float(np.median(self.samples)) if self.samples else None, "sm_max_mhz": self.max_mhz,
-                "reasons": sorted(self.reasons)}
+                "samples": len(self.samples), "reasons": sorted(self.reasons)}
 
 
 def cpu_port_rate(wl, n_envs_sample, steps, threads):
@@ -323,6 +342,8 @@ def main():
     for k in range(args.steps):
         h.step(acts_dev[k % pool])
     e1.record()
+    if sampler.nv is not None and not sampler.samples:
+        sampler.poll()                                   # the queue is still draining: a sample under load
     barrier()
     sampler.stop_flag = True
     launches = h.launch_count - l0
