@@ -10,7 +10,7 @@ static_assert(kBlock == 128, "adrp_api.cu cuts host-path chunks in units of 128-
 inline unsigned grid_for(long long D) { return (unsigned)((D + kBlock - 1) / kBlock); }
 
 template <typename T>
-inline size_t race_smem_bytes(const KParams<T>& P, const RaceParams<T>& RP) { return sizeof(T) * (size_t)RP.TF * (kBlock / P.Mpad); }
+inline size_t race_smem_bytes(const KParams<T>& P, const RaceParams<T>& RP, int block = kBlock) { return sizeof(T) * (size_t)RP.TF * (block / P.Mpad); }
 
 // DSLPIDControl.computeControl for n independent rows (control/DSLPIDControl.py:82-145).
 template <typename T>
@@ -104,7 +104,7 @@ cudaError_t Launch<T>::race_prepare(const RaceParams<T>& RP, const KParams<T>& P
 {
     const size_t bytes = race_smem_bytes(P, RP);
     if (bytes <= 48 * 1024) return cudaSuccess;
-    cudaError_t e = cudaFuncSetAttribute(race_step_fn<T>(P.Mpad, P.action_type == ADRP_ACT_MEL_FULL), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    cudaError_t e = cudaFuncSetAttribute(race_step_fn<T>(P.Mpad, P.action_type == ADRP_ACT_MEL_FULL), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)race_smem_bytes(P, RP, kRaceBlock));
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(race_reset_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
 }
@@ -122,7 +122,7 @@ cudaError_t Launch<T>::race_step(const KParams<T>& P, const RaceParams<T>& RP, c
                                  const T* action, const T* noise, T* obs, T* reward, uint8_t* te, uint8_t* tr,
                                  uint8_t* fl, cudaStream_t s)
 {
-    race_step_fn<T>(P.Mpad, P.action_type == ADRP_ACT_MEL_FULL)<<<grid_for((long long)(P.env_end - P.env_begin) * P.Mpad), kBlock, race_smem_bytes(P, RP), s>>>(P, RP, b, rb, action, noise, obs, reward, te, tr, fl);
+    race_step_fn<T>(P.Mpad, P.action_type == ADRP_ACT_MEL_FULL)<<<(unsigned)(((long long)(P.env_end - P.env_begin) * P.Mpad + kRaceBlock - 1) / kRaceBlock), kRaceBlock, race_smem_bytes(P, RP, kRaceBlock), s>>>(P, RP, b, rb, action, noise, obs, reward, te, tr, fl);
     return cudaGetLastError();
 }
 

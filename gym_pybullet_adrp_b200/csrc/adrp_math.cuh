@@ -69,6 +69,25 @@ template <> struct M<float> {
         if (x < 0.0f) r = 3.141592653589793f - r;
         return copysignf(r, y);
     }
+    // asin for the substep loop: Cephes asinf kernel, x + x z p(z) on |x| <= 0.5 (the usual case: pitch below 30 degrees),
+    // pi/2 - 2 asin(sqrt((1 - |x|) / 2)) beyond; ~1 ulp
+    static __device__ __forceinline__ float asin_poly(float x, float z)
+    {
+        float p = 4.2163199048e-2f;
+        p = p * z + 2.4181311049e-2f;
+        p = p * z + 4.5470025998e-2f;
+        p = p * z + 7.4953002686e-2f;
+        p = p * z + 1.6666752422e-1f;
+        return x + (x * z) * p;
+    }
+    static __device__ __forceinline__ float asin_loop(float x)
+    {
+        const float a = fabsf(x);
+        if (a <= 0.5f) return asin_poly(x, x * x);
+        const float z = 0.5f * (1.0f - a);
+        const float r = 1.5707963267948966f - 2.0f * asin_poly(fsqrt(z), z);
+        return copysignf(r, x);
+    }
     // cos(th) and sin(th)/th from z = th^2 (both even in th: no square root, no division); valid for z <= (pi/4)^2
     static __device__ __forceinline__ void cos_sinc_sq(float z, float* c, float* sinc)
     {
@@ -101,6 +120,7 @@ template <> struct M<double> {
     static __device__ __forceinline__ void sincos_small(double x, double* s, double* c) { ::sincos(x, s, c); }
     static __device__ __forceinline__ double clamp(double v, double lo, double hi) { return v < lo ? lo : (v > hi ? hi : v); }
     static __device__ __forceinline__ double atan2_loop(double y, double x) { return ::atan2(y, x); }
+    static __device__ __forceinline__ double asin_loop(double x) { return ::asin(x); }
     static __device__ __forceinline__ void cos_sinc_sq(double z, double* c, double* sinc)
     {
         const double th = ::sqrt(z);
@@ -193,6 +213,17 @@ template <typename T> __device__ __forceinline__ V3<T> euler_rpy_loop(const Q4<T
     if (sarg >= T(0.99999)) return {T(0), HALF_PI, T(2) * M<T>::atan2(-q.x, q.y)};
     return {M<T>::atan2_loop(T(2) * (q.y * q.z + q.w * q.x), squ - sqx - sqy + sqz), M<T>::asin(sarg),
             M<T>::atan2_loop(T(2) * (q.x * q.y + q.w * q.z), squ + sqx - sqy - sqz)};
+}
+
+// euler_rpy for the fast build's substep loop, read off R = rotmat_loop(q) (already there for the force models):
+// m21 : m22 = 2(yz + wx) : (w^2 - x^2 - y^2 + z^2), -m20 = sarg / |q|^2, m10 : m00 = 2(xy + wz) : (w^2 + x^2 - y^2 - z^2).
+template <typename T> __device__ __forceinline__ V3<T> euler_rpy_rot(const Q4<T>& q, const Mat3<T>& R)
+{
+    const T sarg = -R.m20;
+    const T HALF_PI = T(1.5707963267948966);
+    if (sarg <= T(-0.99999)) return {T(0), -HALF_PI, T(2) * M<T>::atan2(q.x, -q.y)};
+    if (sarg >= T(0.99999)) return {T(0), HALF_PI, T(2) * M<T>::atan2(-q.x, q.y)};
+    return {M<T>::atan2_loop(R.m21, R.m22), M<T>::asin_loop(sarg), M<T>::atan2_loop(R.m10, R.m00)};
 }
 
 // |roll| < pi/2 and |pitch| < pi/2 (the _groundEffect gate, envs/BaseAviary.py:749) without

@@ -72,7 +72,7 @@ __device__ __forceinline__ float fw_lpf2p(float b0, float b1, float b2, float a1
 // controllerMellinger() with mode.x/y/z/quat = modeAbs, roll/pitch/yaw = modeDisable.
 template <typename T>
 __device__ __forceinline__ void fw_mellinger(MelFw& m, const MelSetpoint& sp, float mass, const float pos[3],
-                                             const float vel[3], const float q[4], const float gyro_deg[3])
+                                             const float vel[3], const float q[4], const Mat3<T>& Rq, const float gyro_deg[3])
 {
     const float massThrust = 132000.0f;
     const float kp_xy = 0.4f, kd_xy = 0.2f, ki_xy = 0.05f, i_range_xy = 2.0f;
@@ -94,10 +94,18 @@ __device__ __forceinline__ void fw_mellinger(MelFw& m, const MelSetpoint& sp, fl
     const float sx = 0.0f, sy = 0.0f, sz = sp.qz, sw = sp.qw;
     // (fp32 product build: cos / sin of that angle are the atan2 arguments themselves, see below)
     const float dy_s = 2.0f * (sw * sz + sx * sy), dy_c = 1 - 2 * (sy * sy + sz * sz);
-    const float x = q[0], y = q[1], z = q[2], w = q[3];
-    const float R00 = 1 - 2 * y * y - 2 * z * z, R01 = 2 * x * y - 2 * z * w, R02 = 2 * x * z + 2 * y * w;
-    const float R10 = 2 * x * y + 2 * z * w, R11 = 1 - 2 * x * x - 2 * z * z, R12 = 2 * y * z - 2 * x * w;
-    const float R20 = 2 * x * z - 2 * y * w, R21 = 2 * y * z + 2 * x * w, R22 = 1 - 2 * x * x - 2 * y * y;
+    float R00, R01, R02, R10, R11, R12, R20, R21, R22;
+    if (M<T>::fast) {
+        // the substep's rotation matrix (shared with the force models and the Euler angles): the firmware's
+        // quat2rotmat of a unit quaternion is the same matrix
+        R00 = (float)Rq.m00; R01 = (float)Rq.m01; R02 = (float)Rq.m02; R10 = (float)Rq.m10; R11 = (float)Rq.m11;
+        R12 = (float)Rq.m12; R20 = (float)Rq.m20; R21 = (float)Rq.m21; R22 = (float)Rq.m22;
+    } else {
+        const float x = q[0], y = q[1], z = q[2], w = q[3];
+        R00 = 1 - 2 * y * y - 2 * z * z; R01 = 2 * x * y - 2 * z * w; R02 = 2 * x * z + 2 * y * w;
+        R10 = 2 * x * y + 2 * z * w; R11 = 1 - 2 * x * x - 2 * z * z; R12 = 2 * y * z - 2 * x * w;
+        R20 = 2 * x * z - 2 * y * w; R21 = 2 * y * z + 2 * x * w; R22 = 1 - 2 * x * x - 2 * y * y;
+    }
     const float current_thrust = tt[0] * R02 + tt[1] * R12 + tt[2] * R22;
     const float nt = M<T>::fast ? M<float>::fsqrt(tt[0] * tt[0] + tt[1] * tt[1] + tt[2] * tt[2]) : sqrtf(tt[0] * tt[0] + tt[1] * tt[1] + tt[2] * tt[2]);
     float zd0, zd1, zd2;
@@ -156,6 +164,21 @@ __device__ __forceinline__ void fw_mellinger(MelFw& m, const MelSetpoint& sp, fl
 // (tick/500 - last/500 > 0.002) exactly as Python evaluates it in float64 (:395-411): always true for a gap
 // of two or more ticks, never for a gap of zero; for a gap of one it depends on the rounding of tick/500,
 // which the host tabulates once (bit `tick` of lut).
+// Fast build: the S schedule bits of one control step, fetched once before the substep loop (the tick advances by
+// exactly one per substep).  ok == false (window not inside the table): per-tick evaluation as below.
+struct MelWindow { uint32_t bits; bool ok; };
+template <typename T>
+__device__ __forceinline__ MelWindow mel_schedule_window(const RaceParams<T>& RP, const uint32_t* __restrict__ lut, int tick0, int S)
+{
+    MelWindow w = {0u, false};
+    if (S <= 32 && tick0 >= 0 && tick0 + 64 <= RP.lut_ticks) {
+        const uint32_t lo = __ldg(lut + (tick0 >> 5)), hi = __ldg(lut + (tick0 >> 5) + 1);
+        w.bits = __funnelshift_r(lo, hi, tick0 & 31);
+        w.ok = true;
+    }
+    return w;
+}
+
 template <typename T>
 __device__ __forceinline__ bool mel_schedule_fires(const RaceParams<T>& RP, const uint32_t* __restrict__ lut, int tick, int last)
 {
@@ -169,10 +192,11 @@ __device__ __forceinline__ bool mel_schedule_fires(const RaceParams<T>& RP, cons
 template <typename T>
 __device__ __forceinline__ void mellinger_tick(const RaceParams<T>& RP, const uint32_t* __restrict__ lut, Mel<T>& m,
                                                const MelSetpoint& sp, const V3<T>& p, const Q4<T>& q, const V3<T>& v,
-                                               const T noise4[4])
+                                               const T noise4[4], const Mat3<T>& Rq, const MelWindow win, int s)
 {
     const T FIRMWARE_DT = (T)(1.0 / 500), RAD_TO_DEG = (T)(180.0 / 3.14159265358979323846), DEG_TO_RAD = (T)(3.14159265358979323846 / 180.0);
-    const V3<T> rpy = euler_rpy_loop(q);                                         // obs[i, 3:6] (:242)
+    // obs[i, 3:6] (:242); Rq: rotmat_loop(q), valid in the fast build only
+    const V3<T> rpy = M<T>::fast ? euler_rpy_rot(q, Rq) : euler_rpy_loop(q);
     T rates[3], acc_z;
     float qf[4];
     if (M<T>::fast) {
@@ -204,30 +228,57 @@ __device__ __forceinline__ void mellinger_tick(const RaceParams<T>& RP, const ui
     for (int k = 0; k < 3; ++k)
         gyro[k] = fw_lpf2p(RP.lpf_b0, RP.lpf_b1, RP.lpf_b2, RP.lpf_a1, RP.lpf_a2, m.gd1[k], m.gd2[k], (float)(rates[k] * RAD_TO_DEG));
     // _step_controller (:378-419)
-    T pwms[4] = {T(0), T(0), T(0), T(0)};
     if (m.acc_z < -0.5f) m.tumble += 1; else m.tumble = 0;                       // :382-385
-    if (m.tumble >= 30) {
+    const bool stop = m.tumble >= 30;
+    if (stop) {
         m.tick += 1; m.error = 1;                                                // :387-391: zero PWM
     } else {
-        if (mel_schedule_fires(RP, lut, m.tick, m.last_att)) {
+        const int gap = m.tick - m.last_att;
+        const bool fires = (M<T>::fast && win.ok) ? (gap != 1 ? gap > 1 : ((win.bits >> s) & 1u) != 0u)
+                                                  : mel_schedule_fires(RP, lut, m.tick, m.last_att);
+        if (fires) {
             m.last_att = m.tick;
-            fw_mellinger<T>(m.fw, sp, RP.mel_mass, pos, vel, qf, gyro);
+            fw_mellinger<T>(m.fw, sp, RP.mel_mass, pos, vel, qf, Rq, gyro);
         }
         m.tick += 1;
-        // _compute_pwms (:423-442)
-        const T r = (T)m.fw.roll * T(0.5), pp = (T)m.fw.pitch * T(0.5), y = (T)m.fw.yaw, t = (T)m.fw.thrust;
-        const T th[4] = {t - r + pp + y, t - r - pp - y, t + r - pp + y, t + r + pp - y};
+    }
+    // _compute_pwms (:423-442)
+    const T r = (T)m.fw.roll * T(0.5), pp = (T)m.fw.pitch * T(0.5), y = (T)m.fw.yaw, t = (T)m.fw.thrust;
+    const T th[4] = {t - r + pp + y, t - r - pp - y, t + r - pp + y, t + r + pp - y};
+    const T KF = T(3.16e-10), SCALE = T(0.2685), CONST = T(4070.3);
+    if (M<T>::fast) {
+        // Same chain with the constants folded: battery curve volts / 3 * 65535 = x (A x + B); min(pct, 1) * 65535 and the
+        // PWM clamp of :246 are one clamp; thrust -> (+ noise) -> _thr2pwm -> RPM is sqrt(rp^2 + noise / KF) clamped to the
+        // RPM images of the PWM limits (SCALE > 0: the maps are monotone).
+        const T A = T(-0.0006239 * 65535.0 / 3.0), B = T(0.088 * 65535.0 / 3.0);
+        const T RPM_LO = T(0.2685 * 20000.0 + 4070.3), RPM_HI = T(0.2685 * 65535.0 + 4070.3);
+        T rp[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const T x = M<T>::fast ? M<T>::clamp(th[k], T(0), T(65535)) * T(60.0 / 65535.0) : clampT(th[k], T(0), T(65535)) / T(65535) * T(60);
+            const T x = M<T>::clamp(th[k], T(0), T(65535)) * T(60.0 / 65535.0);
+            T pw = x * (A * x + B);
+            if (stop) pw = T(0);
+            rp[k] = SCALE * M<T>::clamp(pw, T(20000), T(65535)) + CONST;
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {                                            // thrust[[3,2,1,0]] + disturbance (:250-253)
+            const T r2 = rp[3 - k] * rp[3 - k] + noise4[k] * T(1.0 / 3.16e-10);
+            m.rpms[k] = M<T>::clamp(M<T>::fsqrt(M<T>::fmax(r2, T(0))), RPM_LO, RPM_HI);
+        }
+        return;
+    }
+    T pwms[4] = {T(0), T(0), T(0), T(0)};
+    if (!stop) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const T x = clampT(th[k], T(0), T(65535)) / T(65535) * T(60);
             const T volts = T(-0.0006239) * (x * x) + T(0.088) * x;
-            const T v3 = M<T>::fast ? volts * T(1.0 / 3.0) : volts / T(3);
-            const T pct = M<T>::fast ? M<T>::fmin(v3, T(1)) : (v3 < T(1) ? v3 : T(1));
+            const T v3 = volts / T(3);
+            const T pct = v3 < T(1) ? v3 : T(1);
             pwms[k] = pct * T(65535);
         }
     }
     // :246-262
-    const T KF = T(3.16e-10), SCALE = T(0.2685), CONST = T(4070.3);
     T thrust[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
@@ -238,8 +289,8 @@ __device__ __forceinline__ void mellinger_tick(const RaceParams<T>& RP, const ui
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         T tk = thrust[3 - k] + noise4[k];                                        // thrust[[3,2,1,0]] + disturbance (:250-253)
-        if (M<T>::fast) tk = M<T>::fmax(tk, T(0)); else if (tk < T(0)) tk = T(0);  // _thr2pwm (:307-343)
-        T pwm = M<T>::fast ? (M<T>::fsqrt(tk * T(1.0 / 3.16e-10)) - CONST) * T(1.0 / 0.2685) : (M<T>::sqrt(tk / T(1) / KF) - CONST) / SCALE;
+        if (tk < T(0)) tk = T(0);                                                // _thr2pwm (:307-343)
+        T pwm = (M<T>::sqrt(tk / T(1) / KF) - CONST) / SCALE;
         pwm = M<T>::clamp(pwm, T(20000), T(65535));
         m.rpms[k] = SCALE * pwm + CONST;
     }

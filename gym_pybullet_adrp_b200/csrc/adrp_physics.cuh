@@ -237,26 +237,35 @@ template <typename T>
 __device__ __forceinline__ void pyb_substep(const KParams<T>& P, int phy, Drone<T>& d, const Mat3<T>& R, T fz,
                                             const V3<T>& tb, const V3<T>& fext, T m, T jx, T jy, T jz)
 {
-    // world -> base frame
     const V3<T> fw = {R.m02 * fz + fext.x, R.m12 * fz + fext.y, R.m22 * fz + fext.z - m * P.g};
-    const V3<T> f_l = mulT(R, fw), v_l = mulT(R, d.v), w_l = mulT(R, d.w);
-    const T vn = M<T>::fsqrt(dot(v_l, v_l)), wn = M<T>::fsqrt(dot(w_l, w_l));
-    const V3<T> Jw = {jx * w_l.x, jy * w_l.y, jz * w_l.z};
-    const V3<T> gy = cross(w_l, Jw);
-    const T kl = P.lin_damp + P.lin_damp * vn, ka = P.ang_damp + P.ang_damp * wn;
-    V3<T> a_l, al_l;
     if (M<T>::fast) {
-        const T im = M<T>::rcp(m);
-        a_l = {f_l.x * im - v_l.x * kl, f_l.y * im - v_l.y * kl, f_l.z * im - v_l.z * kl};
-        al_l = {(tb.x - Jw.x * ka - gy.x) * M<T>::rcp(jx), (tb.y - Jw.y * ka - gy.y) * M<T>::rcp(jy),
-                (tb.z - Jw.z * ka - gy.z) * M<T>::rcp(jz)};
+        // Bullet updates the base in its own frame: a_w = R (R^T F / m - kl R^T v).  R is orthonormal (rotmat_loop
+        // divides by |q|^2), so the linear part is F / m - kl v with |R^T v| = |v| -- three matrix-vector products
+        // less; only the angular part needs the base frame (diagonal inertia).
+        const V3<T> w_l = mulT(R, d.w);
+        const T vn = M<T>::fsqrt(dot(d.v, d.v)), wn = M<T>::fsqrt(dot(w_l, w_l));
+        const V3<T> Jw = {jx * w_l.x, jy * w_l.y, jz * w_l.z};
+        const V3<T> gy = cross(w_l, Jw);
+        const T kl = P.lin_damp + P.lin_damp * vn, ka = P.ang_damp + P.ang_damp * wn;
+        const T im = M<T>::rcp(m), dkl = T(1) - P.dt * kl, dim = P.dt * im;
+        const V3<T> al_l = {(tb.x - Jw.x * ka - gy.x) * M<T>::rcp(jx), (tb.y - Jw.y * ka - gy.y) * M<T>::rcp(jy),
+                            (tb.z - Jw.z * ka - gy.z) * M<T>::rcp(jz)};
+        const V3<T> al_w = mul(R, al_l);
+        d.v = {d.v.x * dkl + dim * fw.x, d.v.y * dkl + dim * fw.y, d.v.z * dkl + dim * fw.z};
+        d.w = {d.w.x + P.dt * al_w.x, d.w.y + P.dt * al_w.y, d.w.z + P.dt * al_w.z};
     } else {
-        a_l = {(f_l.x - m * v_l.x * kl) / m, (f_l.y - m * v_l.y * kl) / m, (f_l.z - m * v_l.z * kl) / m};
-        al_l = {(tb.x - Jw.x * ka - gy.x) / jx, (tb.y - Jw.y * ka - gy.y) / jy, (tb.z - Jw.z * ka - gy.z) / jz};
+        // world -> base frame
+        const V3<T> f_l = mulT(R, fw), v_l = mulT(R, d.v), w_l = mulT(R, d.w);
+        const T vn = M<T>::fsqrt(dot(v_l, v_l)), wn = M<T>::fsqrt(dot(w_l, w_l));
+        const V3<T> Jw = {jx * w_l.x, jy * w_l.y, jz * w_l.z};
+        const V3<T> gy = cross(w_l, Jw);
+        const T kl = P.lin_damp + P.lin_damp * vn, ka = P.ang_damp + P.ang_damp * wn;
+        const V3<T> a_l = {(f_l.x - m * v_l.x * kl) / m, (f_l.y - m * v_l.y * kl) / m, (f_l.z - m * v_l.z * kl) / m};
+        const V3<T> al_l = {(tb.x - Jw.x * ka - gy.x) / jx, (tb.y - Jw.y * ka - gy.y) / jy, (tb.z - Jw.z * ka - gy.z) / jz};
+        const V3<T> a_w = mul(R, a_l), al_w = mul(R, al_l);
+        d.v = {d.v.x + P.dt * a_w.x, d.v.y + P.dt * a_w.y, d.v.z + P.dt * a_w.z};
+        d.w = {d.w.x + P.dt * al_w.x, d.w.y + P.dt * al_w.y, d.w.z + P.dt * al_w.z};
     }
-    const V3<T> a_w = mul(R, a_l), al_w = mul(R, al_l);
-    d.v = {d.v.x + P.dt * a_w.x, d.v.y + P.dt * a_w.y, d.v.z + P.dt * a_w.z};
-    d.w = {d.w.x + P.dt * al_w.x, d.w.y + P.dt * al_w.y, d.w.z + P.dt * al_w.z};
     d.p = {d.p.x + P.dt * d.v.x, d.p.y + P.dt * d.v.y, d.p.z + P.dt * d.v.z};
     // exponential map (btMultiBody::stepPositionsMultiDof)
     const T w2 = dot(d.w, d.w);

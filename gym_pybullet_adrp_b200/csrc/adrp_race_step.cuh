@@ -3,6 +3,23 @@
 
 namespace adrp {
 
+// Block shape of race_step_kernel.  The kernel needs ~170 registers per thread, so the register file holds 12 warps
+// per SM (3 blocks of 128: without the bound ptxas takes 178 and the third block is lost); ADRP_RACE_BLOCK /
+// ADRP_RACE_MINB exist to measure other operating points.
+#ifndef ADRP_RACE_BLOCK
+#define ADRP_RACE_BLOCK 128
+#endif
+#ifndef ADRP_RACE_MINB
+#define ADRP_RACE_MINB 3
+#endif
+constexpr int kRaceBlock = ADRP_RACE_BLOCK, kRaceMinBlocks = ADRP_RACE_MINB;
+#ifdef ADRP_RACE_MAXNREG
+#define ADRP_RACE_BOUNDS __maxnreg__(ADRP_RACE_MAXNREG)
+#else
+#define ADRP_RACE_BOUNDS __launch_bounds__(kRaceBlock, kRaceMinBlocks)
+#endif
+static_assert(kBlock % kRaceBlock == 0 && kRaceBlock % 32 == 0, "host-path chunks are cut in units of kBlock threads");
+
 // Env.reset for the masked envs (MultiRaceAviary.reset, :127-167); writes the initial observation if asked.
 template <typename T>
 __global__ void __launch_bounds__(kBlock)
@@ -58,7 +75,7 @@ race_reset_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ 
 // MP: lanes per env at compile time (unrolled neighbour loops), 0 = read from the params.
 // FULL: 13-float (Command.FULLSTATE, args) actions (ADRP_ACT_MEL_FULL) instead of [x, y, z, yaw].
 template <typename T, int MP, bool FULL>
-__global__ void __launch_bounds__(kBlock)
+__global__ void ADRP_RACE_BOUNDS
 race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ RaceParams<T> RP, const KBuffers<T> b,
                  const RaceBuffers<T> rb, const T* __restrict__ action, const T* __restrict__ noise, T* __restrict__ obs,
                  T* __restrict__ reward, uint8_t* __restrict__ terminated, uint8_t* __restrict__ truncated,
@@ -67,12 +84,12 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T* trk = reinterpret_cast<T*>(smem_raw);
     const int mpad = MP > 0 ? MP : P.Mpad;
-    const long long t = (long long)P.env_begin * mpad + (long long)blockIdx.x * kBlock + threadIdx.x;
+    const long long t = (long long)P.env_begin * mpad + (long long)blockIdx.x * kRaceBlock + threadIdx.x;
     const int lane = threadIdx.x & 31;
     const int i = (int)(t & (mpad - 1));
     const long long env = t / mpad;
     const int lane_base = lane - i;
-    const int EPB = kBlock / mpad, e = threadIdx.x / mpad;
+    const int EPB = kRaceBlock / mpad, e = threadIdx.x / mpad;
     const bool valid = env < P.env_end && i < P.M;
     const long long D = P.Dpad;
     const int phy = P.physics;
@@ -80,7 +97,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
 
     // ---- stage the block's track instances (coalesced over envs) in shared memory
     const long long env0 = (long long)P.env_begin + (long long)blockIdx.x * EPB;
-    for (int idx = threadIdx.x; idx < RP.TF * EPB; idx += kBlock) {
+    for (int idx = threadIdx.x; idx < RP.TF * EPB; idx += kRaceBlock) {
         const int f = idx / EPB, el = idx - f * EPB;
         trk[idx] = env0 + el < P.N ? rb.track[(long long)f * P.N + env0 + el] : T(0);
     }
@@ -153,6 +170,11 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
         }
     }
     // ---- S fused substeps (:210-254)
+    // fast build: one rotation matrix per substep, computed right after the pose update and shared by the controller
+    // (Euler angles, firmware attitude error) and the next substep's force models; the controller's schedule bits of
+    // the whole control step fetched once
+    Mat3<T> R = rotmat_loop(d.q);
+    const MelWindow win = M<T>::fast ? mel_schedule_window(RP, rb.lut, m.tick, P.S) : MelWindow{0u, false};
     for (int s = 0; s < P.S; ++s) {
         // disturbance draws of this substep: injected, or Philox(seed; env, drone, tick, episode)
         T nz[7] = {T(0), T(0), T(0), T(0), T(0), T(0), T(0)};
@@ -178,7 +200,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
             nz[5] = RP.noise_std * r1 * c1; nz[6] = RP.noise_std * r1 * s1;
         }
         // _apply_physics(self.rpms, self.prev_rpms) (:510-548): forces from the substep-start state
-        const Mat3<T> R = rotmat_loop(d.q);
+        if (!M<T>::fast) R = rotmat_loop(d.q);
         T f[4], tq[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) { f[k] = mul_rn(m.rpms[k] * m.rpms[k], P.kf); tq[k] = mul_rn(m.rpms[k] * m.rpms[k], P.km); }
@@ -202,6 +224,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
             const V3<T> fw = {fext.x + nz[0], fext.y + nz[1], fext.z + nz[2]};         // drag + wind (:532-544)
             pyb_substep(P, phy, d, R, fz, tb, fw, body[0], body[1], body[2], body[3]);
         }
+        if (M<T>::fast) R = rotmat_loop(d.q);
         // controller round trip (:231-254)
         if (eliminated) {
 #pragma unroll
@@ -209,7 +232,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
         } else {
 #pragma unroll
             for (int k = 0; k < 4; ++k) d.last_rpm[k] = m.rpms[k];                       // prev_rpms[i] = rpms[i] (:251)
-            mellinger_tick(RP, rb.lut, m, sp, d.p, d.q, d.v, nz + 3);                    // rpms[i] = recv() (:254)
+            mellinger_tick(RP, rb.lut, m, sp, d.p, d.q, d.v, nz + 3, R, win, s);                   // rpms[i] = recv() (:254)
         }
     }
     if (M<T>::fast) d.q = canon_quat_loop(d.q);             // once per control step in the product build (adrp_physics.cuh)
