@@ -83,20 +83,22 @@ cudaError_t Launch<T>::get_state(const KParams<T>& P, const KBuffers<T>& b, T* r
 template <typename T>
 using RaceStepFn = void (*)(KParams<T>, RaceParams<T>, KBuffers<T>, RaceBuffers<T>, const T*, const T*, T*, T*, uint8_t*,
                             uint8_t*, uint8_t*);
+// quiet: no disturbance draws in this launch (no injected noise, RaceParams::disturbances off) -- the product build
+// then runs the instance without the wind / motor-noise terms.
 template <typename T>
-inline RaceStepFn<T> race_step_fn(int mpad, bool full)
+inline RaceStepFn<T> race_step_fn(int mpad, bool full, bool quiet)
 {
-    if (full) return race_step_kernel<T, 0, true>;           // (Command.FULLSTATE, args) actions: scripted controllers
+    if (full) return race_step_kernel<T, 0, true, false>;    // (Command.FULLSTATE, args) actions: scripted controllers
     if (M<T>::fast) {
         switch (mpad) {
-            case 1: return race_step_kernel<T, 1, false>;
-            case 2: return race_step_kernel<T, 2, false>;
-            case 4: return race_step_kernel<T, 4, false>;
-            case 8: return race_step_kernel<T, 8, false>;
+            case 1: return quiet ? race_step_kernel<T, 1, false, true> : race_step_kernel<T, 1, false, false>;
+            case 2: return quiet ? race_step_kernel<T, 2, false, true> : race_step_kernel<T, 2, false, false>;
+            case 4: return quiet ? race_step_kernel<T, 4, false, true> : race_step_kernel<T, 4, false, false>;
+            case 8: return quiet ? race_step_kernel<T, 8, false, true> : race_step_kernel<T, 8, false, false>;
             default: break;
         }
     }
-    return race_step_kernel<T, 0, false>;
+    return race_step_kernel<T, 0, false, false>;
 }
 
 template <typename T>
@@ -104,7 +106,9 @@ cudaError_t Launch<T>::race_prepare(const RaceParams<T>& RP, const KParams<T>& P
 {
     const size_t bytes = race_smem_bytes(P, RP);
     if (bytes <= 48 * 1024) return cudaSuccess;
-    cudaError_t e = cudaFuncSetAttribute(race_step_fn<T>(P.Mpad, P.action_type == ADRP_ACT_MEL_FULL), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)race_smem_bytes(P, RP, kRaceBlock));
+    cudaError_t e = cudaSuccess;
+    for (int quiet = 0; quiet < 2 && e == cudaSuccess; ++quiet)
+        e = cudaFuncSetAttribute(race_step_fn<T>(P.Mpad, P.action_type == ADRP_ACT_MEL_FULL, quiet != 0), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)race_smem_bytes(P, RP, kRaceBlock));
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(race_reset_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
 }
@@ -122,7 +126,7 @@ cudaError_t Launch<T>::race_step(const KParams<T>& P, const RaceParams<T>& RP, c
                                  const T* action, const T* noise, T* obs, T* reward, uint8_t* te, uint8_t* tr,
                                  uint8_t* fl, cudaStream_t s)
 {
-    race_step_fn<T>(P.Mpad, P.action_type == ADRP_ACT_MEL_FULL)<<<(unsigned)(((long long)(P.env_end - P.env_begin) * P.Mpad + kRaceBlock - 1) / kRaceBlock), kRaceBlock, race_smem_bytes(P, RP, kRaceBlock), s>>>(P, RP, b, rb, action, noise, obs, reward, te, tr, fl);
+    race_step_fn<T>(P.Mpad, P.action_type == ADRP_ACT_MEL_FULL, !noise && !RP.disturbances)<<<(unsigned)(((long long)(P.env_end - P.env_begin) * P.Mpad + kRaceBlock - 1) / kRaceBlock), kRaceBlock, race_smem_bytes(P, RP, kRaceBlock), s>>>(P, RP, b, rb, action, noise, obs, reward, te, tr, fl);
     return cudaGetLastError();
 }
 

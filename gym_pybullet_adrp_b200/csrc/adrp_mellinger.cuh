@@ -33,7 +33,7 @@ struct MelFw {                       // controller_mellinger.c file-scope static
     float i_error_x, i_error_y, i_error_z, i_error_m_x, i_error_m_y, i_error_m_z;
     float prev_omega_roll, prev_omega_pitch, prev_setpoint_omega_roll, prev_setpoint_omega_pitch;
     float thrust;
-    int roll, pitch, yaw;            // int16 values
+    float roll, pitch, yaw;          // int16 values (held as floats: exact, and the PWM mix reads them as such)
 };
 
 template <typename T>
@@ -48,7 +48,18 @@ struct Mel {
 
 // Full-state command (MellingerControl._sendFullStateCmd, :510-543): yaw-only quaternion; vel / acc / attitude rates
 // (deg/s) are zero for ndarray actions (MultiRaceAviary.py:190-195) and literal zeros in those kernels.
-struct MelSetpoint { float pos[3], qz, qw, vel[3], acc[3], rate_deg[3]; };
+struct MelSetpoint { float pos[3], qz, qw, vel[3], acc[3], rate_deg[3], xc0, xc1; };
+
+// fast build: heading of the desired x axis, constant over the control step.  The yaw-only setpoint quaternion is
+// (0, 0, sin(yaw/2), cos(yaw/2)): the firmware's atan2 arguments (dy_s, dy_c) ARE (sin yaw, cos yaw) up to their norm, so
+// its atan2 -> degrees -> radians -> sincos round trip reduces to a normalisation.
+template <typename T> __device__ __forceinline__ void mel_setpoint_heading(MelSetpoint& sp)
+{
+    if (!M<T>::fast) return;
+    const float dy_s = 2.0f * (sp.qw * sp.qz), dy_c = 1 - 2 * (sp.qz * sp.qz);
+    const float in = M<float>::frsqrt(dy_c * dy_c + dy_s * dy_s);
+    sp.xc0 = dy_c * in; sp.xc1 = dy_s * in;
+}
 
 __device__ __forceinline__ float fw_clamp(float v, float lo, float hi) { return v < lo ? lo : (v > hi ? hi : v); }
 template <typename T> __device__ __forceinline__ float fw_clampT(float v, float lo, float hi)
@@ -113,19 +124,15 @@ __device__ __forceinline__ void fw_mellinger(MelFw& m, const MelSetpoint& sp, fl
     else { zd0 = tt[0] / nt; zd1 = tt[1] / nt; zd2 = tt[2] / nt; }
     float xc0, xc1;
     if (M<T>::fast) {
-        // the yaw-only setpoint quaternion is (0, 0, sin(yaw/2), cos(yaw/2)): (dy_c, dy_s) = (cos yaw, sin yaw) up to
-        // its norm, so the degrees -> radians -> sincos round trip of the firmware reduces to a normalisation
-        const float in = M<float>::frsqrt(dy_c * dy_c + dy_s * dy_s);
-        xc0 = dy_c * in; xc1 = dy_s * in;
+        xc0 = sp.xc0; xc1 = sp.xc1;                           // mel_setpoint_heading, once per control step
     } else {
         const float desiredYaw = fw_degrees(FwMath<T>::atan2(dy_s, dy_c));
         FwMath<T>::sincos(fw_radians(desiredYaw), &xc1, &xc0);
     }
     const float xc2 = 0.0f;
     float yd0 = zd1 * xc2 - zd2 * xc1, yd1 = zd2 * xc0 - zd0 * xc2, yd2 = zd0 * xc1 - zd1 * xc0;
-    const float ny = M<T>::fast ? M<float>::fsqrt(yd0 * yd0 + yd1 * yd1 + yd2 * yd2) : sqrtf(yd0 * yd0 + yd1 * yd1 + yd2 * yd2);
-    if (M<T>::fast) { const float in = M<float>::rcp(ny); yd0 *= in; yd1 *= in; yd2 *= in; }
-    else { yd0 /= ny; yd1 /= ny; yd2 /= ny; }
+    if (M<T>::fast) { const float in = M<float>::frsqrt(yd0 * yd0 + yd1 * yd1 + yd2 * yd2); yd0 *= in; yd1 *= in; yd2 *= in; }
+    else { const float ny = sqrtf(yd0 * yd0 + yd1 * yd1 + yd2 * yd2); yd0 /= ny; yd1 /= ny; yd2 /= ny; }
     const float xd0 = yd1 * zd2 - yd2 * zd1, xd1 = yd2 * zd0 - yd0 * zd2, xd2 = yd0 * zd1 - yd1 * zd0;
     // eRM = Rdes^T R - R^T Rdes with Rdes = [xd yd zd] (columns): Rd[k][0] = xd_k, Rd[k][1] = yd_k, Rd[k][2] = zd_k
     float e21 = 0, e02 = 0, e10 = 0;
@@ -146,14 +153,23 @@ __device__ __forceinline__ void fw_mellinger(MelFw& m, const MelSetpoint& sp, fl
     m.i_error_m_x += (-eR0) * dt; m.i_error_m_x = fw_clampT<T>(m.i_error_m_x, -i_range_m_xy, i_range_m_xy);
     m.i_error_m_y += (-eR1) * dt; m.i_error_m_y = fw_clampT<T>(m.i_error_m_y, -i_range_m_xy, i_range_m_xy);
     m.i_error_m_z += (-eR2) * dt; m.i_error_m_z = fw_clampT<T>(m.i_error_m_z, -i_range_m_z, i_range_m_z);
-    const float Mx = -kR_xy * eR0 + kw_xy * ew0 + ki_m_xy * m.i_error_m_x + kd_omega_rp * err_d_roll;
-    const float My = -kR_xy * eR1 + kw_xy * ew1 + ki_m_xy * m.i_error_m_y + kd_omega_rp * err_d_pitch;
+    // (ki_m_xy == 0: the fast build leaves the term out)
+    const float Mx = M<T>::fast ? -kR_xy * eR0 + kw_xy * ew0 + kd_omega_rp * err_d_roll
+                                : -kR_xy * eR0 + kw_xy * ew0 + ki_m_xy * m.i_error_m_x + kd_omega_rp * err_d_roll;
+    const float My = M<T>::fast ? -kR_xy * eR1 + kw_xy * ew1 + kd_omega_rp * err_d_pitch
+                                : -kR_xy * eR1 + kw_xy * ew1 + ki_m_xy * m.i_error_m_y + kd_omega_rp * err_d_pitch;
     const float Mz = -kR_z * eR2 + kw_z * ew2 + ki_m_z * m.i_error_m_z;
     m.thrust = massThrust * current_thrust;
     if (m.thrust > 0) {
-        m.roll = (int)(short)fw_clampT<T>(Mx, -32000, 32000);
-        m.pitch = (int)(short)fw_clampT<T>(My, -32000, 32000);
-        m.yaw = (int)(short)fw_clampT<T>(-Mz, -32000, 32000);
+        // control->roll = clamp(M.x, -32000, 32000) into an int16: truncation toward zero
+        if (M<T>::fast) {
+            m.roll = truncf(fw_clampT<T>(Mx, -32000, 32000)); m.pitch = truncf(fw_clampT<T>(My, -32000, 32000));
+            m.yaw = truncf(fw_clampT<T>(-Mz, -32000, 32000));
+        } else {
+            m.roll = (float)(int)(short)fw_clampT<T>(Mx, -32000, 32000);
+            m.pitch = (float)(int)(short)fw_clampT<T>(My, -32000, 32000);
+            m.yaw = (float)(int)(short)fw_clampT<T>(-Mz, -32000, 32000);
+        }
     } else {
         m.roll = m.pitch = m.yaw = 0;
         m.i_error_x = m.i_error_y = m.i_error_z = 0;          // controllerMellingerReset()
@@ -200,7 +216,9 @@ __device__ __forceinline__ void mellinger_tick(const RaceParams<T>& RP, const ui
     T rates[3], acc_z;
     float qf[4];
     if (M<T>::fast) {
-        rates[0] = (rpy.x - m.prev_rpy.x) * T(500); rates[1] = (rpy.y - m.prev_rpy.y) * T(500); rates[2] = (rpy.z - m.prev_rpy.z) * T(500);
+        // (rates in deg/s straight away: * 500 * 180 / pi; the conversion below is then the identity)
+        const T K = T(500.0 * 180.0 / 3.14159265358979323846);
+        rates[0] = (rpy.x - m.prev_rpy.x) * K; rates[1] = (rpy.y - m.prev_rpy.y) * K; rates[2] = (rpy.z - m.prev_rpy.z) * K;
         acc_z = (v.z - m.prev_vel.z) * T(500.0 / 9.8) + T(1);
         // euler -> degrees -> radians -> quaternion (:446-471) reproduces +-q up to rounding, and the firmware only
         // reads q through its rotation matrix: hand it the state quaternion
@@ -226,7 +244,7 @@ __device__ __forceinline__ void mellinger_tick(const RaceParams<T>& RP, const ui
     float gyro[3];
 #pragma unroll
     for (int k = 0; k < 3; ++k)
-        gyro[k] = fw_lpf2p(RP.lpf_b0, RP.lpf_b1, RP.lpf_b2, RP.lpf_a1, RP.lpf_a2, m.gd1[k], m.gd2[k], (float)(rates[k] * RAD_TO_DEG));
+        gyro[k] = fw_lpf2p(RP.lpf_b0, RP.lpf_b1, RP.lpf_b2, RP.lpf_a1, RP.lpf_a2, m.gd1[k], m.gd2[k], (float)(M<T>::fast ? rates[k] : rates[k] * RAD_TO_DEG));
     // _step_controller (:378-419)
     if (m.acc_z < -0.5f) m.tumble += 1; else m.tumble = 0;                       // :382-385
     const bool stop = m.tumble >= 30;
@@ -262,8 +280,12 @@ __device__ __forceinline__ void mellinger_tick(const RaceParams<T>& RP, const ui
         }
 #pragma unroll
         for (int k = 0; k < 4; ++k) {                                            // thrust[[3,2,1,0]] + disturbance (:250-253)
-            const T r2 = rp[3 - k] * rp[3 - k] + noise4[k] * T(1.0 / 3.16e-10);
-            m.rpms[k] = M<T>::clamp(M<T>::fsqrt(M<T>::fmax(r2, T(0))), RPM_LO, RPM_HI);
+            if (noise4) {
+                const T r2 = rp[3 - k] * rp[3 - k] + noise4[k] * T(1.0 / 3.16e-10);
+                m.rpms[k] = M<T>::clamp(M<T>::fsqrt(M<T>::fmax(r2, T(0))), RPM_LO, RPM_HI);
+            } else {
+                m.rpms[k] = rp[3 - k];                                           // no draw: sqrt(rp^2) = rp, already inside the limits
+            }
         }
         return;
     }

@@ -48,8 +48,8 @@ __device__ __forceinline__ void load_mel(const RaceBuffers<T>& rb, long long D, 
     const int32_t* q = rb.mel_i;
     m.tick = ld(q, D, MI_TICK, t); m.tumble = ld(q, D, MI_TUMBLE, t); m.last_att = ld(q, D, MI_LAST_ATT, t);
     const int rp = ld(q, D, MI_CTL_RP, t), ye = ld(q, D, MI_CTL_Y_ERR, t);
-    m.fw.roll = (int)(short)(rp & 0xffff); m.fw.pitch = rp >> 16;
-    m.fw.yaw = (int)(short)(ye & 0xffff); m.error = ye >> 16;
+    m.fw.roll = (float)(int)(short)(rp & 0xffff); m.fw.pitch = (float)(rp >> 16);
+    m.fw.yaw = (float)(int)(short)(ye & 0xffff); m.error = ye >> 16;
 }
 
 template <typename T>
@@ -69,8 +69,8 @@ __device__ __forceinline__ void store_mel(const RaceBuffers<T>& rb, long long D,
     st(f, D, MF_THRUST, t, m.fw.thrust); st(f, D, MF_ACCZ, t, m.acc_z);
     int32_t* q = rb.mel_i;
     st(q, D, MI_TICK, t, (int32_t)m.tick); st(q, D, MI_TUMBLE, t, (int32_t)m.tumble); st(q, D, MI_LAST_ATT, t, (int32_t)m.last_att);
-    st(q, D, MI_CTL_RP, t, (int32_t)((m.fw.roll & 0xffff) | (m.fw.pitch << 16)));
-    st(q, D, MI_CTL_Y_ERR, t, (int32_t)((m.fw.yaw & 0xffff) | (m.error << 16)));
+    st(q, D, MI_CTL_RP, t, (int32_t)(((int)m.fw.roll & 0xffff) | ((int)m.fw.pitch << 16)));
+    st(q, D, MI_CTL_Y_ERR, t, (int32_t)(((int)m.fw.yaw & 0xffff) | (m.error << 16)));
 }
 
 // ---------------------------------------------------------------- reset of one drone of one env

@@ -74,7 +74,8 @@ race_reset_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ 
 // MultiRaceAviary.step (:171-270).  noise: NULL or (N, M, S, 7) = [wind force xyz (N), motor thrust noise x4 (N)].
 // MP: lanes per env at compile time (unrolled neighbour loops), 0 = read from the params.
 // FULL: 13-float (Command.FULLSTATE, args) actions (ADRP_ACT_MEL_FULL) instead of [x, y, z, yaw].
-template <typename T, int MP, bool FULL>
+// QUIET: the launch has no disturbance draws (noise == NULL and RaceParams::disturbances == 0).
+template <typename T, int MP, bool FULL, bool QUIET>
 __global__ void ADRP_RACE_BOUNDS
 race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ RaceParams<T> RP, const KBuffers<T> b,
                  const RaceBuffers<T> rb, const T* __restrict__ action, const T* __restrict__ noise, T* __restrict__ obs,
@@ -122,7 +123,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
     const bool eliminated = (latch & ADRP_FLAG_ELIMINATED) != 0;
 
     // ---- ndarray action -> FULLSTATE(pos, 0, 0, yaw, 0, step_counter) (:190-202)
-    MelSetpoint sp = {{0.0f, 0.0f, 0.0f}, 0.0f, 1.0f, {0.0f, 0.0f, 0.0f}, {0.0f, 0.0f, 0.0f}, {0.0f, 0.0f, 0.0f}};
+    MelSetpoint sp = {{0.0f, 0.0f, 0.0f}, 0.0f, 1.0f, {0.0f, 0.0f, 0.0f}, {0.0f, 0.0f, 0.0f}, {0.0f, 0.0f, 0.0f}, 1.0f, 0.0f};
     if (valid && !eliminated) {
         const T* a = action + od * (FULL ? 13 : 4);
         T a_yaw;
@@ -143,6 +144,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
         const T yaw = (RP.wrappers & ADRP_WRAP_OBS) ? T(0) : a_yaw;          // DroneObservationWrapper.step (wrapper.py:52-57)
         M<T>::sincos(yaw / T(2), &sy, &cy);                   // utils.get_quaternion_from_euler(0, 0, yaw)
         sp.qz = (float)sy; sp.qw = (float)cy;
+        mel_setpoint_heading<T>(sp);
     }
 
     // ---- RewardWrapper.reset (wrapper.py:96-101) reads drone 0's row of the reset observation: current gate id,
@@ -178,7 +180,8 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
     for (int s = 0; s < P.S; ++s) {
         // disturbance draws of this substep: injected, or Philox(seed; env, drone, tick, episode)
         T nz[7] = {T(0), T(0), T(0), T(0), T(0), T(0), T(0)};
-        if (noise) {
+        if (QUIET) {
+        } else if (noise) {
             if (valid) {
                 const T* np_ = noise + ((od * P.S) + s) * 7;
 #pragma unroll
@@ -221,7 +224,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
             const V3<T> tb = {mul_rn(P.prop_y[0], f[0]) + mul_rn(P.prop_y[1], f[1]) + mul_rn(P.prop_y[2], f[2]) + mul_rn(P.prop_y[3], f[3]),
                               mul_rn(-P.prop_x[0], f[0]) + mul_rn(-P.prop_x[1], f[1]) + mul_rn(-P.prop_x[2], f[2]) + mul_rn(-P.prop_x[3], f[3]),
                               tq[0] - tq[1] + tq[2] - tq[3]};                            // BaseAviary.py:703
-            const V3<T> fw = {fext.x + nz[0], fext.y + nz[1], fext.z + nz[2]};         // drag + wind (:532-544)
+            const V3<T> fw = QUIET ? fext : V3<T>{fext.x + nz[0], fext.y + nz[1], fext.z + nz[2]};   // drag + wind (:532-544)
             pyb_substep(P, phy, d, R, fz, tb, fw, body[0], body[1], body[2], body[3]);
         }
         if (M<T>::fast) R = rotmat_loop(d.q);
@@ -232,7 +235,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
         } else {
 #pragma unroll
             for (int k = 0; k < 4; ++k) d.last_rpm[k] = m.rpms[k];                       // prev_rpms[i] = rpms[i] (:251)
-            mellinger_tick(RP, rb.lut, m, sp, d.p, d.q, d.v, nz + 3, R, win, s);                   // rpms[i] = recv() (:254)
+            mellinger_tick(RP, rb.lut, m, sp, d.p, d.q, d.v, QUIET ? (const T*)nullptr : nz + 3, R, win, s);                   // rpms[i] = recv() (:254)
         }
     }
     if (M<T>::fast) d.q = canon_quat_loop(d.q);             // once per control step in the product build (adrp_physics.cuh)
