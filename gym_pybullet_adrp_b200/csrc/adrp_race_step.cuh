@@ -7,10 +7,10 @@ namespace adrp {
 // per SM (3 blocks of 128: without the bound ptxas takes 178 and the third block is lost); ADRP_RACE_BLOCK /
 // ADRP_RACE_MINB exist to measure other operating points.
 #ifndef ADRP_RACE_BLOCK
-#define ADRP_RACE_BLOCK 128
+#define ADRP_RACE_BLOCK 64
 #endif
 #ifndef ADRP_RACE_MINB
-#define ADRP_RACE_MINB 3
+#define ADRP_RACE_MINB 6
 #endif
 constexpr int kRaceBlock = ADRP_RACE_BLOCK, kRaceMinBlocks = ADRP_RACE_MINB;
 #ifdef ADRP_RACE_MAXNREG
