@@ -26,4 +26,10 @@ struct Launch {
                                    T* yaw_e, cudaStream_t s);
 };
 
+// Race step kernels of the product build with the physics mask as a template argument, one translation unit per mask
+// (adrp_race_f32_phy16.cu: Physics.PYB, adrp_race_f32_phy30.cu: Physics.PYB_GND_DRAG_DW).  NULL: no such instance.
+using RaceStepFnF32 = void (*)(KParams<float>, RaceParams<float>, KBuffers<float>, RaceBuffers<float>, const float*, const float*,
+                               float*, float*, uint8_t*, uint8_t*, uint8_t*);
+template <int PHY> RaceStepFnF32 race_step_special(int mpad, bool quiet);
+
 }  // namespace adrp

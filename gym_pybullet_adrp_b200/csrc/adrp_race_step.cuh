@@ -75,7 +75,8 @@ race_reset_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ 
 // MP: lanes per env at compile time (unrolled neighbour loops), 0 = read from the params.
 // FULL: 13-float (Command.FULLSTATE, args) actions (ADRP_ACT_MEL_FULL) instead of [x, y, z, yaw].
 // QUIET: the launch has no disturbance draws (noise == NULL and RaceParams::disturbances == 0).
-template <typename T, int MP, bool FULL, bool QUIET>
+// PHY_CT >= 0: physics mask known at compile time (no per-substep mask tests: +6 % on C5M); -1: read from the params.
+template <typename T, int MP, bool FULL, bool QUIET, int PHY_CT>
 __global__ void ADRP_RACE_BOUNDS
 race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ RaceParams<T> RP, const KBuffers<T> b,
                  const RaceBuffers<T> rb, const T* __restrict__ action, const T* __restrict__ noise, T* __restrict__ obs,
@@ -93,7 +94,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
     const int EPB = kRaceBlock / mpad, e = threadIdx.x / mpad;
     const bool valid = env < P.env_end && i < P.M;
     const long long D = P.Dpad;
-    const int phy = P.physics;
+    const int phy = PHY_CT >= 0 ? PHY_CT : P.physics;
     const long long od = valid ? env * P.M + i : 0;
 
     // ---- stage the block's track instances (coalesced over envs) in shared memory

@@ -22,6 +22,11 @@ import subprocess
 import tempfile
 
 
+def _norm(name):
+    """ncu prints template arguments differently per page ("(int)8" / "8", with or without the namespace)."""
+    return re.sub(r"\((?:int|bool)\)|adrp::|\s", "", name)
+
+
 def sass_counts(report, kernel_sub):
     out = subprocess.run(["ncu", "-i", report, "--page", "source", "--csv", "--print-source", "sass"],
                          capture_output=True, text=True, check=True).stdout
@@ -35,7 +40,7 @@ def sass_counts(report, kernel_sub):
         if rec[0] == "Address":
             header = {k: i for i, k in enumerate(rec)}
             continue
-        if header and name and kernel_sub in name:
+        if header and name and _norm(kernel_sub) in _norm(name):
             rows.append((rec[header["Source"]].strip(), int(rec[header["Instructions Executed"]] or 0),
                          {k: int(rec[i] or 0) for k, i in header.items() if k.startswith("stall_") and "Not Issued" not in k}))
     return name, rows
