@@ -271,12 +271,15 @@ __device__ __forceinline__ void mellinger_tick(const RaceParams<T>& RP, const ui
         const T A = T(-0.0006239 * 65535.0 / 3.0), B = T(0.088 * 65535.0 / 3.0);
         const T RPM_LO = T(0.2685 * 20000.0 + 4070.3), RPM_HI = T(0.2685 * 65535.0 + 4070.3);
         T rp[4];
+        if (stop) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const T x = M<T>::clamp(th[k], T(0), T(65535)) * T(60.0 / 65535.0);
-            T pw = x * (A * x + B);
-            if (stop) pw = T(0);
-            rp[k] = SCALE * M<T>::clamp(pw, T(20000), T(65535)) + CONST;
+            for (int k = 0; k < 4; ++k) rp[k] = RPM_LO;                          // zero PWM, clamped to 20000 (:246)
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const T x = M<T>::clamp(th[k], T(0), T(65535)) * T(60.0 / 65535.0);
+                rp[k] = SCALE * M<T>::clamp(x * (A * x + B), T(20000), T(65535)) + CONST;
+            }
         }
 #pragma unroll
         for (int k = 0; k < 4; ++k) {                                            // thrust[[3,2,1,0]] + disturbance (:250-253)

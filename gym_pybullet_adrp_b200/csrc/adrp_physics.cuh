@@ -231,28 +231,51 @@ __device__ __forceinline__ void dyn_substep(const KParams<T>& P, Drone<T>& d, co
     d.w = mul(R, d.rt);                                                          // :875-879 (pre-update R)
 }
 
+// Base-frame angular velocity for pyb_substep's fast path, and back (R: rotmat_loop of the pose at that moment).
+template <typename T> __device__ __forceinline__ V3<T> pyb_body_rates(const Mat3<T>& R, const V3<T>& w) { return mulT(R, w); }
+template <typename T> __device__ __forceinline__ V3<T> pyb_world_rates(const Mat3<T>& R, const V3<T>& wl) { return mul(R, wl); }
+
 // Bullet free body.  fz: total body-z force at the props + downwash; tb: body torque; fext: world force;
 // m, j*: the body's mass and principal inertia (per drone in the race env, changeDynamics).
+// wl (fast build only): the angular velocity in the BASE frame, carried by the caller across the substeps of one
+// control step (pyb_body_rates before the loop, pyb_world_rates after it); d.w is not touched in between.
 template <typename T>
-__device__ __forceinline__ void pyb_substep(const KParams<T>& P, int phy, Drone<T>& d, const Mat3<T>& R, T fz,
+__device__ __forceinline__ void pyb_substep(const KParams<T>& P, int phy, Drone<T>& d, V3<T>& wl, const Mat3<T>& R, T fz,
                                             const V3<T>& tb, const V3<T>& fext, T m, T jx, T jy, T jz)
 {
     const V3<T> fw = {R.m02 * fz + fext.x, R.m12 * fz + fext.y, R.m22 * fz + fext.z - m * P.g};
     if (M<T>::fast) {
         // Bullet updates the base in its own frame: a_w = R (R^T F / m - kl R^T v).  R is orthonormal (rotmat_loop
-        // divides by |q|^2), so the linear part is F / m - kl v with |R^T v| = |v| -- three matrix-vector products
-        // less; only the angular part needs the base frame (diagonal inertia).
-        const V3<T> w_l = mulT(R, d.w);
-        const T vn = M<T>::fsqrt(dot(d.v, d.v)), wn = M<T>::fsqrt(dot(w_l, w_l));
-        const V3<T> Jw = {jx * w_l.x, jy * w_l.y, jz * w_l.z};
-        const V3<T> gy = cross(w_l, Jw);
+        // divides by |q|^2), so the linear part is F / m - kl v with |R^T v| = |v|.  Angular part: with u = w_l + dt al_l
+        // the new world rate is R u and the pose update is q' = dq(R u dt) q = q dq(u dt), hence R' = R Exp(u dt) and the
+        // next substep's base-frame rate R'^T R u = Exp(-u dt) u = u: the base-frame rate integrates without any
+        // rotation, and the world rate is only needed once the control step is over.
+        const T vn = M<T>::fsqrt(dot(d.v, d.v)), wn = M<T>::fsqrt(dot(wl, wl));
+        const V3<T> Jw = {jx * wl.x, jy * wl.y, jz * wl.z};
+        const V3<T> gy = cross(wl, Jw);
         const T kl = P.lin_damp + P.lin_damp * vn, ka = P.ang_damp + P.ang_damp * wn;
         const T im = M<T>::rcp(m), dkl = T(1) - P.dt * kl, dim = P.dt * im;
-        const V3<T> al_l = {(tb.x - Jw.x * ka - gy.x) * M<T>::rcp(jx), (tb.y - Jw.y * ka - gy.y) * M<T>::rcp(jy),
-                            (tb.z - Jw.z * ka - gy.z) * M<T>::rcp(jz)};
-        const V3<T> al_w = mul(R, al_l);
+        const T dx = P.dt * M<T>::rcp(jx), dy = P.dt * M<T>::rcp(jy), dz = P.dt * M<T>::rcp(jz);
+        wl = {wl.x + dx * (tb.x - Jw.x * ka - gy.x), wl.y + dy * (tb.y - Jw.y * ka - gy.y), wl.z + dz * (tb.z - Jw.z * ka - gy.z)};
         d.v = {d.v.x * dkl + dim * fw.x, d.v.y * dkl + dim * fw.y, d.v.z * dkl + dim * fw.z};
-        d.w = {d.w.x + P.dt * al_w.x, d.w.y + P.dt * al_w.y, d.w.z + P.dt * al_w.z};
+        d.p = {d.p.x + P.dt * d.v.x, d.p.y + P.dt * d.v.y, d.p.z + P.dt * d.v.z};
+        // exponential map (btMultiBody::stepPositionsMultiDof) in the base frame: q <- q (k u, cos)
+        const T w2 = dot(wl, wl);
+        T k, cw;
+        if (w2 * (P.dt * P.dt) <= T(0.6168502750680849)) {
+            // |w| dt <= pi/4 (no clamp): cos(|w| dt/2) and sin(|w| dt/2)/|w| as polynomials in (|w| dt/2)^2, which also
+            // covers Bullet's own Taylor branch below 1e-3 rad/s
+            M<T>::cos_sinc_sq(w2 * (P.half_dt * P.half_dt), &cw, &k);
+            k *= P.half_dt;
+        } else {
+            // |w| dt > pi/4: Bullet clamps the angle, not the axis -- (w sin(pi/8) / (pi / 4 dt), cos(pi/8)), normalised later
+            cw = T(0.9238795325112867);
+            k = T(0.3826834323650898 / 0.7853981633974483) * P.dt;
+        }
+        const V3<T> ax = {wl.x * k, wl.y * k, wl.z * k};
+        const Q4<T> q = d.q;
+        d.q = {q.w * ax.x + q.x * cw + q.y * ax.z - q.z * ax.y, q.w * ax.y - q.x * ax.z + q.y * cw + q.z * ax.x,
+               q.w * ax.z + q.x * ax.y - q.y * ax.x + q.z * cw, q.w * cw - q.x * ax.x - q.y * ax.y - q.z * ax.z};
     } else {
         // world -> base frame
         const V3<T> f_l = mulT(R, fw), v_l = mulT(R, d.v), w_l = mulT(R, d.w);
@@ -265,35 +288,27 @@ __device__ __forceinline__ void pyb_substep(const KParams<T>& P, int phy, Drone<
         const V3<T> a_w = mul(R, a_l), al_w = mul(R, al_l);
         d.v = {d.v.x + P.dt * a_w.x, d.v.y + P.dt * a_w.y, d.v.z + P.dt * a_w.z};
         d.w = {d.w.x + P.dt * al_w.x, d.w.y + P.dt * al_w.y, d.w.z + P.dt * al_w.z};
-    }
-    d.p = {d.p.x + P.dt * d.v.x, d.p.y + P.dt * d.v.y, d.p.z + P.dt * d.v.z};
-    // exponential map (btMultiBody::stepPositionsMultiDof)
-    const T w2 = dot(d.w, d.w);
-    T k, cw;
-    if (M<T>::fast && w2 * (P.dt * P.dt) <= T(0.6168502750680849)) {
-        // |w| dt <= pi/4 (no clamp): cos(|w| dt/2) and sin(|w| dt/2)/|w| as polynomials in (|w| dt/2)^2, which also
-        // covers Bullet's own Taylor branch below 1e-3 rad/s
-        M<T>::cos_sinc_sq(w2 * (P.half_dt * P.half_dt), &cw, &k);
-        k *= P.half_dt;
-    } else {
-        T ang = M<T>::fsqrt(w2);
+        d.p = {d.p.x + P.dt * d.v.x, d.p.y + P.dt * d.v.y, d.p.z + P.dt * d.v.z};
+        // exponential map (btMultiBody::stepPositionsMultiDof)
+        T ang = M<T>::sqrt(dot(d.w, d.w));
+        T k, cw;
         if (ang * P.dt > T(0.7853981633974483)) ang = T(0.7853981633974483) / P.dt;
         if (ang < T(0.001)) {
             k = T(0.5) * P.dt - (P.dt * P.dt * P.dt) * T(0.020833333333) * ang * ang;
             cw = M<T>::cos(ang * P.dt * T(0.5));
         } else {
-            T s;
-            M<T>::sincos_small(T(0.5) * ang * P.dt, &s, &cw);
-            k = M<T>::fdiv(s, ang);
+            T sn;
+            M<T>::sincos(T(0.5) * ang * P.dt, &sn, &cw);
+            k = sn / ang;
         }
+        const V3<T> ax = {d.w.x * k, d.w.y * k, d.w.z * k};
+        const Q4<T> q = d.q;
+        d.q = {cw * q.x + ax.x * q.w + ax.y * q.z - ax.z * q.y, cw * q.y + ax.y * q.w + ax.z * q.x - ax.x * q.z,
+               cw * q.z + ax.z * q.w + ax.x * q.y - ax.y * q.x, cw * q.w - ax.x * q.x - ax.y * q.y - ax.z * q.z};
+        d.q = canon_quat(d.q);                                                   // Bullet renormalises every step
     }
-    const V3<T> ax = {d.w.x * k, d.w.y * k, d.w.z * k};
-    const Q4<T> q = d.q;
-    d.q = {cw * q.x + ax.x * q.w + ax.y * q.z - ax.z * q.y, cw * q.y + ax.y * q.w + ax.z * q.x - ax.x * q.z,
-           cw * q.z + ax.z * q.w + ax.x * q.y - ax.y * q.x, cw * q.w - ax.x * q.x - ax.y * q.y - ax.z * q.z};
-    // Bullet renormalises every step; the product build does it once per control step (kernel epilogue): the
-    // update is linear in q and rotmat_loop divides by |q|^2
-    if (!M<T>::fast) d.q = canon_quat(d.q);
+    // (the product build renormalises once per control step, in the kernel epilogue: the update is linear in q and
+    // rotmat_loop divides by |q|^2)
     if (phy & ADRP_PHY_GROUND) {
         // declared plane response: project the lowest point of the collision cylinder back to z = 0,
         // cancel the approaching normal velocity, Coulomb friction mu = 0.5 on the tangential part

@@ -178,6 +178,10 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
     // the whole control step fetched once
     Mat3<T> R = rotmat_loop(d.q);
     const MelWindow win = M<T>::fast ? mel_schedule_window(RP, rb.lut, m.tick, P.S) : MelWindow{0u, false};
+    // product build, Bullet free body: the angular velocity stays in the base frame for the whole control step
+    const bool body_rates = M<T>::fast && !(phy & ADRP_PHY_DYN);
+    V3<T> wl = {T(0), T(0), T(0)};
+    if (body_rates) wl = pyb_body_rates(R, d.w);
     for (int s = 0; s < P.S; ++s) {
         // disturbance draws of this substep: injected, or Philox(seed; env, drone, tick, episode)
         T nz[7] = {T(0), T(0), T(0), T(0), T(0), T(0), T(0)};
@@ -226,7 +230,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
                               mul_rn(-P.prop_x[0], f[0]) + mul_rn(-P.prop_x[1], f[1]) + mul_rn(-P.prop_x[2], f[2]) + mul_rn(-P.prop_x[3], f[3]),
                               tq[0] - tq[1] + tq[2] - tq[3]};                            // BaseAviary.py:703
             const V3<T> fw = QUIET ? fext : V3<T>{fext.x + nz[0], fext.y + nz[1], fext.z + nz[2]};   // drag + wind (:532-544)
-            pyb_substep(P, phy, d, R, fz, tb, fw, body[0], body[1], body[2], body[3]);
+            pyb_substep(P, phy, d, wl, R, fz, tb, fw, body[0], body[1], body[2], body[3]);
         }
         if (M<T>::fast) R = rotmat_loop(d.q);
         // controller round trip (:231-254)
@@ -239,6 +243,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
             mellinger_tick(RP, rb.lut, m, sp, d.p, d.q, d.v, QUIET ? (const T*)nullptr : nz + 3, R, win, s);                   // rpms[i] = recv() (:254)
         }
     }
+    if (body_rates) d.w = pyb_world_rates(R, wl);           // R: the pose after the last substep
     if (M<T>::fast) d.q = canon_quat_loop(d.q);             // once per control step in the product build (adrp_physics.cuh)
     __syncthreads();                                                                     // shared track is complete
 

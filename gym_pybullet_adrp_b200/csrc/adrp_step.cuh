@@ -146,6 +146,10 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
     for (int k = 0; k < 4; ++k) { f0[k] = mul_rn(rpm[k] * rpm[k], P.kf); tq[k] = mul_rn(rpm[k] * rpm[k], P.km); }
     const T drag_sum_prev = T(0.10471975511965977) * ((d.last_rpm[0] + d.last_rpm[1]) + (d.last_rpm[2] + d.last_rpm[3]));   // 2 pi / 60
     const T drag_sum_cur = T(0.10471975511965977) * ((rpm[0] + rpm[1]) + (rpm[2] + rpm[3]));
+    // product build, Bullet free body: the angular velocity stays in the base frame for the whole control step
+    const bool body_rates = M<T>::fast && !(phy & ADRP_PHY_DYN);
+    V3<T> wl = {T(0), T(0), T(0)};
+    if (body_rates) wl = pyb_body_rates(rotmat_loop(d.q), d.w);
     for (int s = 0; s < P.S; ++s) {
         const Mat3<T> R = rotmat_loop(d.q);
         T f[4] = {f0[0], f0[1], f0[2], f0[3]};
@@ -169,7 +173,7 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
             const V3<T> tb = {mul_rn(P.prop_y[0], f[0]) + mul_rn(P.prop_y[1], f[1]) + mul_rn(P.prop_y[2], f[2]) + mul_rn(P.prop_y[3], f[3]),
                               -(mul_rn(P.prop_x[0], f[0]) + mul_rn(P.prop_x[1], f[1]) + mul_rn(P.prop_x[2], f[2]) + mul_rn(P.prop_x[3], f[3])),
                               tq[0] - tq[1] + tq[2] - tq[3]};                   // :703
-            pyb_substep(P, phy, d, R, fz, tb, fext, P.pyb_mass, P.pyb_jx, P.pyb_jy, P.pyb_jz);
+            pyb_substep(P, phy, d, wl, R, fz, tb, fext, P.pyb_mass, P.pyb_jx, P.pyb_jy, P.pyb_jz);
         }
         if (!M<T>::fast) {
 #pragma unroll
@@ -181,6 +185,7 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
         for (int k = 0; k < 4; ++k) d.last_rpm[k] = rpm[k];                      // :376 (S >= 1)
     }
     if (M<T>::fast) d.q = canon_quat_loop(d.q);          // once per control step in the product build (adrp_physics.cuh)
+    if (body_rates) d.w = pyb_world_rates(rotmat_loop(d.q), wl);
 
     // ---- observation (CtrlAviary.py:106-117; BaseRLAviary.py:284-322).  CtrlAviary has no flag that depends on the
     // Euler angles, so the product build may use the loop's polynomial atan2 there (1 ulp); the RL aviaries threshold

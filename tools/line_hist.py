@@ -47,10 +47,14 @@ def sass_counts(report, kernel_sub):
 
 
 def line_table(obj, kernel_sub):
-    tmp = tempfile.mkdtemp()
-    subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(obj)], cwd=tmp, capture_output=True, check=True)
-    cubin = glob.glob(os.path.join(tmp, "*.cubin"))[0]
-    txt = subprocess.run(["nvdisasm", "-gi", "-c", cubin], capture_output=True, text=True, check=True).stdout
+    """obj: one object file, or a directory whose *.o are all searched (one translation unit per kernel family)."""
+    objs = sorted(glob.glob(os.path.join(obj, "*.o"))) if os.path.isdir(obj) else [obj]
+    txt = ""
+    for o in objs:
+        tmp = tempfile.mkdtemp()
+        subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(o)], cwd=tmp, capture_output=True)
+        for cubin in glob.glob(os.path.join(tmp, "*.cubin")):
+            txt += subprocess.run(["nvdisasm", "-gi", "-c", cubin], capture_output=True, text=True, check=True).stdout
     insts, frames, pending, inside, sections = [], [], [], False, {}
     for line in txt.splitlines():
         if line.startswith(".text."):
@@ -110,7 +114,8 @@ def main():
     print(f"# total warp instructions {total}  (opcode mismatches: {mism})")
     for (f, n), c in hist.most_common(a.top):
         if f not in src:
-            cand = glob.glob(os.path.join(os.path.dirname(os.path.abspath(a.obj)), "..", "csrc", f))
+            base = os.path.abspath(a.obj) if os.path.isdir(a.obj) else os.path.dirname(os.path.abspath(a.obj))
+            cand = glob.glob(os.path.join(base, "..", "csrc", f))
             src[f] = open(cand[0]).read().splitlines() if cand else []
         text = src[f][n - 1].strip()[:100] if 0 < n <= len(src[f]) else ""
         extra = ""

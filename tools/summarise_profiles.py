@@ -6,7 +6,7 @@
     TAG_sass_hist_<wl>.txt                          warp-level SASS instructions executed, by opcode
     TAG_line_hist_<wl>.txt                          ... per source line (tools/line_hist.py, leaf frames + inclusive)
 
-    python tools/summarise_profiles.py TAG [--obj gym_pybullet_adrp_b200/build/adrp_kernels_f32.o]
+    python tools/summarise_profiles.py TAG [--obj gym_pybullet_adrp_b200/build]
 """
 from __future__ import annotations
 
@@ -69,7 +69,7 @@ def sass_hist(rep):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("tag")
-    ap.add_argument("--obj", default=os.path.join(ROOT, "gym_pybullet_adrp_b200", "build", "adrp_kernels_f32.o"))
+    ap.add_argument("--obj", default=os.path.join(ROOT, "gym_pybullet_adrp_b200", "build"), help="object file or directory of *.o")
     a = ap.parse_args()
     src, dst = os.path.join(ROOT, "gpurun_out"), os.path.join(ROOT, "profiles")
     for f in glob.glob(os.path.join(src, f"{a.tag}_bench_*.json")) + glob.glob(os.path.join(src, f"{a.tag}_launches_*.csv")):
