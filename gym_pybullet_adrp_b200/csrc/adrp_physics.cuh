@@ -50,6 +50,22 @@ __device__ __forceinline__ void ground_effect(const KParams<T>& P, const Drone<T
     }
 }
 
+// Product build: thrust INCLUDING the ground effect, f_i (1 + c / h_i^2) -- one select for the tilt gate, one multiply-add
+// per propeller.  Equal commands at equal heights still give bit-equal thrusts (the torque sums cancel exactly).
+template <typename T>
+__device__ __forceinline__ void ground_effect_total(const KParams<T>& P, const Drone<T>& d, const Mat3<T>& R,
+                                                    const T rpm2kf[4], T out[4])
+{
+    const bool on = R.m22 > T(0) && M<T>::abs(R.m20) < T(0.99999);
+    const T c = on ? P.gnd_eff_coeff * P.qr4 * P.qr4 : T(0);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        T h = d.p.z + R.m20 * P.prop_x[i] + R.m21 * P.prop_y[i];
+        h = M<T>::fmax(h, P.gnd_eff_h_clip);
+        out[i] = mul_rn(rpm2kf[i], c * M<T>::rcp(h * h) + T(1));
+    }
+}
+
 // World-frame drag force (:761-788): R^T (c o v) applied in LINK_FRAME == c o v.
 template <typename T>
 __device__ __forceinline__ V3<T> drag_force(const KParams<T>& P, const Drone<T>& d)

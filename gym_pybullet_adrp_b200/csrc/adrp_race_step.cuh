@@ -213,10 +213,14 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
 #pragma unroll
         for (int k = 0; k < 4; ++k) { f[k] = mul_rn(m.rpms[k] * m.rpms[k], P.kf); tq[k] = mul_rn(m.rpms[k] * m.rpms[k], P.km); }
         if (phy & ADRP_PHY_GND) {
-            T gnd[4];
-            ground_effect(P, d, R, f, gnd);
+            if (M<T>::fast) {
+                ground_effect_total(P, d, R, f, f);
+            } else {
+                T gnd[4];
+                ground_effect(P, d, R, f, gnd);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) f[k] += gnd[k];
+                for (int k = 0; k < 4; ++k) f[k] += gnd[k];
+            }
         }
         V3<T> fext = {T(0), T(0), T(0)};
         if (phy & ADRP_PHY_DRAG) fext = drag_force(P, d);      // prev_rpms = state row 16:20

@@ -154,10 +154,14 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
         const Mat3<T> R = rotmat_loop(d.q);
         T f[4] = {f0[0], f0[1], f0[2], f0[3]};
         if (phy & ADRP_PHY_GND) {
-            T gnd[4];
-            ground_effect(P, d, R, f0, gnd);
+            if (M<T>::fast) {
+                ground_effect_total(P, d, R, f0, f);
+            } else {
+                T gnd[4];
+                ground_effect(P, d, R, f0, gnd);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) f[k] += gnd[k];
+                for (int k = 0; k < 4; ++k) f[k] += gnd[k];
+            }
         }
         V3<T> fext = {T(0), T(0), T(0)};
         if (phy & ADRP_PHY_DRAG) {                         // last_clipped_action: the previous step's RPM during the first substep (:363,:376)
