@@ -211,7 +211,7 @@ template <typename T> __device__ __forceinline__ V3<T> euler_rpy_loop(const Q4<T
     const T HALF_PI = T(1.5707963267948966);
     if (sarg <= T(-0.99999)) return {T(0), -HALF_PI, T(2) * M<T>::atan2(q.x, -q.y)};
     if (sarg >= T(0.99999)) return {T(0), HALF_PI, T(2) * M<T>::atan2(-q.x, q.y)};
-    return {M<T>::atan2_loop(T(2) * (q.y * q.z + q.w * q.x), squ - sqx - sqy + sqz), M<T>::asin(sarg),
+    return {M<T>::atan2_loop(T(2) * (q.y * q.z + q.w * q.x), squ - sqx - sqy + sqz), M<T>::asin_loop(sarg),
             M<T>::atan2_loop(T(2) * (q.x * q.y + q.w * q.z), squ + sqx - sqy - sqz)};
 }
 
