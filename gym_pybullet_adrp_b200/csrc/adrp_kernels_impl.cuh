@@ -49,20 +49,20 @@ cudaError_t Launch<T>::step(const KParams<T>& P, const KBuffers<T>& b, const T* 
 {
     const bool pid = P.action_type == ADRP_ACT_PID || P.action_type == ADRP_ACT_ONE_D_PID ||
                      P.action_type == ADRP_ACT_VEL || P.action_type == ADRP_ACT_PID_FULL;
-    const unsigned grid = grid_for((long long)(P.env_end - P.env_begin) * P.Mpad);
-#define ADRP_LAUNCH_STEP(MP) step_kernel<T, -1, 0, MP><<<grid, kBlock, 0, s>>>(P, b, action, obs, reward, te, tr, fl)
+    const unsigned grid = (unsigned)(((long long)(P.env_end - P.env_begin) * P.Mpad + kStepBlock - 1) / kStepBlock);
+#define ADRP_LAUNCH_STEP(MP) step_kernel<T, -1, 0, MP><<<grid, kStepBlock, 0, s>>>(P, b, action, obs, reward, te, tr, fl)
     // product build, formations with every force model on (PYB_GND_DRAG_DW and its DYN counterpart): the physics mask
     // as a template argument drops the per-substep mask tests and 23 registers (95 -> 72), +2 % on C5
     if (!pid && M<T>::fast && (P.Mpad == 2 || P.Mpad == 4 || P.Mpad == 8)) {
         constexpr int ALL = ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW;
-#define ADRP_LAUNCH_PHY(PHY, MP) step_kernel<T, PHY, 0, MP><<<grid, kBlock, 0, s>>>(P, b, action, obs, reward, te, tr, fl)
+#define ADRP_LAUNCH_PHY(PHY, MP) step_kernel<T, PHY, 0, MP><<<grid, kStepBlock, 0, s>>>(P, b, action, obs, reward, te, tr, fl)
 #define ADRP_LAUNCH_PHY_MP(PHY) (P.Mpad == 2 ? ADRP_LAUNCH_PHY(PHY, 2) : P.Mpad == 4 ? ADRP_LAUNCH_PHY(PHY, 4) : ADRP_LAUNCH_PHY(PHY, 8))
         if (P.physics == (ALL | ADRP_PHY_DYN)) { ADRP_LAUNCH_PHY_MP(ALL | ADRP_PHY_DYN); return cudaGetLastError(); }
         if (P.physics == (ALL | ADRP_PHY_GROUND)) { ADRP_LAUNCH_PHY_MP(ALL | ADRP_PHY_GROUND); return cudaGetLastError(); }
 #undef ADRP_LAUNCH_PHY_MP
 #undef ADRP_LAUNCH_PHY
     }
-    if (pid) step_kernel<T, -1, 1, 0><<<grid, kBlock, 0, s>>>(P, b, action, obs, reward, te, tr, fl);
+    if (pid) step_kernel<T, -1, 1, 0><<<grid, kStepBlock, 0, s>>>(P, b, action, obs, reward, te, tr, fl);
     else switch (P.Mpad) {
         case 1: ADRP_LAUNCH_STEP(1); break;
         case 2: ADRP_LAUNCH_STEP(2); break;

@@ -10,6 +10,15 @@
 namespace adrp {
 
 constexpr int kBlock = 128;
+// Block size of step_kernel (a divisor of kBlock: the host path cuts its chunks in units of kBlock threads).
+#ifndef ADRP_STEP_BLOCK
+#define ADRP_STEP_BLOCK 128
+#endif
+#ifndef ADRP_STEP_MINB
+#define ADRP_STEP_MINB 1
+#endif
+constexpr int kStepBlock = ADRP_STEP_BLOCK;
+static_assert(kBlock % kStepBlock == 0 && kStepBlock % 32 == 0, "step blocks must tile the host path's chunk unit");
 
 template <typename T> __device__ __forceinline__ T ld(const T* base, long long D, int field, long long t) { return base[(long long)field * D + t]; }
 template <typename T> __device__ __forceinline__ void st(T* base, long long D, int field, long long t, T v) { base[(long long)field * D + t] = v; }
@@ -67,13 +76,13 @@ __device__ __forceinline__ int group_or(int v, int Mpad)
 // PHY_CT >= 0: physics mask known at compile time (specialised kernels); -1: read from the params.
 // ACTC: 0 = RPM-type actions, 1 = DSLPID-type actions.  MP: lanes per env (0 = read from the params).
 template <typename T, int PHY_CT, int ACTC, int MP>
-__global__ void __launch_bounds__(kBlock)
+__global__ void __launch_bounds__(kStepBlock, ADRP_STEP_MINB)
 step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* __restrict__ action,
             T* __restrict__ obs, T* __restrict__ reward, uint8_t* __restrict__ terminated,
             uint8_t* __restrict__ truncated, uint8_t* __restrict__ drone_flags)
 {
     const int mpad = MP > 0 ? MP : P.Mpad;
-    const long long t = (long long)P.env_begin * mpad + (long long)blockIdx.x * kBlock + threadIdx.x;
+    const long long t = (long long)P.env_begin * mpad + (long long)blockIdx.x * kStepBlock + threadIdx.x;
     const int lane = threadIdx.x & 31;
     const int i = (int)(t & (mpad - 1));
     const long long env = t / mpad;

@@ -18,3 +18,15 @@ for wl in c5 c5m c3; do
       python bench.py --workload $wl --steps 6 --warmup 3 --no-cpu-baseline > /dev/null 2>&1
 done
 ls -la gpurun_out | grep ${TAG}_
+# size sweep of the headline workload (D = 1, 2, 4, 8 x 2^20 drones on one GPU) and C3 at 8x its batch
+echo "workload,envs_per_gpu,drones,drone_steps_per_s,ms_per_step,kernel_ms,fp32_frac,hbm_frac" > gpurun_out/${TAG}_sweep_size.csv
+for spec in c5:16384 c5:32768 c5:65536 c5:131072 c5:262144 c5:524288 c5:1048576 c5m:32768 c5m:131072 c5m:524288 c3:16384 c3:131072; do
+  wl=${spec%%:*}; n=${spec##*:}
+  python bench.py --workload $wl --envs-per-gpu $n --steps 60 --warmup 6 --no-cpu-baseline 2>/dev/null | python -c "
+import json,sys
+d=json.loads(sys.stdin.read())
+c=d['config']
+print('$wl,$n,%d,%.4g,%.4f,%.4f,%.3f,%.3f' % (c['envs_per_gpu']*c['drones_per_env'], d['value'], d['ms_per_step'], d['roofline']['kernel_ms'], d['fp32_roofline']['frac'], d['roofline']['frac']))
+" >> gpurun_out/${TAG}_sweep_size.csv
+done
+cat gpurun_out/${TAG}_sweep_size.csv

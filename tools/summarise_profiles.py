@@ -72,8 +72,8 @@ def main():
     ap.add_argument("--obj", default=os.path.join(ROOT, "gym_pybullet_adrp_b200", "build"), help="object file or directory of *.o")
     a = ap.parse_args()
     src, dst = os.path.join(ROOT, "gpurun_out"), os.path.join(ROOT, "profiles")
-    for f in glob.glob(os.path.join(src, f"{a.tag}_bench_*.json")) + glob.glob(os.path.join(src, f"{a.tag}_launches_*.csv")):
-        if os.path.getsize(f):
+    for f in glob.glob(os.path.join(src, f"{a.tag}_bench_*.json")) + glob.glob(os.path.join(src, f"{a.tag}_launches_*.csv")) + glob.glob(os.path.join(src, f"{a.tag}_sweep_*.csv")):
+        if os.path.getsize(f):  # (empty: the run failed)
             shutil.copy(f, dst)
     for rep in sorted(glob.glob(os.path.join(src, f"{a.tag}_ncu_*.ncu-rep"))):
         wl = os.path.basename(rep)[len(a.tag) + 5:-8]
