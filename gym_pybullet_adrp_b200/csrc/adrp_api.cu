@@ -64,6 +64,14 @@ struct Handle : HandleBase {
 };
 
 
+// Every entry point runs on the handle's device, whatever the caller's current device is, and leaves the caller's
+// device selected on return.
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int device) { if (cudaGetDevice(&prev) == cudaSuccess && prev != device) cudaSetDevice(device); else prev = -1; }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
 int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
 
 int action_dim(int act)
@@ -317,8 +325,14 @@ int create_typed(const adrp_config* cfg, adrp_handle** out)
     h->race = cfg->env_kind == ADRP_ENV_RACE;
     derive_params<T>(*cfg, h->P);
     if (h->race) derive_race<T>(*cfg, h->P, h->RP);
-    cudaError_t e = cudaSetDevice(cfg->device);
-    if (e != cudaSuccess) { g_create_error = std::string("cudaSetDevice: ") + cudaGetErrorString(e); delete h; return ADRP_ECUDA; }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || cfg->device < 0 || cfg->device >= ndev) {
+        g_create_error = std::string("cudaSetDevice: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "invalid device ordinal");
+        delete h;
+        return ADRP_ECUDA;
+    }
+    DeviceGuard dg(cfg->device);
     int rc = alloc_buffers(h);
     if (rc == ADRP_OK) rc = do_reset<T>(h, nullptr, nullptr, nullptr, 0);
     if (rc == ADRP_OK && cudaDeviceSynchronize() != cudaSuccess) { h->err = "reset kernel failed"; rc = ADRP_ECUDA; }
@@ -366,6 +380,7 @@ int adrp_destroy(adrp_handle* h)
 {
     if (!h) return ADRP_EINVAL;
     HandleBase* b = base(h);
+    DeviceGuard dg(b->cfg.device);
     cudaDeviceSynchronize();
     if (b->precision == ADRP_F64) free_buffers(typed<double>(h)); else free_buffers(typed<float>(h));
     if (b->ev0) cudaEventDestroy(b->ev0);
@@ -381,9 +396,9 @@ int adrp_destroy(adrp_handle* h)
 
 #define BY_PRECISION(h, expr64, expr32) (base(h)->precision == ADRP_F64 ? (expr64) : (expr32))
 
-int adrp_obs_dim(const adrp_handle* h) { return BY_PRECISION(h, typed<double>(const_cast<adrp_handle*>(h))->P.O, typed<float>(const_cast<adrp_handle*>(h))->P.O); }
-int adrp_action_dim(const adrp_handle* h) { return BY_PRECISION(h, typed<double>(const_cast<adrp_handle*>(h))->P.A, typed<float>(const_cast<adrp_handle*>(h))->P.A); }
-int adrp_substeps(const adrp_handle* h) { return BY_PRECISION(h, typed<double>(const_cast<adrp_handle*>(h))->P.S, typed<float>(const_cast<adrp_handle*>(h))->P.S); }
+int adrp_obs_dim(const adrp_handle* h) { return !h ? 0 : BY_PRECISION(h, typed<double>(const_cast<adrp_handle*>(h))->P.O, typed<float>(const_cast<adrp_handle*>(h))->P.O); }
+int adrp_action_dim(const adrp_handle* h) { return !h ? 0 : BY_PRECISION(h, typed<double>(const_cast<adrp_handle*>(h))->P.A, typed<float>(const_cast<adrp_handle*>(h))->P.A); }
+int adrp_substeps(const adrp_handle* h) { return !h ? 0 : BY_PRECISION(h, typed<double>(const_cast<adrp_handle*>(h))->P.S, typed<float>(const_cast<adrp_handle*>(h))->P.S); }
 int adrp_noise_dim(const adrp_handle*) { return 7; }
 int adrp_reset_draws_dim(const adrp_handle* h)
 {
@@ -396,6 +411,7 @@ int adrp_reset_draws_dim(const adrp_handle* h)
 int adrp_reset(adrp_handle* h, const uint8_t* env_mask, const void* draws, void* obs, void* stream)
 {
     if (!h) return ADRP_EINVAL;
+    DeviceGuard dg(base(h)->cfg.device);
     cudaStream_t s = (cudaStream_t)stream;
     return BY_PRECISION(h, do_reset<double>(typed<double>(h), env_mask, (const double*)draws, (double*)obs, s),
                         do_reset<float>(typed<float>(h), env_mask, (const float*)draws, (float*)obs, s));
@@ -404,6 +420,7 @@ int adrp_reset(adrp_handle* h, const uint8_t* env_mask, const void* draws, void*
 int adrp_set_state(adrp_handle* h, const void* state, void* stream)
 {
     if (!h || !state) return ADRP_EINVAL;
+    DeviceGuard dg(base(h)->cfg.device);
     cudaStream_t s = (cudaStream_t)stream;
     base(h)->launches++;
     if (base(h)->precision == ADRP_F64) {
@@ -419,6 +436,7 @@ int adrp_set_state(adrp_handle* h, const void* state, void* stream)
 int adrp_get_state(adrp_handle* h, void* state, void* stream)
 {
     if (!h || !state) return ADRP_EINVAL;
+    DeviceGuard dg(base(h)->cfg.device);
     cudaStream_t s = (cudaStream_t)stream;
     base(h)->launches++;
     if (base(h)->precision == ADRP_F64) {
@@ -438,6 +456,7 @@ int adrp_step(adrp_handle* h, const void* action, const void* noise, void* obs, 
         if (h) base(h)->err = "adrp_step: NULL buffer";
         return ADRP_EINVAL;
     }
+    DeviceGuard dg(base(h)->cfg.device);
     cudaStream_t s = (cudaStream_t)stream;
     return BY_PRECISION(h, do_step<double>(typed<double>(h), (const double*)action, (const double*)noise, (double*)obs, (double*)reward, terminated, truncated, drone_flags, s),
                         do_step<float>(typed<float>(h), (const float*)action, (const float*)noise, (float*)obs, (float*)reward, terminated, truncated, drone_flags, s));
@@ -526,7 +545,11 @@ extern "C" {
 int adrp_step_host(adrp_handle* h, const void* action, void* obs, void* reward, uint8_t* terminated,
                    uint8_t* truncated, uint8_t* drone_flags)
 {
-    if (!h || !action || !obs || !reward || !terminated || !truncated) return ADRP_EINVAL;
+    if (!h || !action || !obs || !reward || !terminated || !truncated) {
+        if (h) base(h)->err = "adrp_step_host: NULL buffer";
+        return ADRP_EINVAL;
+    }
+    DeviceGuard dg(base(h)->cfg.device);
     return BY_PRECISION(h, do_step_host<double>(typed<double>(h), action, obs, reward, terminated, truncated, drone_flags),
                         do_step_host<float>(typed<float>(h), action, obs, reward, terminated, truncated, drone_flags));
 }

@@ -144,7 +144,7 @@ class BaseAviary:
         if isinstance(action, torch.Tensor):
             a = action.to(device=h.device, dtype=h.dtype)
         else:
-            a = torch.as_tensor(np.asarray(action), dtype=h.dtype, device=h.device)
+            a = torch.tensor(np.asarray(action), dtype=h.dtype, device=h.device)      # (copies: read-only arrays are fine)
         return a.reshape(h.N, h.M, h.A)
 
     def _out_obs(self, obs):

@@ -52,3 +52,18 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dp, f)).read()
                 assert not re.search(r"import[^\n]*oracle|from[^\n]*oracle|liboracle|oracle_lib|oracle/", src), f
+
+
+def test_no_gpu_fails_loudly_and_null_handles_are_safe(lib):
+    """No CPU fallback: a valid config on a machine without a usable device is an error with a message, and the
+    query entry points tolerate a NULL handle."""
+    import torch
+    assert lib.adrp_obs_dim(None) == 0 and lib.adrp_action_dim(None) == 0 and lib.adrp_substeps(None) == 0
+    assert lib.adrp_launch_count(None) == 0 and lib.adrp_destroy(None) == -1
+    assert lib.adrp_step_host(None, None, None, None, None, None, None) == -1
+    cfg = _abi.make_config(num_envs=4)
+    cfg.device = 9999 if torch.cuda.is_available() else 0
+    h = C.c_void_p()
+    assert lib.adrp_create(C.byref(cfg), C.byref(h)) == -2           # ADRP_ECUDA
+    assert b"cudaSetDevice" in lib.adrp_last_error(None)
+    assert not h.value
