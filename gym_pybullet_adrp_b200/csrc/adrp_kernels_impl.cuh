@@ -1,11 +1,54 @@
 // adrp_kernels_impl.cuh -- Launch<T> bodies; included by exactly one .cu per precision.
 #pragma once
+#include <cstdlib>
+#include <map>
+#include <mutex>
+#include <utility>
+
 #include "adrp_kernels.cuh"
 #include "adrp_race.cuh"
 
 namespace adrp {
 
 static_assert(kBlock == 128, "adrp_api.cu cuts host-path chunks in units of 128-thread blocks");
+
+// Launch with programmatic stream serialisation (see pdl_wait in adrp_step.cuh) when the grid is longer than one wave of
+// resident blocks: the next step's blocks then fill the slots the last wave frees (C4 +13 %, C5 +2 %).  A grid that fits
+// one wave launches plainly: its dependents would be placed into whatever slots the running grid leaves, unevenly over
+// the SMs (measured: C2 -17 %, C3 -13 %).  ADRP_PDL=0 in the environment switches it off altogether.
+template <typename... KArgs, typename... Args>
+inline void launch_pdl(void (*kernel)(KArgs...), unsigned grid, unsigned block, size_t smem, cudaStream_t s, Args... args)
+{
+    static const bool enabled = [] { const char* e = getenv("ADRP_PDL"); return !e || e[0] != '0'; }();
+    static std::mutex mu;
+    static std::map<std::pair<const void*, int>, long long> wave;     // (kernel, device) -> resident blocks of the device
+    bool pdl = false;
+    if (enabled) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        std::lock_guard<std::mutex> lock(mu);
+        auto key = std::make_pair((const void*)kernel, dev);
+        auto it = wave.find(key);
+        if (it == wave.end()) {
+            int per_sm = 0, sms = 0;
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, (int)block, smem);
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            it = wave.emplace(key, (long long)per_sm * sms).first;
+        }
+        pdl = it->second > 0 && (long long)grid > it->second;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid, 1, 1);
+    cfg.blockDim = dim3(block, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
 
 inline unsigned grid_for(long long D) { return (unsigned)((D + kBlock - 1) / kBlock); }
 
@@ -50,19 +93,19 @@ cudaError_t Launch<T>::step(const KParams<T>& P, const KBuffers<T>& b, const T* 
     const bool pid = P.action_type == ADRP_ACT_PID || P.action_type == ADRP_ACT_ONE_D_PID ||
                      P.action_type == ADRP_ACT_VEL || P.action_type == ADRP_ACT_PID_FULL;
     const unsigned grid = (unsigned)(((long long)(P.env_end - P.env_begin) * P.Mpad + kStepBlock - 1) / kStepBlock);
-#define ADRP_LAUNCH_STEP(MP) step_kernel<T, -1, 0, MP><<<grid, kStepBlock, 0, s>>>(P, b, action, obs, reward, te, tr, fl)
+#define ADRP_LAUNCH_STEP(MP) launch_pdl(step_kernel<T, -1, 0, MP>, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl)
     // product build, formations with every force model on (PYB_GND_DRAG_DW and its DYN counterpart): the physics mask
     // as a template argument drops the per-substep mask tests and 23 registers (95 -> 72), +2 % on C5
     if (!pid && M<T>::fast && (P.Mpad == 2 || P.Mpad == 4 || P.Mpad == 8)) {
         constexpr int ALL = ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW;
-#define ADRP_LAUNCH_PHY(PHY, MP) step_kernel<T, PHY, 0, MP><<<grid, kStepBlock, 0, s>>>(P, b, action, obs, reward, te, tr, fl)
+#define ADRP_LAUNCH_PHY(PHY, MP) launch_pdl(step_kernel<T, PHY, 0, MP>, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl)
 #define ADRP_LAUNCH_PHY_MP(PHY) (P.Mpad == 2 ? ADRP_LAUNCH_PHY(PHY, 2) : P.Mpad == 4 ? ADRP_LAUNCH_PHY(PHY, 4) : ADRP_LAUNCH_PHY(PHY, 8))
         if (P.physics == (ALL | ADRP_PHY_DYN)) { ADRP_LAUNCH_PHY_MP(ALL | ADRP_PHY_DYN); return cudaGetLastError(); }
         if (P.physics == (ALL | ADRP_PHY_GROUND)) { ADRP_LAUNCH_PHY_MP(ALL | ADRP_PHY_GROUND); return cudaGetLastError(); }
 #undef ADRP_LAUNCH_PHY_MP
 #undef ADRP_LAUNCH_PHY
     }
-    if (pid) step_kernel<T, -1, 1, 0><<<grid, kStepBlock, 0, s>>>(P, b, action, obs, reward, te, tr, fl);
+    if (pid) launch_pdl(step_kernel<T, -1, 1, 0>, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl);
     else switch (P.Mpad) {
         case 1: ADRP_LAUNCH_STEP(1); break;
         case 2: ADRP_LAUNCH_STEP(2); break;
@@ -143,7 +186,9 @@ cudaError_t Launch<T>::race_step(const KParams<T>& P, const RaceParams<T>& RP, c
                                  const T* action, const T* noise, T* obs, T* reward, uint8_t* te, uint8_t* tr,
                                  uint8_t* fl, cudaStream_t s)
 {
-    race_step_fn<T>(P.Mpad, P.action_type == ADRP_ACT_MEL_FULL, !noise && !RP.disturbances, P.physics)<<<(unsigned)(((long long)(P.env_end - P.env_begin) * P.Mpad + kRaceBlock - 1) / kRaceBlock), kRaceBlock, race_smem_bytes(P, RP, kRaceBlock), s>>>(P, RP, b, rb, action, noise, obs, reward, te, tr, fl);
+    launch_pdl(race_step_fn<T>(P.Mpad, P.action_type == ADRP_ACT_MEL_FULL, !noise && !RP.disturbances, P.physics),
+               (unsigned)(((long long)(P.env_end - P.env_begin) * P.Mpad + kRaceBlock - 1) / kRaceBlock), kRaceBlock,
+               race_smem_bytes(P, RP, kRaceBlock), s, P, RP, b, rb, action, noise, obs, reward, te, tr, fl);
     return cudaGetLastError();
 }
 

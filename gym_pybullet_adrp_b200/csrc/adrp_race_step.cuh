@@ -97,6 +97,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
     const int phy = PHY_CT >= 0 ? PHY_CT : P.physics;
     const long long od = valid ? env * P.M + i : 0;
 
+    pdl_wait();                                               // (the track below is rewritten by the previous step's auto-resets)
     // ---- stage the block's track instances (coalesced over envs) in shared memory
     const long long env0 = (long long)P.env_begin + (long long)blockIdx.x * EPB;
     for (int idx = threadIdx.x; idx < RP.TF * EPB; idx += kRaceBlock) {
@@ -247,6 +248,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
             mellinger_tick(RP, rb.lut, m, sp, d.p, d.q, d.v, QUIET ? (const T*)nullptr : nz + 3, R, win, s);                   // rpms[i] = recv() (:254)
         }
     }
+    pdl_launch_dependents();                                // the next step's blocks may be scheduled during the epilogue
     if (body_rates) d.w = pyb_world_rates(R, wl);           // R: the pose after the last substep
     if (M<T>::fast) d.q = canon_quat_loop(d.q);             // once per control step in the product build (adrp_physics.cuh)
     __syncthreads();                                                                     // shared track is complete

@@ -67,6 +67,13 @@ template <typename T> __device__ __forceinline__ T group_sum(T v, int Mpad)
     for (int o = Mpad >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
 }
+// Programmatic dependent launch (sm_90+): the step kernels are launched with programmatic stream serialisation, so the
+// blocks of control step n+1 are scheduled while the last wave of step n drains; they run their index arithmetic and then
+// wait here for step n to complete and flush (no global access before pdl_wait).  Both are no-ops for a kernel launched
+// without the attribute or behind a non-kernel operation.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 __device__ __forceinline__ int group_or(int v, int Mpad)
 {
     for (int o = Mpad >> 1; o > 0; o >>= 1) v |= __shfl_xor_sync(0xffffffffu, v, o);
@@ -91,6 +98,7 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
     const long long D = P.Dpad;
     const int phy = PHY_CT >= 0 ? PHY_CT : P.physics;
     const long long od = valid ? env * P.M + i : 0;      // row of this drone in (N, M, .) tensors
+    pdl_wait();
 
     Drone<T> d;
     if (valid) load_drone(b, D, t, d); else init_drone(P, 0, d);
@@ -197,6 +205,7 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
 #pragma unroll
         for (int k = 0; k < 4; ++k) d.last_rpm[k] = rpm[k];                      // :376 (S >= 1)
     }
+    pdl_launch_dependents();                             // the next step's blocks may be scheduled while this one writes out
     if (M<T>::fast) d.q = canon_quat_loop(d.q);          // once per control step in the product build (adrp_physics.cuh)
     if (body_rates) d.w = pyb_world_rates(rotmat_loop(d.q), wl);
 
