@@ -69,6 +69,19 @@ template <> struct M<float> {
         if (x < 0.0f) r = 3.141592653589793f - r;
         return copysignf(r, y);
     }
+    // Box-Muller pair for the substep loop's disturbance draws: radius sqrt(-2 ln u), u in (0, 1], through lg2.approx / sqrt.approx;
+    // sin / cos of 2 pi v, v in [0, 1), through sin.approx / cos.approx on the angle shifted into [-pi, pi) (absolute error
+    // ~5e-7 of a unit normal; the draws scale a noise of 1e-3 N)
+    static __device__ __forceinline__ void box_muller(float u, float v, float* n0, float* n1)
+    {
+        float l, sn, cs;
+        asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l) : "f"(u));
+        const float r = fsqrt(l * -1.3862943611198906f);            // -2 ln 2 * log2(u)
+        const float a = v * 6.283185307179586f - 3.141592653589793f;
+        asm("sin.approx.ftz.f32 %0, %1;" : "=f"(sn) : "f"(a));
+        asm("cos.approx.ftz.f32 %0, %1;" : "=f"(cs) : "f"(a));
+        *n0 = -(r * cs); *n1 = -(r * sn);                           // cos(a + pi) = -cos a, sin(a + pi) = -sin a
+    }
     // asin for the substep loop: Cephes asinf kernel, x + x z p(z) on |x| <= 0.5 (the usual case: pitch below 30 degrees),
     // pi/2 - 2 asin(sqrt((1 - |x|) / 2)) beyond; ~1 ulp
     static __device__ __forceinline__ float asin_poly(float x, float z)
@@ -121,6 +134,11 @@ template <> struct M<double> {
     static __device__ __forceinline__ double clamp(double v, double lo, double hi) { return v < lo ? lo : (v > hi ? hi : v); }
     static __device__ __forceinline__ double atan2_loop(double y, double x) { return ::atan2(y, x); }
     static __device__ __forceinline__ double asin_loop(double x) { return ::asin(x); }
+    static __device__ __forceinline__ void box_muller(double u, double v, double* n0, double* n1)   // (fast build only; unused here)
+    {
+        const double r = ::sqrt(-2.0 * ::log(u));
+        *n0 = r * ::cos(6.283185307179586 * v); *n1 = r * ::sin(6.283185307179586 * v);
+    }
     static __device__ __forceinline__ void cos_sinc_sq(double z, double* c, double* sinc)
     {
         const double th = ::sqrt(z);

@@ -154,8 +154,11 @@ __device__ __forceinline__ void store_body(const RaceBuffers<T>& rb, long long D
 template <typename T>
 __device__ __forceinline__ void race_write_obs(const KParams<T>& P, const RaceParams<T>& RP, const T* trk, int EPB, int e,
                                                const Drone<T>& d, const V3<T>& rpy, T hz, int current_gate, int i, int lane_base,
-                                               bool valid, T* __restrict__ o)
+                                               bool valid, T* __restrict__ o, T* min_dist = nullptr)
 {
+    // min_dist: smallest drone-to-gate / drone-to-obstacle distance of this drone, the same gate_distance / obstacle_distance
+    // values the visibility flags use -- the step kernel's contact test (_collision, :552-562) compares it with its margin
+    T dmin = T(1e30);
     if (valid) {
         o[0] = d.p.x; o[1] = d.p.y; o[2] = d.p.z; o[3] = rpy.x; o[4] = rpy.y; o[5] = rpy.z;
         o[6] = d.v.x; o[7] = d.v.y; o[8] = d.v.z; o[9] = d.w.x; o[10] = d.w.y; o[11] = d.w.z;
@@ -163,7 +166,9 @@ __device__ __forceinline__ void race_write_obs(const KParams<T>& P, const RacePa
         for (int g = 0; g < RP.G; ++g) {
             const T* tg = trk + (kGateFields * g) * EPB + e;
             const T x = tg[0], y = tg[EPB], z = tg[2 * EPB], yaw = tg[3 * EPB], c = tg[4 * EPB], s = tg[5 * EPB];
-            const bool in_range = gate_distance(d.p, hz, P.coll_r, x, y, z, c, s, RP.gate_type[g]) < RP.visibility;   // :614-626
+            const T dist = gate_distance(d.p, hz, P.coll_r, x, y, z, c, s, RP.gate_type[g]);
+            dmin = dist < dmin ? dist : dmin;
+            const bool in_range = dist < RP.visibility;                                                                  // :614-626
             o[k + 4 * g] = in_range ? x : RP.gate_nom[g][0];
             o[k + 4 * g + 1] = in_range ? y : RP.gate_nom[g][1];
             o[k + 4 * g + 2] = in_range ? z : RP.gate_nom[g][2];
@@ -174,7 +179,9 @@ __device__ __forceinline__ void race_write_obs(const KParams<T>& P, const RacePa
         for (int b = 0; b < RP.NO; ++b) {
             const T* to = trk + (kGateFields * RP.G + kObstFields * b) * EPB + e;
             const T x = to[0], y = to[EPB], z = to[2 * EPB];
-            const bool in_range = obstacle_distance(d.p, hz, P.coll_r, x, y, z) < RP.visibility;                        // :631-643
+            const T dist = obstacle_distance(d.p, hz, P.coll_r, x, y, z);
+            dmin = dist < dmin ? dist : dmin;
+            const bool in_range = dist < RP.visibility;                                                                  // :631-643
             o[k + 3 * b] = in_range ? x : RP.obst_nom[b][0];
             o[k + 3 * b + 1] = in_range ? y : RP.obst_nom[b][1];
             o[k + 3 * b + 2] = in_range ? z : RP.obst_nom[b][2];
@@ -183,6 +190,7 @@ __device__ __forceinline__ void race_write_obs(const KParams<T>& P, const RacePa
         k += 4 * RP.NO;
         o[k] = (T)current_gate;                                                                                          // :651
     }
+    if (min_dist) *min_dist = dmin;
     if (RP.compete) {                                                                                                   // :654-659
         int k = 12 + 5 * RP.G + 4 * RP.NO + 1;
         for (int j = 0; j < P.Mpad; ++j) {

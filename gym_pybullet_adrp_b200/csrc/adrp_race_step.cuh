@@ -200,13 +200,21 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
             philox4x32(genv, (uint32_t)(128 + i), tick, (uint32_t)episode, RP.seed_lo, RP.seed_hi, o1);
 #pragma unroll
             for (int k = 0; k < 3; ++k) nz[k] = RP.wind_lo[k] + u01<T>(o0[k]) * (RP.wind_hi[k] - RP.wind_lo[k]);
-            const T r0 = M<T>::sqrt(T(-2) * M<T>::log(u01_open<T>(o1[0]))), r1 = M<T>::sqrt(T(-2) * M<T>::log(u01_open<T>(o1[2])));
-            const T a0 = T(6.283185307179586) * u01<T>(o1[1]), a1 = T(6.283185307179586) * u01<T>(o1[3]);
-            T s0, c0, s1, c1;
-            M<T>::sincos(a0, &s0, &c0);
-            M<T>::sincos(a1, &s1, &c1);
-            nz[3] = RP.noise_std * r0 * c0; nz[4] = RP.noise_std * r0 * s0;
-            nz[5] = RP.noise_std * r1 * c1; nz[6] = RP.noise_std * r1 * s1;
+            if (M<T>::fast) {
+                T g0, g1, g2, g3;
+                M<T>::box_muller(u01_open<T>(o1[0]), u01<T>(o1[1]), &g0, &g1);
+                M<T>::box_muller(u01_open<T>(o1[2]), u01<T>(o1[3]), &g2, &g3);
+                nz[3] = RP.noise_std * g0; nz[4] = RP.noise_std * g1;
+                nz[5] = RP.noise_std * g2; nz[6] = RP.noise_std * g3;
+            } else {
+                const T r0 = M<T>::sqrt(T(-2) * M<T>::log(u01_open<T>(o1[0]))), r1 = M<T>::sqrt(T(-2) * M<T>::log(u01_open<T>(o1[2])));
+                const T a0 = T(6.283185307179586) * u01<T>(o1[1]), a1 = T(6.283185307179586) * u01<T>(o1[3]);
+                T s0, c0, s1, c1;
+                M<T>::sincos(a0, &s0, &c0);
+                M<T>::sincos(a1, &s1, &c1);
+                nz[3] = RP.noise_std * r0 * c0; nz[4] = RP.noise_std * r0 * s0;
+                nz[5] = RP.noise_std * r1 * c1; nz[6] = RP.noise_std * r1 * s1;
+            }
         }
         // _apply_physics(self.rpms, self.prev_rpms) (:510-548): forces from the substep-start state
         if (!M<T>::fast) R = rotmat_loop(d.q);
@@ -295,22 +303,16 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
     // ---- observation (:566-661)
     const V3<T> rpy = euler_rpy(d.q);
     const T hz = drone_half_height(P.coll_r, P.coll_h, Rn.m22);
-    race_write_obs(P, RP, trk, EPB, e, d, rpy, hz, current_gate, i, lane_base, valid, obs + od * P.O);
+    T track_gap;                                             // closest gate / obstacle, from the observation's visibility tests
+    race_write_obs(P, RP, trk, EPB, e, d, rpy, hz, current_gate, i, lane_base, valid, obs + od * P.O, &track_gap);
 
     // ---- _computeTerminated (:674-698) with _collision (:552-562)
     int fl = 0;
     if (M<T>::abs(d.p.x) > RP.bounds_hi[0] || M<T>::abs(d.p.y) > RP.bounds_hi[1] || M<T>::abs(d.p.z) > RP.bounds_hi[2]) fl |= ADRP_FLAG_OUT_OF_BOUNDS;   // :684
     if (M<T>::abs(d.w.x) > T(20) || M<T>::abs(d.w.y) > T(20) || M<T>::abs(d.w.z) > T(20)) fl |= ADRP_FLAG_UNSTABLE;                                      // :685
     if (!(phy & ADRP_PHY_DYN)) {                               // getContactPoints reflects the last stepSimulation: never in DYN
-        bool crashed = false;
-        for (int g = 0; g < RP.G; ++g) {
-            const T* tg = trk + (kGateFields * g) * EPB + e;
-            crashed = crashed || gate_distance(d.p, hz, P.coll_r, tg[0], tg[EPB], tg[2 * EPB], tg[4 * EPB], tg[5 * EPB], RP.gate_type[g]) < RP.contact_margin;
-        }
-        for (int ob = 0; ob < RP.NO; ++ob) {
-            const T* to = trk + (kGateFields * RP.G + kObstFields * ob) * EPB + e;
-            crashed = crashed || obstacle_distance(d.p, hz, P.coll_r, to[0], to[EPB], to[2 * EPB]) < RP.contact_margin;
-        }
+        // any gate or obstacle closer than the margin: min over the distances <=> OR over the comparisons (same values)
+        bool crashed = track_gap < RP.contact_margin;
         crashed = crashed || (d.p.z - hz < RP.contact_margin);                           // plane
         if (RP.compete) {                                                                // drones collide with each other (:153-154)
             for (int j = 0; j < mpad; ++j) {
