@@ -94,16 +94,23 @@ cudaError_t Launch<T>::step(const KParams<T>& P, const KBuffers<T>& b, const T* 
                      P.action_type == ADRP_ACT_VEL || P.action_type == ADRP_ACT_PID_FULL;
     const unsigned grid = (unsigned)(((long long)(P.env_end - P.env_begin) * P.Mpad + kStepBlock - 1) / kStepBlock);
 #define ADRP_LAUNCH_STEP(MP) launch_pdl(step_kernel<T, -1, 0, MP>, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl)
-    // product build, formations with every force model on (PYB_GND_DRAG_DW and its DYN counterpart): the physics mask
-    // as a template argument drops the per-substep mask tests and 23 registers (95 -> 72), +2 % on C5
-    if (!pid && M<T>::fast && (P.Mpad == 2 || P.Mpad == 4 || P.Mpad == 8)) {
-        constexpr int ALL = ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW;
-#define ADRP_LAUNCH_PHY(PHY, MP) launch_pdl(step_kernel<T, PHY, 0, MP>, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl)
-#define ADRP_LAUNCH_PHY_MP(PHY) (P.Mpad == 2 ? ADRP_LAUNCH_PHY(PHY, 2) : P.Mpad == 4 ? ADRP_LAUNCH_PHY(PHY, 4) : ADRP_LAUNCH_PHY(PHY, 8))
-        if (P.physics == (ALL | ADRP_PHY_DYN)) { ADRP_LAUNCH_PHY_MP(ALL | ADRP_PHY_DYN); return cudaGetLastError(); }
-        if (P.physics == (ALL | ADRP_PHY_GROUND)) { ADRP_LAUNCH_PHY_MP(ALL | ADRP_PHY_GROUND); return cudaGetLastError(); }
-#undef ADRP_LAUNCH_PHY_MP
-#undef ADRP_LAUNCH_PHY
+    // product build: the all-forces masks have instances with the mask as a template argument (no per-substep mask tests,
+    // 95 -> 64 registers: C5 +2 %), compiled in their own translation unit (step_special).  The plain masks (Physics.PYB / DYN)
+    // stay on the generic instance: their specialisation (80 -> 72 registers, a seventh block per SM) measured +5 % on C2 at
+    // 65 536 envs but -4 % at 262 144 and -8 % at 1 048 576 (memory-bound, more resident blocks thrash).
+    if constexpr (M<T>::fast) {
+        static const bool generic = [] { const char* e = getenv("ADRP_STEP_GENERIC"); return e && e[0] == '1'; }();   // diagnostic
+        if (!pid && !generic) {
+            StepFnF32 f = nullptr;
+            switch (P.physics) {
+                case ADRP_PHY_DYN | ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW:
+                    f = step_special<ADRP_PHY_DYN | ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW>(P.Mpad); break;
+                case ADRP_PHY_GROUND | ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW:
+                    f = step_special<ADRP_PHY_GROUND | ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW>(P.Mpad); break;
+                default: break;
+            }
+            if (f) { launch_pdl(f, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl); return cudaGetLastError(); }
+        }
     }
     if (pid) launch_pdl(step_kernel<T, -1, 1, 0>, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl);
     else switch (P.Mpad) {
