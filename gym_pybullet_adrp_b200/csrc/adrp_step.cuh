@@ -74,6 +74,13 @@ template <typename T> __device__ __forceinline__ T group_sum(T v, int Mpad)
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
+// Action ring of the RL aviaries: element (slot, component k) of padded drone t.  Slot-major, then drone, then component, so
+// the A components of one slot are adjacent: a 4-component action is one 16-byte access, coalesced over the warp.
+__device__ __forceinline__ long long ring_idx(long long D, int A, int slot, int k, long long t)
+{
+    return ((long long)slot * D + t) * A + k;
+}
+
 __device__ __forceinline__ int group_or(int v, int Mpad)
 {
     for (int o = Mpad >> 1; o > 0; o >>= 1) v |= __shfl_xor_sync(0xffffffffu, v, o);
@@ -246,23 +253,36 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
         // action buffer (deque(maxlen=ctrl_freq//2), BaseRLAviary.py:66-67,187): the newest action
         // overwrites the oldest ring slot; the observation lists the slots oldest -> newest
         head = b.ring_head[env];
-#pragma unroll
-        for (int k = 0; k < AMAX; ++k)
-            if (k < P.A) st(b.ring, D, head * P.A + k, t, act_in[k]);
         const int nh = head + 1 == P.B ? 0 : head + 1;
-        if (vec) {                                             // P.A == 4: one 16-byte store per ring slot
+        if (vec) {                                             // P.A == 4: one 16-byte access per ring slot
+            float4* r4 = reinterpret_cast<float4*>(b.ring);
             float4* o4 = reinterpret_cast<float4*>(o) + 3;
-            for (int j = 0; j < P.B; ++j) {
-                int slot = nh + j;
-                if (slot >= P.B) slot -= P.B;
-                o4[j] = make_float4((float)ld(b.ring, D, slot * 4, t), (float)ld(b.ring, D, slot * 4 + 1, t),
-                                    (float)ld(b.ring, D, slot * 4 + 2, t), (float)ld(b.ring, D, slot * 4 + 3, t));
+            const float4 newest = make_float4((float)act_in[0], (float)act_in[1], (float)act_in[2], (float)act_in[3]);
+            r4[(long long)head * D + t] = newest;
+            // eight slots in flight before the first store (the ring may alias the observation as far as the compiler knows:
+            // slot by slot the loop is one L2 round trip per slot, 40 % of the warp's time in the C2 capture); the newest slot
+            // comes from the registers
+            for (int j0 = 0; j0 < P.B; j0 += 8) {
+                float4 v[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    int slot = nh + j0 + u;
+                    if (slot >= P.B) slot -= P.B;
+                    if (j0 + u < P.B - 1) v[u] = r4[(long long)slot * D + t];
+                    else v[u] = newest;
+                }
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    if (j0 + u < P.B) o4[j0 + u] = v[u];
             }
         } else {
+#pragma unroll
+            for (int k = 0; k < AMAX; ++k)
+                if (k < P.A) b.ring[ring_idx(D, P.A, head, k, t)] = act_in[k];
             for (int j = 0; j < P.B; ++j) {
                 int slot = nh + j;
                 if (slot >= P.B) slot -= P.B;
-                for (int k = 0; k < P.A; ++k) o[12 + j * P.A + k] = ld(b.ring, D, slot * P.A + k, t);
+                for (int k = 0; k < P.A; ++k) o[12 + j * P.A + k] = b.ring[ring_idx(D, P.A, slot, k, t)];
             }
         }
         head = nh;
@@ -303,7 +323,8 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
             init_drone(P, i, d);
             pc.ipos = pc.irpy = pc.last_rpy = {T(0), T(0), T(0)};
             if (P.env_kind != ADRP_ENV_CTRL)
-                for (int k = 0; k < P.B * P.A; ++k) st(b.ring, D, k, t, T(0));
+                for (int sl = 0; sl < P.B; ++sl)
+                    for (int k = 0; k < P.A; ++k) b.ring[ring_idx(D, P.A, sl, k, t)] = T(0);
         }
         store_drone(b, D, t, d);
         if (ACTC == 1) {
@@ -351,7 +372,8 @@ __global__ void reset_kernel(const KParams<T> P, KBuffers<T> b, const uint8_t* _
     init_drone(P, i, d);
     store_drone(b, P.Dpad, t, d);
     for (int k = 0; k < 9; ++k) b.pid[(long long)k * P.Dpad + t] = T(0);
-    for (int k = 0; k < P.B * P.A; ++k) b.ring[(long long)k * P.Dpad + t] = T(0);
+    for (int sl = 0; sl < P.B; ++sl)
+        for (int k = 0; k < P.A; ++k) b.ring[ring_idx(P.Dpad, P.A, sl, k, t)] = T(0);
     if (i == 0) { b.step_counter[env] = 0; b.ring_head[env] = 0; }
     if (obs) {
         T* o = obs + (env * P.M + i) * P.O;
