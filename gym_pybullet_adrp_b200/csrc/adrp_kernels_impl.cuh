@@ -94,15 +94,16 @@ cudaError_t Launch<T>::step(const KParams<T>& P, const KBuffers<T>& b, const T* 
                      P.action_type == ADRP_ACT_VEL || P.action_type == ADRP_ACT_PID_FULL;
     const unsigned grid = (unsigned)(((long long)(P.env_end - P.env_begin) * P.Mpad + kStepBlock - 1) / kStepBlock);
 #define ADRP_LAUNCH_STEP(MP) launch_pdl(step_kernel<T, -1, 0, MP>, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl)
-    // product build: the all-forces masks have instances with the mask as a template argument (no per-substep mask tests,
-    // 95 -> 64 registers: C5 +2 %), compiled in their own translation unit (step_special).  The plain masks (Physics.PYB / DYN)
-    // stay on the generic instance: their specialisation (80 -> 72 registers, a seventh block per SM) measured +5 % on C2 at
-    // 65 536 envs but -4 % at 262 144 and -8 % at 1 048 576 (memory-bound, more resident blocks thrash).
+    // product build: the masks the configs use (Physics.DYN, Physics.PYB and the two all-forces masks) have instances with the
+    // mask as a template argument (no per-substep mask tests, fewer registers: C5 +2 %, C2 +2 % at every batch size measured),
+    // compiled in their own translation units (step_special)
     if constexpr (M<T>::fast) {
         static const bool generic = [] { const char* e = getenv("ADRP_STEP_GENERIC"); return e && e[0] == '1'; }();   // diagnostic
         if (!pid && !generic) {
             StepFnF32 f = nullptr;
             switch (P.physics) {
+                case ADRP_PHY_DYN: f = step_special<ADRP_PHY_DYN>(P.Mpad); break;
+                case ADRP_PHY_GROUND: f = step_special<ADRP_PHY_GROUND>(P.Mpad); break;
                 case ADRP_PHY_DYN | ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW:
                     f = step_special<ADRP_PHY_DYN | ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW>(P.Mpad); break;
                 case ADRP_PHY_GROUND | ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW:

@@ -1,5 +1,5 @@
 // adrp_step_special.cuh -- step_kernel instances of the fp32 product build for ONE physics mask (template argument), RPM-type
-// actions, 1 / 2 / 4 / 8 lanes per env.  Included by adrp_step_f32_forces.cu only.
+// actions, 1 / 2 / 4 / 8 lanes per env.  Included by adrp_step_f32_plain.cu / adrp_step_f32_forces.cu only.
 #pragma once
 #include "adrp_kernels.cuh"
 #include "adrp_step.cuh"
