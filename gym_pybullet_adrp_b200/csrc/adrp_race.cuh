@@ -159,6 +159,10 @@ __device__ __forceinline__ void race_write_obs(const KParams<T>& P, const RacePa
     // min_dist: smallest drone-to-gate / drone-to-obstacle distance of this drone, the same gate_distance / obstacle_distance
     // values the visibility flags use -- the step kernel's contact test (_collision, :552-562) compares it with its margin
     T dmin = T(1e30);
+    // distances reported for culled bodies: above both thresholds, so every comparison made with them is the exact one's
+    const T thr = (RP.visibility > RP.contact_margin ? RP.visibility : RP.contact_margin) + T(0.01);
+    const T far_gate = T(0.2513) + P.coll_r + thr, far_obst = T(0.1061) + P.coll_r + thr;
+    const T far_gate2 = far_gate * far_gate, far_obst2 = far_obst * far_obst;
     if (valid) {
         o[0] = d.p.x; o[1] = d.p.y; o[2] = d.p.z; o[3] = rpy.x; o[4] = rpy.y; o[5] = rpy.z;
         o[6] = d.v.x; o[7] = d.v.y; o[8] = d.v.z; o[9] = d.w.x; o[10] = d.w.y; o[11] = d.w.z;
@@ -166,7 +170,12 @@ __device__ __forceinline__ void race_write_obs(const KParams<T>& P, const RacePa
         for (int g = 0; g < RP.G; ++g) {
             const T* tg = trk + (kGateFields * g) * EPB + e;
             const T x = tg[0], y = tg[EPB], z = tg[2 * EPB], yaw = tg[3 * EPB], c = tg[4 * EPB], s = tg[5 * EPB];
-            const T dist = gate_distance(d.p, hz, P.coll_r, x, y, z, c, s, RP.gate_type[g]);
+            // every part of a gate lies within 0.2513 m (horizontally) of its centre: a drone further away than that plus its own
+            // radius plus the larger of the two thresholds (and a centimetre for rounding) is neither in range nor in contact,
+            // whatever the exact distance is -- the five prism distances are only evaluated near the gate
+            const T gdx = d.p.x - x, gdy = d.p.y - y;
+            T dist = far_gate;
+            if (gdx * gdx + gdy * gdy <= far_gate2) dist = gate_distance(d.p, hz, P.coll_r, x, y, z, c, s, RP.gate_type[g]);
             dmin = dist < dmin ? dist : dmin;
             const bool in_range = dist < RP.visibility;                                                                  // :614-626
             o[k + 4 * g] = in_range ? x : RP.gate_nom[g][0];
@@ -179,7 +188,9 @@ __device__ __forceinline__ void race_write_obs(const KParams<T>& P, const RacePa
         for (int b = 0; b < RP.NO; ++b) {
             const T* to = trk + (kGateFields * RP.G + kObstFields * b) * EPB + e;
             const T x = to[0], y = to[EPB], z = to[2 * EPB];
-            const T dist = obstacle_distance(d.p, hz, P.coll_r, x, y, z);
+            const T odx = d.p.x - x, ody = d.p.y - y;                      // obstacle parts: within 0.1061 m of the axis
+            T dist = far_obst;
+            if (odx * odx + ody * ody <= far_obst2) dist = obstacle_distance(d.p, hz, P.coll_r, x, y, z);
             dmin = dist < dmin ? dist : dmin;
             const bool in_range = dist < RP.visibility;                                                                  // :631-643
             o[k + 3 * b] = in_range ? x : RP.obst_nom[b][0];

@@ -275,6 +275,8 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
         const T half_length = T(0.1875);
         const T delta_x = T(0.05) * gc, delta_y = T(0.05) * gs;
         const V3<T> dir = {T(0), T(0), (height + half_length) - (height - half_length)};
+        const T hh_ = T(0.5) * P.coll_h;
+        const T ray_reach = T(0.16) + M<T>::sqrt(P.coll_r * P.coll_r + hh_ * hh_), ray_reach2 = ray_reach * ray_reach;
         T best[7];
         int best_id[7];
 #pragma unroll
@@ -284,6 +286,10 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
             const V3<T> cj = {__shfl_sync(0xffffffffu, d.p.x, src), __shfl_sync(0xffffffffu, d.p.y, src), __shfl_sync(0xffffffffu, d.p.z, src)};
             const V3<T> aj = {__shfl_sync(0xffffffffu, axis.x, src), __shfl_sync(0xffffffffu, axis.y, src), __shfl_sync(0xffffffffu, axis.z, src)};
             if (!active || j >= P.M) continue;
+            // the seven rays are vertical and start within 0.15 m of the gate centre: a cylinder whose centre is further away
+            // (horizontally) than that plus its bounding radius cannot be hit by any of them
+            const T jdx = cj.x - gx, jdy = cj.y - gy;
+            if (jdx * jdx + jdy * jdy > ray_reach2) continue;
 #pragma unroll
             for (int k = 0; k < 7; ++k) {
                 // ray order of the reference: centre, +1, -1, +2, -2, +3, -3
