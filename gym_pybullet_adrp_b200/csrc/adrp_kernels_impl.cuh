@@ -102,12 +102,12 @@ cudaError_t Launch<T>::step(const KParams<T>& P, const KBuffers<T>& b, const T* 
         if (!pid && !generic) {
             StepFnF32 f = nullptr;
             switch (P.physics) {
-                case ADRP_PHY_DYN: f = step_special<ADRP_PHY_DYN>(P.Mpad); break;
-                case ADRP_PHY_GROUND: f = step_special<ADRP_PHY_GROUND>(P.Mpad); break;
+                case ADRP_PHY_DYN: f = step_special<ADRP_PHY_DYN>(P.Mpad, P.env_kind == ADRP_ENV_CTRL); break;
+                case ADRP_PHY_GROUND: f = step_special<ADRP_PHY_GROUND>(P.Mpad, P.env_kind == ADRP_ENV_CTRL); break;
                 case ADRP_PHY_DYN | ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW:
-                    f = step_special<ADRP_PHY_DYN | ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW>(P.Mpad); break;
+                    f = step_special<ADRP_PHY_DYN | ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW>(P.Mpad, P.env_kind == ADRP_ENV_CTRL); break;
                 case ADRP_PHY_GROUND | ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW:
-                    f = step_special<ADRP_PHY_GROUND | ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW>(P.Mpad); break;
+                    f = step_special<ADRP_PHY_GROUND | ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW>(P.Mpad, P.env_kind == ADRP_ENV_CTRL); break;
                 default: break;
             }
             if (f) { launch_pdl(f, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl); return cudaGetLastError(); }

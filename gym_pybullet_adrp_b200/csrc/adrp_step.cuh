@@ -18,6 +18,13 @@ constexpr int kBlock = 128;
 #define ADRP_STEP_MINB 1
 #endif
 constexpr int kStepBlock = ADRP_STEP_BLOCK;
+// Ring slots loaded before the first observation store of the RL aviaries' action-buffer copy.  The registers of the batch
+// count for EVERY instance of step_kernel (the env kind is a run-time branch): 8 slots took the all-forces instances from 88 to
+// 110 registers and C5 from 1.18e10 to 1.09e10 drone-steps/s.
+#ifndef ADRP_RING_BATCH
+#define ADRP_RING_BATCH 4
+#endif
+constexpr int kRingBatchGeneric = ADRP_RING_BATCH;       // (the RL-only instances, ENVK = 1, take 8)
 static_assert(kBlock % kStepBlock == 0 && kStepBlock % 32 == 0, "step blocks must tile the host path's chunk unit");
 
 template <typename T> __device__ __forceinline__ T ld(const T* base, long long D, int field, long long t) { return base[(long long)field * D + t]; }
@@ -89,7 +96,10 @@ __device__ __forceinline__ int group_or(int v, int Mpad)
 
 // PHY_CT >= 0: physics mask known at compile time (specialised kernels); -1: read from the params.
 // ACTC: 0 = RPM-type actions, 1 = DSLPID-type actions.  MP: lanes per env (0 = read from the params).
-template <typename T, int PHY_CT, int ACTC, int MP>
+// ENVK: -1 = env kind read from the params; 0 = CtrlAviary-kind (20-float rows, no reward / action buffer) compiled in;
+// 1 = an RL aviary (Hover / MultiHover, told apart at run time) compiled in.  The epilogues of the two families differ
+// a lot (5 stores vs. the action-buffer copy), and the registers of the larger one count for the whole kernel.
+template <typename T, int PHY_CT, int ACTC, int MP, int ENVK = -1>
 __global__ void __launch_bounds__(kStepBlock, ADRP_STEP_MINB)
 step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* __restrict__ action,
             T* __restrict__ obs, T* __restrict__ reward, uint8_t* __restrict__ terminated,
@@ -104,6 +114,8 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
     const bool valid = env < P.env_end && i < P.M;
     const long long D = P.Dpad;
     const int phy = PHY_CT >= 0 ? PHY_CT : P.physics;
+    const bool is_ctrl = ENVK == 0 ? true : (ENVK == 1 ? false : P.env_kind == ADRP_ENV_CTRL);
+    constexpr int kRingBatch = ENVK == 1 ? 8 : kRingBatchGeneric;
     const long long od = valid ? env * P.M + i : 0;      // row of this drone in (N, M, .) tensors
     pdl_wait();
 
@@ -219,13 +231,13 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
     // ---- observation (CtrlAviary.py:106-117; BaseRLAviary.py:284-322).  CtrlAviary has no flag that depends on the
     // Euler angles, so the product build may use the loop's polynomial atan2 there (1 ulp); the RL aviaries threshold
     // |roll|, |pitch| and keep libm, so that their flags stay a bit-exact function of the stored state
-    const V3<T> rpy = P.env_kind == ADRP_ENV_CTRL ? euler_rpy_loop(d.q) : euler_rpy(d.q);
+    const V3<T> rpy = is_ctrl ? euler_rpy_loop(d.q) : euler_rpy(d.q);
     T* o = obs + od * P.O;
     int head = 0;
     // fp32 build: rows whose length is a multiple of 4 floats go out as 16-byte stores (a warp's scalar store of one
     // column touches 32 sectors for 128 useful bytes; the float4 form moves 4x the payload per sector access)
     const bool vec = M<T>::fast && P.obs_vec;
-    if (P.env_kind == ADRP_ENV_CTRL) {
+    if (is_ctrl) {
         if (valid && vec) {
             float4* o4 = reinterpret_cast<float4*>(o);
             o4[0] = make_float4((float)d.p.x, (float)d.p.y, (float)d.p.z, (float)d.q.x);
@@ -259,20 +271,20 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
             float4* o4 = reinterpret_cast<float4*>(o) + 3;
             const float4 newest = make_float4((float)act_in[0], (float)act_in[1], (float)act_in[2], (float)act_in[3]);
             r4[(long long)head * D + t] = newest;
-            // eight slots in flight before the first store (the ring may alias the observation as far as the compiler knows:
+            // kRingBatch slots in flight before the first store (the ring may alias the observation as far as the compiler knows:
             // slot by slot the loop is one L2 round trip per slot, 40 % of the warp's time in the C2 capture); the newest slot
             // comes from the registers
-            for (int j0 = 0; j0 < P.B; j0 += 8) {
-                float4 v[8];
+            for (int j0 = 0; j0 < P.B; j0 += kRingBatch) {
+                float4 v[kRingBatch];
 #pragma unroll
-                for (int u = 0; u < 8; ++u) {
+                for (int u = 0; u < kRingBatch; ++u) {
                     int slot = nh + j0 + u;
                     if (slot >= P.B) slot -= P.B;
                     if (j0 + u < P.B - 1) v[u] = r4[(long long)slot * D + t];
                     else v[u] = newest;
                 }
 #pragma unroll
-                for (int u = 0; u < 8; ++u)
+                for (int u = 0; u < kRingBatch; ++u)
                     if (j0 + u < P.B) o4[j0 + u] = v[u];
             }
         } else {
@@ -292,7 +304,7 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
     T rew = T(-1);
     int term = 0, trunc = 0;
     const int counter = env < P.env_end ? b.step_counter[env] : 0;
-    if (P.env_kind != ADRP_ENV_CTRL) {
+    if (!is_ctrl) {
         T r = T(0), dist = T(0);
         int tr = 0;
         if (valid) {
@@ -313,7 +325,7 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
         terminated[env] = (uint8_t)term;
         truncated[env] = (uint8_t)trunc;
         b.step_counter[env] = done ? 0 : counter + P.S;                          // BaseAviary.py:386
-        if (P.env_kind != ADRP_ENV_CTRL) b.ring_head[env] = done ? 0 : head;
+        if (!is_ctrl) b.ring_head[env] = done ? 0 : head;
     }
     if (valid && drone_flags) drone_flags[od] = 0;
 
@@ -322,7 +334,7 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
         if (done) {
             init_drone(P, i, d);
             pc.ipos = pc.irpy = pc.last_rpy = {T(0), T(0), T(0)};
-            if (P.env_kind != ADRP_ENV_CTRL)
+            if (!is_ctrl)
                 for (int sl = 0; sl < P.B; ++sl)
                     for (int k = 0; k < P.A; ++k) b.ring[ring_idx(D, P.A, sl, k, t)] = T(0);
         }

@@ -1,21 +1,32 @@
 // adrp_step_special.cuh -- step_kernel instances of the fp32 product build for ONE physics mask (template argument), RPM-type
-// actions, 1 / 2 / 4 / 8 lanes per env.  Included by adrp_step_f32_plain.cu / adrp_step_f32_forces.cu only.
+// actions, 1 / 2 / 4 / 8 lanes per env, with the env family compiled in (CtrlAviary-kind or RL aviary).  Included by
+// adrp_step_f32_plain.cu / adrp_step_f32_forces.cu only.
 #pragma once
 #include "adrp_kernels.cuh"
 #include "adrp_step.cuh"
 
 namespace adrp {
 
-template <int PHY>
-StepFnF32 step_special(int mpad)
+template <int PHY, int ENVK>
+StepFnF32 step_special_mp(int mpad)
 {
     switch (mpad) {
-        case 1: return step_kernel<float, PHY, 0, 1>;
-        case 2: return step_kernel<float, PHY, 0, 2>;
-        case 4: return step_kernel<float, PHY, 0, 4>;
-        case 8: return step_kernel<float, PHY, 0, 8>;
+        case 1: return step_kernel<float, PHY, 0, 1, ENVK>;
+        case 2: return step_kernel<float, PHY, 0, 2, ENVK>;
+        case 4: return step_kernel<float, PHY, 0, 4, ENVK>;
+        case 8: return step_kernel<float, PHY, 0, 8, ENVK>;
         default: return nullptr;
     }
+}
+
+// ctrl: CtrlAviary-kind env; rl_too: this mask also has RL-aviary instances (the plain masks: learn.py / HoverAviary shapes)
+template <int PHY>
+StepFnF32 step_special(int mpad, bool ctrl)
+{
+    constexpr bool rl_too = PHY == ADRP_PHY_DYN || PHY == ADRP_PHY_GROUND;
+    if (ctrl) return step_special_mp<PHY, 0>(mpad);
+    if constexpr (rl_too) return step_special_mp<PHY, 1>(mpad);
+    return nullptr;
 }
 
 }  // namespace adrp
