@@ -1,0 +1,71 @@
+"""GPU: the launch-time choices of the library do not change results.
+
+* Programmatic dependent launch (grids longer than one wave) against plain launches (`ADRP_PDL=0`): bit-identical --
+  back-to-back control steps where step n+1's blocks are scheduled while step n drains must still see all of step n.
+* The physics-mask / env-family instances of the step kernel against the generic instance (`ADRP_STEP_GENERIC=1`):
+  same formulas, but the compiler may contract multiply-adds differently, so the comparison is at 1e-5.
+
+Both switches are read once per process, hence the subprocesses.
+"""
+import hashlib
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+SCRIPT = r"""
+import hashlib, json, sys
+import numpy as np
+sys.path.insert(0, %(root)r)
+import bench
+from gym_pybullet_adrp_b200 import _lib
+wl, n, steps = %(wl)r, %(n)d, %(steps)d
+M = bench.WORKLOADS[wl][1]
+h = _lib.Handle(bench.make_cfg(wl, n))
+if bench.WORKLOADS[wl][5] == bench._abi.ENV_CTRL:
+    h.set_state(bench.initial_state(wl, n, M, 21))
+else:
+    h.reset()
+acts = bench.make_actions(wl, n, M, h.A, 21, 4)
+import torch
+dev = [torch.as_tensor(a, device=h.device) for a in acts]
+for k in range(steps):                                   # back to back, no host synchronisation in between
+    h.step(dev[k %% 4])
+torch.cuda.synchronize()
+obs = h.obs.cpu().numpy()
+st = h.get_state().cpu().numpy()
+print(json.dumps({"obs_sha": hashlib.sha256(obs.tobytes()).hexdigest(), "state_sha": hashlib.sha256(st.tobytes()).hexdigest(),
+                  "obs_sample": obs.reshape(-1)[::997][:4096].astype(float).tolist(), "finite": bool(np.isfinite(obs).all())}))
+"""
+
+
+def _run(wl, n, steps, **env):
+    e = dict(os.environ)
+    e.update(env)
+    out = subprocess.run([sys.executable, "-c", SCRIPT % {"root": ROOT, "wl": wl, "n": n, "steps": steps}],
+                         capture_output=True, text=True, env=e, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    return json.loads(out.stdout.strip().splitlines()[-1])
+
+
+@pytest.mark.parametrize("wl,n", [("c4", 32768), ("c5m", 32768), ("c2", 262144)])
+def test_programmatic_launch_is_bit_identical(wl, n):
+    """Multi-wave grids (2048+ blocks): 12 control steps enqueued back to back, with and without the launch attribute."""
+    a = _run(wl, n, 12, ADRP_PDL="1")
+    b = _run(wl, n, 12, ADRP_PDL="0")
+    assert a["finite"] and a["obs_sha"] == b["obs_sha"] and a["state_sha"] == b["state_sha"]
+
+
+@pytest.mark.parametrize("wl,n", [("c4", 4096), ("c2", 4096)])
+def test_specialised_step_instances_match_generic(wl, n):
+    a = _run(wl, n, 8)
+    b = _run(wl, n, 8, ADRP_STEP_GENERIC="1")
+    x, y = np.array(a["obs_sample"]), np.array(b["obs_sample"])
+    assert a["finite"] and np.max(np.abs(x - y) / np.maximum(np.abs(y), 1.0)) < 1e-5
