@@ -98,12 +98,6 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
     const long long od = valid ? env * P.M + i : 0;
 
     pdl_wait();                                               // (the track below is rewritten by the previous step's auto-resets)
-    // ---- stage the block's track instances (coalesced over envs) in shared memory
-    const long long env0 = (long long)P.env_begin + (long long)blockIdx.x * EPB;
-    for (int idx = threadIdx.x; idx < RP.TF * EPB; idx += kRaceBlock) {
-        const int f = idx / EPB, el = idx - f * EPB;
-        trk[idx] = env0 + el < P.N ? rb.track[(long long)f * P.N + env0 + el] : T(0);
-    }
 
     Drone<T> d;
     Mel<T> m;
@@ -120,6 +114,26 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
     } else {
         init_drone(P, 0, d);
         m = Mel<T>{};
+    }
+    // ---- stage the block's track instances (coalesced over envs) in shared memory: after the state loads have been issued
+    // (their latency covers this), six loads in flight per thread -- one element at a time the loop was 18 exposed L2 round
+    // trips per control step for level3's 36 fields (14 % of the stall samples of the C3 capture).  First read after the
+    // __syncthreads that follows the substep loop.
+    {
+        const long long env0 = (long long)P.env_begin + (long long)blockIdx.x * EPB;
+        const int total = RP.TF * EPB;
+        for (int base = threadIdx.x; base < total; base += 6 * kRaceBlock) {
+            T v[6];
+#pragma unroll
+            for (int u = 0; u < 6; ++u) {
+                const int idx = base + u * kRaceBlock;
+                const int f = idx / EPB, el = idx - f * EPB;
+                v[u] = (idx < total && env0 + el < P.N) ? rb.track[(long long)f * P.N + env0 + el] : T(0);
+            }
+#pragma unroll
+            for (int u = 0; u < 6; ++u)
+                if (base + u * kRaceBlock < total) trk[base + u * kRaceBlock] = v[u];
+        }
     }
     int current_gate = gl & 0xffff, latch = gl >> 16;
     const bool eliminated = (latch & ADRP_FLAG_ELIMINATED) != 0;
