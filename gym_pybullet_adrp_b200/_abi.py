@@ -11,19 +11,21 @@ import math
 from .assets import DroneParams, drone_params
 from .utils.enums import ActionType, DroneModel, Physics, RaceMode
 
-ABI_VERSION = 4
+ABI_VERSION = 5
 MAX_DRONES, MAX_GATES, MAX_OBSTACLES, STATE_DIM = 32, 8, 8, 20
 
 F32, F64 = 0, 1
 PHY_DYN, PHY_GND, PHY_DRAG, PHY_DW, PHY_GROUND = 1, 2, 4, 8, 16
-ACT_RPM_RAW, ACT_RPM, ACT_ONE_D_RPM, ACT_PID, ACT_ONE_D_PID, ACT_VEL, ACT_MEL, ACT_PID_FULL, ACT_MEL_FULL = range(9)
+ACT_RPM_RAW, ACT_RPM, ACT_ONE_D_RPM, ACT_PID, ACT_ONE_D_PID, ACT_VEL, ACT_MEL, ACT_PID_FULL, ACT_MEL_FULL, ACT_MEL_CMD = range(10)
+# enum adrp_command: Command (utils/enums.py:58-70) as the first float of an ACT_MEL_CMD row
+CMD_ID = {"non": 0, "fst": 1, "tko": 2, "toy": 3, "tov": 4, "lnd": 5, "ldy": 6, "ldv": 7, "stp": 8, "gto": 9, "ntf": 10}
 ENV_CTRL, ENV_HOVER, ENV_MULTIHOVER, ENV_RACE = range(4)
 FLAG_ELIMINATED, FLAG_FINISHED, FLAG_CRASHED, FLAG_OUT_OF_BOUNDS, FLAG_UNSTABLE, FLAG_TUMBLE_STOP = 1, 2, 4, 8, 16, 32
 WRAP_OBS, WRAP_REWARD = 1, 2                           # adrp_config.wrappers (gym_pybullet_adrp/utils/wrapper.py fused)
 
 MODEL_ID = {DroneModel.CF2X: 0, DroneModel.CF2P: 1, DroneModel.RACE: 2}
 ACTION_DIM = {ACT_RPM_RAW: 4, ACT_RPM: 4, ACT_ONE_D_RPM: 1, ACT_PID: 3, ACT_ONE_D_PID: 1, ACT_VEL: 4, ACT_MEL: 4,
-              ACT_PID_FULL: 12, ACT_MEL_FULL: 13}
+              ACT_PID_FULL: 12, ACT_MEL_FULL: 13, ACT_MEL_CMD: 16}
 ACTION_ID = {ActionType.RPM: ACT_RPM, ActionType.ONE_D_RPM: ACT_ONE_D_RPM, ActionType.PID: ACT_PID,
              ActionType.ONE_D_PID: ACT_ONE_D_PID, ActionType.VEL: ACT_VEL, ActionType.MEL: ACT_MEL}
 
@@ -147,7 +149,7 @@ def make_config(*, num_envs, num_drones=1, drone_model=DroneModel.CF2X, physics=
 def make_race_config(race_config, *, num_envs, num_drones=2, drone_model=DroneModel.CF2X, physics=Physics.PYB,
                      pyb_freq=500, ctrl_freq=25, racemode=RaceMode.COMPARE, precision=F32, device=0, seed=None,
                      env_offset=0, auto_reset=False, physics_mask=None, mel_mass=0.027, wrappers=0,
-                     full_state_actions=False) -> ConfigC:
+                     full_state_actions=False, command_actions=False) -> ConfigC:
     """adrp_config for MultiRaceAviary(race_config, ...) (envs/MultiRaceAviary.py:31-123)."""
     rc = race_config
     drones = list(rc["init_states"].keys())[:num_drones]
@@ -155,7 +157,7 @@ def make_race_config(race_config, *, num_envs, num_drones=2, drone_model=DroneMo
         raise ValueError("race_config.init_states has fewer entries than num_drones")
     st = [rc["init_states"][d] for d in drones]
     c = make_config(num_envs=num_envs, num_drones=num_drones, drone_model=drone_model, physics=physics,
-                    pyb_freq=pyb_freq, ctrl_freq=ctrl_freq, action_type=ACT_MEL_FULL if full_state_actions else ACT_MEL,
+                    pyb_freq=pyb_freq, ctrl_freq=ctrl_freq, action_type=ACT_MEL_CMD if command_actions else (ACT_MEL_FULL if full_state_actions else ACT_MEL),
                     env_kind=ENV_RACE, precision=precision,
                     device=device, initial_xyzs=[s["pos"] for s in st],
                     # _drone_init uses the config rpy WITHOUT deg->rad (MultiRaceAviary.py:459)

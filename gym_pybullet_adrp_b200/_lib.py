@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(PKG_DIR, "libadrp_b200.so")
 
 EXPORTS = ["adrp_create", "adrp_destroy", "adrp_obs_dim", "adrp_action_dim", "adrp_noise_dim",
            "adrp_reset_draws_dim", "adrp_substeps", "adrp_reset", "adrp_set_state", "adrp_get_state",
-           "adrp_step", "adrp_step_host", "adrp_dslpid_control", "adrp_launch_count", "adrp_set_profiling",
+           "adrp_step", "adrp_step_n", "adrp_step_host", "adrp_dslpid_control", "adrp_launch_count", "adrp_set_profiling",
            "adrp_step_kernel_ms", "adrp_fp32_peak_tflops", "adrp_last_error", "adrp_abi_version", "adrp_config_size"]
 
 _lib = None
@@ -44,6 +44,7 @@ def load():
     lib.adrp_set_state.argtypes = [vp, vp, vp]
     lib.adrp_get_state.argtypes = [vp, vp, vp]
     lib.adrp_step.argtypes = [vp, vp, vp, vp, vp, u8p, u8p, u8p, vp]
+    lib.adrp_step_n.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, u8p, u8p, u8p, vp]
     lib.adrp_step_host.argtypes = [vp, vp, vp, vp, u8p, u8p, u8p]
     lib.adrp_dslpid_control.argtypes = [C.c_int, C.c_int, C.POINTER(_abi.DroneParamsC), C.c_double, C.c_int,
                                         C.c_double] + [vp] * 12
@@ -149,6 +150,39 @@ class Handle:
                                        self.obs.data_ptr(), self.reward.data_ptr(), self.terminated.data_ptr(),
                                        self.truncated.data_ptr(), self.flags.data_ptr(), self._stream()), "adrp_step")
         return self.obs, self.reward, self.terminated, self.truncated, self.flags
+
+    def step_n(self, actions, n_steps=None, noise=None, keep_outputs=False):
+        """``n_steps`` control steps in ONE launch (adrp_step_n), bit-identical to that many ``step`` calls.
+
+        ``actions``: (K, N, M, A) -- one slice per step -- or (N, M, A), held for all ``n_steps`` (a fixed DSLPID target, a
+        hover setpoint).  ``keep_outputs``: return every step's outputs, shaped (K, N, M, O) / (K, N) / (K, N, M), in
+        fresh tensors; otherwise the handle's own tensors end up holding the last step's."""
+        torch = _torch()
+        a = torch.as_tensor(actions, dtype=self.dtype, device=self.device).contiguous()
+        per_step = a.dim() == 4
+        K = int(a.shape[0]) if per_step else int(n_steps)
+        if n_steps is not None and per_step and int(n_steps) != K:
+            raise ValueError("n_steps does not match the leading dimension of actions")
+        a = a.reshape((K, self.N, self.M, self.A) if per_step else (self.N, self.M, self.A))
+        nz = None
+        if noise is not None:
+            nz = torch.as_tensor(noise, dtype=self.dtype, device=self.device).contiguous()
+            nz = nz.reshape((K, self.N, self.M, self.S, 7) if per_step else (self.N, self.M, self.S, 7))
+        if keep_outputs:
+            out = (torch.empty((K, self.N, self.M, self.O), dtype=self.dtype, device=self.device),
+                   torch.empty((K, self.N), dtype=self.dtype, device=self.device),
+                   torch.empty((K, self.N), dtype=torch.uint8, device=self.device),
+                   torch.empty((K, self.N), dtype=torch.uint8, device=self.device),
+                   torch.empty((K, self.N, self.M), dtype=torch.uint8, device=self.device))
+        else:
+            out = (self.obs, self.reward, self.terminated, self.truncated, self.flags)
+        self._check(self.lib.adrp_step_n(self._h, K, int(per_step), int(keep_outputs), a.data_ptr(),
+                                         None if nz is None else nz.data_ptr(), *[t.data_ptr() for t in out],
+                                         self._stream()), "adrp_step_n")
+        if keep_outputs:                                   # the handle's tensors mirror the last step, as after step()
+            for dst, src in zip((self.obs, self.reward, self.terminated, self.truncated, self.flags), out):
+                dst.copy_(src[-1])
+        return out
 
     def step_host(self, action: np.ndarray):
         """Host path (NumPy in, NumPy out): H2D, launch, D2H inside the C call."""

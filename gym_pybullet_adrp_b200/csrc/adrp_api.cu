@@ -51,6 +51,11 @@ struct HandleBase {
     void *d_action = nullptr, *d_obs = nullptr, *d_reward = nullptr;
     uint8_t *d_term = nullptr, *d_trunc = nullptr, *d_flags = nullptr;
     cudaStream_t own_stream = nullptr, own_stream2 = nullptr;
+    // Recorded on the caller's stream at the end of every device-path entry point (reset, set_state, get_state, step,
+    // step_n); the host path's private streams wait on it before touching the handle's buffers, so that
+    // set_state() / reset() followed by step_host() is ordered without a device-wide synchronisation.
+    cudaEvent_t ev_order = nullptr;
+    bool order_pending = false;
     virtual ~HandleBase() {}
 };
 
@@ -73,6 +78,17 @@ struct DeviceGuard {
 };
 
 int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
+
+// see HandleBase::ev_order
+int mark_order(HandleBase* b, cudaStream_t s)
+{
+    if (!b->ev_order && cudaEventCreateWithFlags(&b->ev_order, cudaEventDisableTiming) != cudaSuccess) {
+        b->err = "cudaEventCreateWithFlags failed"; return ADRP_ECUDA;
+    }
+    if (cudaEventRecord(b->ev_order, s) != cudaSuccess) { b->err = "cudaEventRecord failed"; return ADRP_ECUDA; }
+    b->order_pending = true;
+    return ADRP_OK;
+}
 
 int action_dim(int act)
 {
@@ -114,6 +130,7 @@ void derive_params(const adrp_config& c, KParams<T>& P)
     P.race_mode = c.race_mode; P.auto_reset = c.auto_reset; P.pid_model = c.dslpid_model;
     P.Dpad = (long long)P.N * P.Mpad;
     P.env_begin = 0; P.env_end = P.N; P.obs_vec = 0; P.act_vec = 0;
+    P.K = 1; P.act_step = P.obs_step = P.env_step = P.drone_step = P.noise_step = 0;
     P.pyb_freq = c.pyb_freq;
     // step_counter / PYB_FREQ > EPISODE_LEN_SEC, evaluated like Python does (double division)
     int ts = 0;
@@ -236,6 +253,9 @@ int alloc_buffers(Handle<T>* h)
     CUDA_TRY(h, cudaMalloc(&h->B.step_counter, sizeof(int32_t) * P.N));
     CUDA_TRY(h, cudaMalloc(&h->B.ring_head, sizeof(int32_t) * P.N));
     CUDA_TRY(h, cudaMemset(h->B.state, 0, sizeof(T) * F_COUNT * D));
+    // BaseRLAviary.__init__ (:66-67) fills the action buffer with zeros ONCE; reset() keeps it
+    CUDA_TRY(h, cudaMemset(h->B.ring, 0, sizeof(T) * (size_t)(P.B * P.A > 0 ? P.B * P.A : 1) * D));
+    CUDA_TRY(h, cudaMemset(h->B.ring_head, 0, sizeof(int32_t) * P.N));
     if (h->race) {
         RaceBuffers<T>& rb = h->RB;
         const RaceParams<T>& R = h->RP;
@@ -291,12 +311,18 @@ int do_reset(Handle<T>* h, const uint8_t* mask, const T* draws, T* obs, cudaStre
     return ADRP_OK;
 }
 
+// K control steps in one launch (K = 1: adrp_step).  actions_per_step / outputs_per_step: the action (and noise) / output
+// buffers hold one slice per control step, or one slice that every step reads / overwrites.
 template <typename T>
 int do_step(Handle<T>* h, const T* action, const T* noise, T* obs, T* reward, uint8_t* te, uint8_t* tr, uint8_t* fl, cudaStream_t s,
-            int env_begin = 0, int env_end = -1)
+            int env_begin = 0, int env_end = -1, int K = 1, bool actions_per_step = false, bool outputs_per_step = false)
 {
     KParams<T> P = h->P;
     P.env_begin = env_begin; P.env_end = env_end < 0 ? P.N : env_end;
+    P.K = K;
+    const long long nd = (long long)P.N * P.M;
+    if (actions_per_step) { P.act_step = nd * P.A; P.noise_step = nd * P.S * 7; }
+    if (outputs_per_step) { P.obs_step = nd * P.O; P.env_step = P.N; P.drone_step = nd; }
     P.obs_vec = sizeof(T) == 4 && (P.O % 4) == 0 && (P.A == 4 || P.env_kind == ADRP_ENV_CTRL) && ((uintptr_t)obs & 15) == 0;
     P.act_vec = sizeof(T) == 4 && P.A == 4 && ((uintptr_t)action & 15) == 0;
     if (h->profiling) {
@@ -385,6 +411,7 @@ int adrp_destroy(adrp_handle* h)
     if (b->precision == ADRP_F64) free_buffers(typed<double>(h)); else free_buffers(typed<float>(h));
     if (b->ev0) cudaEventDestroy(b->ev0);
     if (b->ev1) cudaEventDestroy(b->ev1);
+    if (b->ev_order) cudaEventDestroy(b->ev_order);
     cudaFreeHost(b->h_action); cudaFreeHost(b->h_obs); cudaFreeHost(b->h_reward);
     cudaFreeHost(b->h_term); cudaFreeHost(b->h_trunc); cudaFreeHost(b->h_flags);
     cudaFree(b->d_action); cudaFree(b->d_obs); cudaFree(b->d_reward); cudaFree(b->d_term); cudaFree(b->d_trunc); cudaFree(b->d_flags);
@@ -413,8 +440,9 @@ int adrp_reset(adrp_handle* h, const uint8_t* env_mask, const void* draws, void*
     if (!h) return ADRP_EINVAL;
     DeviceGuard dg(base(h)->cfg.device);
     cudaStream_t s = (cudaStream_t)stream;
-    return BY_PRECISION(h, do_reset<double>(typed<double>(h), env_mask, (const double*)draws, (double*)obs, s),
-                        do_reset<float>(typed<float>(h), env_mask, (const float*)draws, (float*)obs, s));
+    const int rc = BY_PRECISION(h, do_reset<double>(typed<double>(h), env_mask, (const double*)draws, (double*)obs, s),
+                                do_reset<float>(typed<float>(h), env_mask, (const float*)draws, (float*)obs, s));
+    return rc != ADRP_OK ? rc : mark_order(base(h), s);
 }
 
 int adrp_set_state(adrp_handle* h, const void* state, void* stream)
@@ -430,7 +458,7 @@ int adrp_set_state(adrp_handle* h, const void* state, void* stream)
         auto* t = typed<float>(h);
         CUDA_TRY(t, Launch<float>::set_state(t->P, t->B, (const float*)state, s));
     }
-    return ADRP_OK;
+    return mark_order(base(h), s);
 }
 
 int adrp_get_state(adrp_handle* h, void* state, void* stream)
@@ -446,7 +474,7 @@ int adrp_get_state(adrp_handle* h, void* state, void* stream)
         auto* t = typed<float>(h);
         CUDA_TRY(t, Launch<float>::get_state(t->P, t->B, (float*)state, s));
     }
-    return ADRP_OK;
+    return mark_order(base(h), s);
 }
 
 int adrp_step(adrp_handle* h, const void* action, const void* noise, void* obs, void* reward,
@@ -458,8 +486,24 @@ int adrp_step(adrp_handle* h, const void* action, const void* noise, void* obs, 
     }
     DeviceGuard dg(base(h)->cfg.device);
     cudaStream_t s = (cudaStream_t)stream;
-    return BY_PRECISION(h, do_step<double>(typed<double>(h), (const double*)action, (const double*)noise, (double*)obs, (double*)reward, terminated, truncated, drone_flags, s),
-                        do_step<float>(typed<float>(h), (const float*)action, (const float*)noise, (float*)obs, (float*)reward, terminated, truncated, drone_flags, s));
+    const int rc = BY_PRECISION(h, do_step<double>(typed<double>(h), (const double*)action, (const double*)noise, (double*)obs, (double*)reward, terminated, truncated, drone_flags, s),
+                                do_step<float>(typed<float>(h), (const float*)action, (const float*)noise, (float*)obs, (float*)reward, terminated, truncated, drone_flags, s));
+    return rc != ADRP_OK ? rc : mark_order(base(h), s);
+}
+
+int adrp_step_n(adrp_handle* h, int n_steps, int actions_per_step, int outputs_per_step, const void* action, const void* noise,
+                void* obs, void* reward, uint8_t* terminated, uint8_t* truncated, uint8_t* drone_flags, void* stream)
+{
+    if (!h || !action || !obs || !reward || !terminated || !truncated || n_steps < 1) {
+        if (h) base(h)->err = "adrp_step_n: NULL buffer or n_steps < 1";
+        return ADRP_EINVAL;
+    }
+    DeviceGuard dg(base(h)->cfg.device);
+    cudaStream_t s = (cudaStream_t)stream;
+    const bool aps = actions_per_step != 0, ops = outputs_per_step != 0;
+    const int rc = BY_PRECISION(h, do_step<double>(typed<double>(h), (const double*)action, (const double*)noise, (double*)obs, (double*)reward, terminated, truncated, drone_flags, s, 0, -1, n_steps, aps, ops),
+                                do_step<float>(typed<float>(h), (const float*)action, (const float*)noise, (float*)obs, (float*)reward, terminated, truncated, drone_flags, s, 0, -1, n_steps, aps, ops));
+    return rc != ADRP_OK ? rc : mark_order(base(h), s);
 }
 
 }  // extern "C"
@@ -511,6 +555,11 @@ int do_step_host(Handle<T>* h, const void* action, void* obs, void* reward, uint
     const T* a_src = pin_a ? (const T*)action : (const T*)h->h_action;
     T* o_dst = pin_o ? (T*)obs : (T*)h->h_obs;
     if (!pin_a) memcpy(h->h_action, action, sizeof(T) * nd * P.A);
+    if (h->order_pending) {                                  // earlier device-path work on this handle (reset, set_state, step)
+        CUDA_TRY(h, cudaStreamWaitEvent(h->own_stream, h->ev_order, 0));
+        CUDA_TRY(h, cudaStreamWaitEvent(h->own_stream2, h->ev_order, 0));
+        h->order_pending = false;
+    }
     const int epb = kBlockHost / P.Mpad;                                   // envs per thread block
     int chunks = (int)(nd * P.O * sizeof(T) / (8u << 20));                  // ~8 MiB of observations per chunk
     chunks = chunks < 1 ? 1 : (chunks > 8 ? 8 : chunks);
@@ -562,6 +611,10 @@ int adrp_dslpid_control(int precision, int drone_model, const adrp_drone_params*
     if (!drone || n < 0 || !pos || !quat || !vel || !target_pos || !ctrl_state || !rpm) return ADRP_EINVAL;
     if (drone_model != ADRP_CF2X && drone_model != ADRP_CF2P) return ADRP_EUNSUPPORTED;   // DSLPIDControl.py:34-36
     if (n == 0) return ADRP_OK;
+    // run on the device that owns the buffers, whatever the caller's current device is
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, rpm) != cudaSuccess || at.type != cudaMemoryTypeDevice) { cudaGetLastError(); return ADRP_EINVAL; }
+    DeviceGuard dg(at.device);
     cudaStream_t s = (cudaStream_t)stream;
     cudaError_t e;
     if (precision == ADRP_F64)
@@ -581,6 +634,7 @@ int adrp_set_profiling(adrp_handle* h, int enabled)
 {
     if (!h) return ADRP_EINVAL;
     HandleBase* b = base(h);
+    DeviceGuard dg(b->cfg.device);
     if (enabled && !b->ev0) {
         CUDA_TRY(b, cudaEventCreate(&b->ev0));
         CUDA_TRY(b, cudaEventCreate(&b->ev1));
@@ -595,6 +649,7 @@ double adrp_step_kernel_ms(adrp_handle* h, int reset)
 {
     if (!h) return -1.0;
     HandleBase* b = base(h);
+    DeviceGuard dg(b->cfg.device);
     if (b->ev_pending) {
         float ms = 0;
         if (cudaEventSynchronize(b->ev1) == cudaSuccess && cudaEventElapsedTime(&ms, b->ev0, b->ev1) == cudaSuccess) {
@@ -609,14 +664,20 @@ double adrp_step_kernel_ms(adrp_handle* h, int reset)
 
 double adrp_fp32_peak_tflops(int device)
 {
-    if (cudaSetDevice(device) != cudaSuccess) return -1.0;
-    cudaDeviceProp prop;
-    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return -1.0;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return -1.0;
+    DeviceGuard dg(device);                               // (the caller's device is selected again on return)
+    int sms = 0;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) return -1.0;
     float* sink = nullptr;
     if (cudaMalloc(&sink, sizeof(float) * 1024) != cudaSuccess) return -1.0;
-    const int iters = 4096, blocks = prop.multiProcessorCount * 8, threads = 256;
-    cudaEvent_t e0, e1;
-    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    const int iters = 4096, blocks = sms * 8, threads = 256;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess) {
+        if (e0) cudaEventDestroy(e0);
+        cudaFree(sink);
+        return -1.0;
+    }
     double best = -1.0;
     for (int rep = 0; rep < 5; ++rep) {
         cudaEventRecord(e0);

@@ -12,41 +12,61 @@ namespace adrp {
 
 static_assert(kBlock == 128, "adrp_api.cu cuts host-path chunks in units of 128-thread blocks");
 
-// Launch with programmatic stream serialisation (see pdl_wait in adrp_step.cuh) when the grid is longer than one wave of
-// resident blocks: the next step's blocks then fill the slots the last wave frees (C4 +13 %, C5 +2 %).  A grid that fits
-// one wave launches plainly: its dependents would be placed into whatever slots the running grid leaves, unevenly over
-// the SMs (measured: C2 -17 %, C3 -13 %).  ADRP_PDL=0 in the environment switches it off altogether.
+// Launch `threads` threads of `kernel`.
+// Block size: grids longer than one wave of resident blocks use block_max.  A grid that fits one wave is cut into the
+// block size (block_max, block_max / 2, ... >= 32) that loads the busiest SM least: BASELINE's C2 is 65 536 threads = 512
+// blocks of 128 on 148 SMs -- 3.46 per SM, i.e. SMs with 4 blocks set the time (512 threads) -- but 1 024 blocks of 64 are
+// 7 per SM at most (448 threads); C3's 32 768 threads are 4 x 64 vs 7 x 32.  The kernels index with blockDim.x.
+// ADRP_BLOCK=<n> forces a size (diagnostic).
+// Programmatic stream serialisation (see pdl_wait in adrp_step.cuh) when the grid is longer than one wave: the next
+// step's blocks then fill the slots the last wave frees (C4 +13 %, C5 +2 %).  A grid that fits one wave launches plainly:
+// its dependents would be placed into whatever slots the running grid leaves, unevenly over the SMs (measured: C2 -17 %,
+// C3 -13 %).  ADRP_PDL=0 in the environment switches it off altogether.
 template <typename... KArgs, typename... Args>
-inline void launch_pdl(void (*kernel)(KArgs...), unsigned grid, unsigned block, size_t smem, cudaStream_t s, Args... args)
+inline void launch_pdl(void (*kernel)(KArgs...), long long threads, unsigned block_max, size_t smem_at_max, cudaStream_t s, Args... args)
 {
     static const bool enabled = [] { const char* e = getenv("ADRP_PDL"); return !e || e[0] != '0'; }();
+    static const int forced = [] { const char* e = getenv("ADRP_BLOCK"); return e ? atoi(e) : 0; }();
     static std::mutex mu;
-    static std::map<std::pair<const void*, int>, long long> wave;     // (kernel, device) -> resident blocks of the device
-    bool pdl = false;
-    if (enabled) {
+    struct Info { long long wave; int sms; };
+    static std::map<std::pair<const void*, int>, Info> cache;     // (kernel, device) -> resident blocks at block_max, SMs
+    Info info;
+    {
         int dev = 0;
         cudaGetDevice(&dev);
         std::lock_guard<std::mutex> lock(mu);
         auto key = std::make_pair((const void*)kernel, dev);
-        auto it = wave.find(key);
-        if (it == wave.end()) {
+        auto it = cache.find(key);
+        if (it == cache.end()) {
             int per_sm = 0, sms = 0;
-            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, (int)block, smem);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, (int)block_max, smem_at_max);
             cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-            it = wave.emplace(key, (long long)per_sm * sms).first;
+            it = cache.emplace(key, Info{(long long)per_sm * sms, sms}).first;
         }
-        pdl = it->second > 0 && (long long)grid > it->second;
+        info = it->second;
+    }
+    unsigned block = block_max;
+    const long long grid_max = (threads + block_max - 1) / block_max;
+    const bool one_wave = info.wave > 0 && grid_max <= info.wave;
+    if (forced >= 32 && forced <= (int)block_max && block_max % forced == 0) block = (unsigned)forced;
+    else if (one_wave && info.sms > 0) {
+        long long best = -1;
+        for (unsigned b = block_max; b >= 32; b >>= 1) {
+            const long long blocks = (threads + b - 1) / b;
+            const long long busiest = (blocks + info.sms - 1) / info.sms * b;      // threads on the fullest SM
+            if (best < 0 || busiest < best) { best = busiest; block = b; }
+        }
     }
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(grid, 1, 1);
+    cfg.gridDim = dim3((unsigned)((threads + block - 1) / block), 1, 1);
     cfg.blockDim = dim3(block, 1, 1);
-    cfg.dynamicSmemBytes = smem;
+    cfg.dynamicSmemBytes = smem_at_max * block / block_max;
     cfg.stream = s;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = pdl ? 1 : 0;
+    cfg.numAttrs = (enabled && !one_wave) ? 1 : 0;
     cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
 
@@ -92,8 +112,8 @@ cudaError_t Launch<T>::step(const KParams<T>& P, const KBuffers<T>& b, const T* 
 {
     const bool pid = P.action_type == ADRP_ACT_PID || P.action_type == ADRP_ACT_ONE_D_PID ||
                      P.action_type == ADRP_ACT_VEL || P.action_type == ADRP_ACT_PID_FULL;
-    const unsigned grid = (unsigned)(((long long)(P.env_end - P.env_begin) * P.Mpad + kStepBlock - 1) / kStepBlock);
-#define ADRP_LAUNCH_STEP(MP) launch_pdl(step_kernel<T, -1, 0, MP>, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl)
+    const bool multi = P.K > 1;                               // adrp_step_n: the instances with the control-step loop
+    const long long grid = (long long)(P.env_end - P.env_begin) * P.Mpad;      // threads of this launch
     // product build: the masks the configs use (Physics.DYN, Physics.PYB and the two all-forces masks) have instances with the
     // mask as a template argument (no per-substep mask tests, fewer registers: C5 +2 %, C2 +2 % at every batch size measured),
     // compiled in their own translation units (step_special)
@@ -101,19 +121,23 @@ cudaError_t Launch<T>::step(const KParams<T>& P, const KBuffers<T>& b, const T* 
         static const bool generic = [] { const char* e = getenv("ADRP_STEP_GENERIC"); return e && e[0] == '1'; }();   // diagnostic
         if (!pid && !generic) {
             StepFnF32 f = nullptr;
+            const bool ctrl = P.env_kind == ADRP_ENV_CTRL;
+            constexpr int ALL = ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW;
             switch (P.physics) {
-                case ADRP_PHY_DYN: f = step_special<ADRP_PHY_DYN>(P.Mpad, P.env_kind == ADRP_ENV_CTRL); break;
-                case ADRP_PHY_GROUND: f = step_special<ADRP_PHY_GROUND>(P.Mpad, P.env_kind == ADRP_ENV_CTRL); break;
-                case ADRP_PHY_DYN | ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW:
-                    f = step_special<ADRP_PHY_DYN | ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW>(P.Mpad, P.env_kind == ADRP_ENV_CTRL); break;
-                case ADRP_PHY_GROUND | ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW:
-                    f = step_special<ADRP_PHY_GROUND | ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW>(P.Mpad, P.env_kind == ADRP_ENV_CTRL); break;
+                case ADRP_PHY_DYN: f = multi ? step_special_multi<ADRP_PHY_DYN>(P.Mpad, ctrl) : step_special<ADRP_PHY_DYN>(P.Mpad, ctrl); break;
+                case ADRP_PHY_GROUND: f = multi ? step_special_multi<ADRP_PHY_GROUND>(P.Mpad, ctrl) : step_special<ADRP_PHY_GROUND>(P.Mpad, ctrl); break;
+                case ADRP_PHY_DYN | ALL: f = multi ? step_special_multi<ADRP_PHY_DYN | ALL>(P.Mpad, ctrl) : step_special<ADRP_PHY_DYN | ALL>(P.Mpad, ctrl); break;
+                case ADRP_PHY_GROUND | ALL: f = multi ? step_special_multi<ADRP_PHY_GROUND | ALL>(P.Mpad, ctrl) : step_special<ADRP_PHY_GROUND | ALL>(P.Mpad, ctrl); break;
                 default: break;
             }
             if (f) { launch_pdl(f, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl); return cudaGetLastError(); }
         }
     }
-    if (pid) launch_pdl(step_kernel<T, -1, 1, 0>, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl);
+#define ADRP_LAUNCH_STEP(MP) launch_pdl(step_kernel<T, -1, 0, MP>, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl)
+    if (multi) {                                              // generic instances with the control-step loop
+        if (pid) launch_pdl(step_kernel<T, -1, 1, 0, -1, true>, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl);
+        else launch_pdl(step_kernel<T, -1, 0, 0, -1, true>, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl);
+    } else if (pid) launch_pdl(step_kernel<T, -1, 1, 0>, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl);
     else switch (P.Mpad) {
         case 1: ADRP_LAUNCH_STEP(1); break;
         case 2: ADRP_LAUNCH_STEP(2); break;
@@ -149,15 +173,18 @@ using RaceStepFn = void (*)(KParams<T>, RaceParams<T>, KBuffers<T>, RaceBuffers<
 // then runs the instance without the wind / motor-noise terms; phy: the physics mask, for which the product build has
 // instances in their own translation units (race_step_special).
 template <typename T>
-inline RaceStepFn<T> race_step_fn(int mpad, bool full, bool quiet, int phy)
+inline RaceStepFn<T> race_step_fn(int mpad, bool full, bool quiet, int phy, bool multi = false)
 {
-    if (full) return race_step_kernel<T, 0, true, false, -1>;    // (Command.FULLSTATE, args) actions: scripted controllers
+    if (full) return multi ? race_step_kernel<T, 0, true, false, -1, true> : race_step_kernel<T, 0, true, false, -1>;    // (Command.FULLSTATE, args) actions: scripted controllers
     if constexpr (M<T>::fast) {
         RaceStepFn<T> f = nullptr;
-        if (phy == ADRP_PHY_GROUND) f = race_step_special<ADRP_PHY_GROUND>(mpad, quiet);
-        if (phy == (ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW | ADRP_PHY_GROUND))
-            f = race_step_special<ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW | ADRP_PHY_GROUND>(mpad, quiet);
+        constexpr int ALL = ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW | ADRP_PHY_GROUND;
+        if (phy == ADRP_PHY_GROUND) f = multi ? race_step_special_multi<ADRP_PHY_GROUND>(mpad, quiet) : race_step_special<ADRP_PHY_GROUND>(mpad, quiet);
+        if (phy == ALL) f = multi ? race_step_special_multi<ALL>(mpad, quiet) : race_step_special<ALL>(mpad, quiet);
         if (f) return f;
+    }
+    if (multi) return race_step_kernel<T, 0, false, false, -1, true>;
+    if constexpr (M<T>::fast) {
         switch (mpad) {
             case 1: return quiet ? race_step_kernel<T, 1, false, true, -1> : race_step_kernel<T, 1, false, false, -1>;
             case 2: return quiet ? race_step_kernel<T, 2, false, true, -1> : race_step_kernel<T, 2, false, false, -1>;
@@ -175,8 +202,8 @@ cudaError_t Launch<T>::race_prepare(const RaceParams<T>& RP, const KParams<T>& P
     const size_t bytes = race_smem_bytes(P, RP);
     if (bytes <= 48 * 1024) return cudaSuccess;
     cudaError_t e = cudaSuccess;
-    for (int quiet = 0; quiet < 2 && e == cudaSuccess; ++quiet)
-        e = cudaFuncSetAttribute(race_step_fn<T>(P.Mpad, P.action_type == ADRP_ACT_MEL_FULL, quiet != 0, P.physics), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)race_smem_bytes(P, RP, kRaceBlock));
+    for (int v = 0; v < 4 && e == cudaSuccess; ++v)
+        e = cudaFuncSetAttribute(race_step_fn<T>(P.Mpad, P.action_type == ADRP_ACT_MEL_FULL, (v & 1) != 0, P.physics, (v & 2) != 0), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)race_smem_bytes(P, RP, kRaceBlock));
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(race_reset_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
 }
@@ -194,8 +221,8 @@ cudaError_t Launch<T>::race_step(const KParams<T>& P, const RaceParams<T>& RP, c
                                  const T* action, const T* noise, T* obs, T* reward, uint8_t* te, uint8_t* tr,
                                  uint8_t* fl, cudaStream_t s)
 {
-    launch_pdl(race_step_fn<T>(P.Mpad, P.action_type == ADRP_ACT_MEL_FULL, !noise && !RP.disturbances, P.physics),
-               (unsigned)(((long long)(P.env_end - P.env_begin) * P.Mpad + kRaceBlock - 1) / kRaceBlock), kRaceBlock,
+    launch_pdl(race_step_fn<T>(P.Mpad, P.action_type == ADRP_ACT_MEL_FULL, !noise && !RP.disturbances, P.physics, P.K > 1),
+               (long long)(P.env_end - P.env_begin) * P.Mpad, kRaceBlock,
                race_smem_bytes(P, RP, kRaceBlock), s, P, RP, b, rb, action, noise, obs, reward, te, tr, fl);
     return cudaGetLastError();
 }

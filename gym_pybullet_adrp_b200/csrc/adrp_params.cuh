@@ -21,6 +21,11 @@ struct KParams {
     int env_begin, env_end;               // env range of THIS launch (chunked host path); the whole shard otherwise
     int obs_vec;                          // this launch may write observation rows with 16-byte stores (fp32, rows and base 16 B aligned)
     int act_vec;                          // ... and read 4-float action rows with one 16-byte load
+    // adrp_step_n: K control steps in this launch (state in registers across them); element strides from one step to the
+    // next of the action / observation / per-env (reward, terminated, truncated) / per-drone (flags) / noise buffers, 0 = the
+    // same buffer every step
+    int K;
+    long long act_step, obs_step, env_step, drone_step, noise_step;
     int pyb_freq;
     int trunc_steps;                      // smallest step_counter with step_counter/PYB_FREQ > EPISODE_LEN_SEC
     // BaseAviary constants (envs/BaseAviary.py:74-128)

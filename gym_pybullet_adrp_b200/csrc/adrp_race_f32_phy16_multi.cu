@@ -1,0 +1,4 @@
+// fp32 product build of the race step kernel for Physics.PYB, adrp_step_n instances (K control steps per launch).
+#define ADRP_MULTI_TU
+#include "adrp_race_special.cuh"
+template adrp::RaceStepFnF32 adrp::race_step_special_multi<16>(int, bool);

@@ -6,16 +6,21 @@
 
 namespace adrp {
 
-template <int PHY>
-RaceStepFnF32 race_step_special(int mpad, bool quiet)
+template <int PHY, bool MULTI>
+RaceStepFnF32 race_step_special_impl(int mpad, bool quiet)
 {
     switch (mpad) {
-        case 1: return quiet ? race_step_kernel<float, 1, false, true, PHY> : race_step_kernel<float, 1, false, false, PHY>;
-        case 2: return quiet ? race_step_kernel<float, 2, false, true, PHY> : race_step_kernel<float, 2, false, false, PHY>;
-        case 4: return quiet ? race_step_kernel<float, 4, false, true, PHY> : race_step_kernel<float, 4, false, false, PHY>;
-        case 8: return quiet ? race_step_kernel<float, 8, false, true, PHY> : race_step_kernel<float, 8, false, false, PHY>;
+        case 1: return quiet ? race_step_kernel<float, 1, false, true, PHY, MULTI> : race_step_kernel<float, 1, false, false, PHY, MULTI>;
+        case 2: return quiet ? race_step_kernel<float, 2, false, true, PHY, MULTI> : race_step_kernel<float, 2, false, false, PHY, MULTI>;
+        case 4: return quiet ? race_step_kernel<float, 4, false, true, PHY, MULTI> : race_step_kernel<float, 4, false, false, PHY, MULTI>;
+        case 8: return quiet ? race_step_kernel<float, 8, false, true, PHY, MULTI> : race_step_kernel<float, 8, false, false, PHY, MULTI>;
         default: return nullptr;
     }
 }
+#ifdef ADRP_MULTI_TU
+template <int PHY> RaceStepFnF32 race_step_special_multi(int mpad, bool quiet) { return race_step_special_impl<PHY, true>(mpad, quiet); }
+#else
+template <int PHY> RaceStepFnF32 race_step_special(int mpad, bool quiet) { return race_step_special_impl<PHY, false>(mpad, quiet); }
+#endif
 
 }  // namespace adrp

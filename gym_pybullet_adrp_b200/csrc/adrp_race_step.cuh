@@ -76,7 +76,8 @@ race_reset_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ 
 // FULL: 13-float (Command.FULLSTATE, args) actions (ADRP_ACT_MEL_FULL) instead of [x, y, z, yaw].
 // QUIET: the launch has no disturbance draws (noise == NULL and RaceParams::disturbances == 0).
 // PHY_CT >= 0: physics mask known at compile time (no per-substep mask tests: +6 % on C5M); -1: read from the params.
-template <typename T, int MP, bool FULL, bool QUIET, int PHY_CT>
+// MULTI: adrp_step_n instances -- P.K control steps per launch (the single-step instances compile the loop away).
+template <typename T, int MP, bool FULL, bool QUIET, int PHY_CT, bool MULTI = false>
 __global__ void ADRP_RACE_BOUNDS
 race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ RaceParams<T> RP, const KBuffers<T> b,
                  const RaceBuffers<T> rb, const T* __restrict__ action, const T* __restrict__ noise, T* __restrict__ obs,
@@ -86,12 +87,13 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T* trk = reinterpret_cast<T*>(smem_raw);
     const int mpad = MP > 0 ? MP : P.Mpad;
-    const long long t = (long long)P.env_begin * mpad + (long long)blockIdx.x * kRaceBlock + threadIdx.x;
+    const long long t = (long long)P.env_begin * mpad + (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
     const int i = (int)(t & (mpad - 1));
     const long long env = t / mpad;
     const int lane_base = lane - i;
-    const int EPB = kRaceBlock / mpad, e = threadIdx.x / mpad;
+    const int nthr = (int)blockDim.x;                         // 32 or 64: launch_pdl picks the size that balances the SMs
+    const int EPB = nthr / mpad, e = threadIdx.x / mpad;
     const bool valid = env < P.env_end && i < P.M;
     const long long D = P.Dpad;
     const int phy = PHY_CT >= 0 ? PHY_CT : P.physics;
@@ -115,33 +117,54 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
         init_drone(P, 0, d);
         m = Mel<T>{};
     }
+    int current_gate = gl & 0xffff, latch = gl >> 16;
+    // RewardWrapper state (wrapper.py:78-80) of this env, held by drone 0's thread
+    int sh_gate = 0;
+    T sh[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+    const bool shaper = (RP.wrappers & ADRP_WRAP_REWARD) && valid && i == 0;
+    if (shaper) {
+        sh_gate = rb.shape_gate[env];
+        if (sh_gate >= 0) {
+#pragma unroll
+            for (int k = 0; k < 6; ++k) sh[k] = rb.shape_vec[(long long)k * P.N + env];
+        }
+    }
+
+    // ---- K control steps per launch (adrp_step_n; K = 1 for adrp_step): rigid-body, controller and latch state stay in
+    // registers from one control step to the next
+    int restage = 1;
+    const int K = MULTI ? P.K : 1;
+    for (int ks = 0; ks < K; ++ks) {
     // ---- stage the block's track instances (coalesced over envs) in shared memory: after the state loads have been issued
     // (their latency covers this), six loads in flight per thread -- one element at a time the loop was 18 exposed L2 round
     // trips per control step for level3's 36 fields (14 % of the stall samples of the C3 capture).  First read after the
-    // __syncthreads that follows the substep loop.
-    {
+    // __syncthreads that follows the substep loop.  Later control steps of the same launch re-stage only after an in-kernel
+    // reset re-randomised a track of this block (the barrier also orders the previous step's reads of the old copy).
+    const int kv = ks;
+    if (ks > 0) restage = __syncthreads_or(restage);
+    if (restage) {
         const long long env0 = (long long)P.env_begin + (long long)blockIdx.x * EPB;
         const int total = RP.TF * EPB;
-        for (int base = threadIdx.x; base < total; base += 6 * kRaceBlock) {
+        for (int base = threadIdx.x; base < total; base += 6 * nthr) {
             T v[6];
 #pragma unroll
             for (int u = 0; u < 6; ++u) {
-                const int idx = base + u * kRaceBlock;
+                const int idx = base + u * nthr;
                 const int f = idx / EPB, el = idx - f * EPB;
                 v[u] = (idx < total && env0 + el < P.N) ? rb.track[(long long)f * P.N + env0 + el] : T(0);
             }
 #pragma unroll
             for (int u = 0; u < 6; ++u)
-                if (base + u * kRaceBlock < total) trk[base + u * kRaceBlock] = v[u];
+                if (base + u * nthr < total) trk[base + u * nthr] = v[u];
         }
     }
-    int current_gate = gl & 0xffff, latch = gl >> 16;
+    restage = 0;
     const bool eliminated = (latch & ADRP_FLAG_ELIMINATED) != 0;
 
     // ---- ndarray action -> FULLSTATE(pos, 0, 0, yaw, 0, step_counter) (:190-202)
     MelSetpoint sp = {{0.0f, 0.0f, 0.0f}, 0.0f, 1.0f, {0.0f, 0.0f, 0.0f}, {0.0f, 0.0f, 0.0f}, {0.0f, 0.0f, 0.0f}, 1.0f, 0.0f};
     if (valid && !eliminated) {
-        const T* a = action + od * (FULL ? 13 : 4);
+        const T* a = action + (long long)kv * P.act_step + od * (FULL ? 13 : 4);
         T a_yaw;
         if (M<T>::fast && !FULL && P.act_vec) {               // one 16-byte load per drone instead of four strided ones
             const float4 a4 = *reinterpret_cast<const float4*>(a);
@@ -165,11 +188,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
 
     // ---- RewardWrapper.reset (wrapper.py:96-101) reads drone 0's row of the reset observation: current gate id,
     // observed pose of gate 0, position.  Evaluated on the state the episode starts from, by drone 0's thread.
-    int sh_gate = 0;
-    T sh[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
-    const bool shaper = (RP.wrappers & ADRP_WRAP_REWARD) && valid && i == 0;
     if (shaper) {
-        sh_gate = rb.shape_gate[env];
         if (sh_gate < 0) {
             sh_gate = current_gate;
             if (RP.G > 0) {
@@ -182,9 +201,6 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
                 sh[2] = in_range ? tg[2 * N] : RP.gate_nom[0][2];
             }
             sh[3] = d.p.x; sh[4] = d.p.y; sh[5] = d.p.z;
-        } else {
-#pragma unroll
-            for (int k = 0; k < 6; ++k) sh[k] = rb.shape_vec[(long long)k * P.N + env];
         }
     }
     // ---- S fused substeps (:210-254)
@@ -203,7 +219,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
         if (QUIET) {
         } else if (noise) {
             if (valid) {
-                const T* np_ = noise + ((od * P.S) + s) * 7;
+                const T* np_ = noise + (long long)kv * P.noise_step + ((od * P.S) + s) * 7;
 #pragma unroll
                 for (int k = 0; k < 7; ++k) nz[k] = np_[k];
             }
@@ -270,7 +286,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
             mellinger_tick(RP, rb.lut, m, sp, d.p, d.q, d.v, QUIET ? (const T*)nullptr : nz + 3, R, win, s);                   // rpms[i] = recv() (:254)
         }
     }
-    pdl_launch_dependents();                                // the next step's blocks may be scheduled during the epilogue
+    if (ks == K - 1) pdl_launch_dependents();             // the next launch's blocks may be scheduled during the epilogue
     if (body_rates) d.w = pyb_world_rates(R, wl);           // R: the pose after the last substep
     if (M<T>::fast) d.q = canon_quat_loop(d.q);             // once per control step in the product build (adrp_physics.cuh)
     __syncthreads();                                                                     // shared track is complete
@@ -324,7 +340,8 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
     const V3<T> rpy = euler_rpy(d.q);
     const T hz = drone_half_height(P.coll_r, P.coll_h, Rn.m22);
     T track_gap;                                             // closest gate / obstacle, from the observation's visibility tests
-    race_write_obs(P, RP, trk, EPB, e, d, rpy, hz, current_gate, i, lane_base, valid, obs + od * P.O, &track_gap);
+    T* const obs_row = obs + (long long)kv * P.obs_step + od * P.O;
+    race_write_obs(P, RP, trk, EPB, e, d, rpy, hz, current_gate, i, lane_base, valid, obs_row, &track_gap);
 
     // ---- _computeTerminated (:674-698) with _collision (:552-562)
     int fl = 0;
@@ -356,7 +373,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
         // RewardWrapper._compute_reward (wrapper.py:121-186) on this step's observation row of drone 0.  Declared
         // where the reference raises: info has no "task_completed" key in this fork -> drone 0's FINISHED latch;
         // gate id == number of gates has no entry in its pose table -> the target is kept.
-        const T* o = obs + od * P.O;
+        const T* o = obs_row;
         T r_passed = T(0), r_end = T(0);
         if (current_gate > sh_gate % 4) {
             sh_gate = current_gate;
@@ -374,28 +391,36 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
         term |= __shfl_sync(0xffffffffu, current_gate, lane_base) >= 2;
     const int trunc = counter >= P.trunc_steps;                                          // step_counter / PYB_FREQ > episode_len_sec (:709)
     const bool done = P.auto_reset && (term || trunc);
-    if (valid && drone_flags) drone_flags[od] = (uint8_t)(fl | latch);
+    if (valid && drone_flags) drone_flags[(long long)kv * P.drone_step + od] = (uint8_t)(fl | latch);
     if (valid && i == 0) {
-        reward[env] = rew;
-        terminated[env] = (uint8_t)term;
-        truncated[env] = (uint8_t)trunc;
+        const long long eo = (long long)kv * P.env_step + env;
+        reward[eo] = rew;
+        terminated[eo] = (uint8_t)term;
+        truncated[eo] = (uint8_t)trunc;
     }
     __syncwarp();
+    if (valid && done) {
+        // reset into copies: the out-of-line call takes addresses, and the live state must stay in registers
+        Drone<T> d2;
+        Mel<T> m2;
+        T body2[4];
+        race_reset_drone(P, RP, rb, env, i, episode, (const T*)nullptr, d2, m2, body2);
+        d = d2; m = m2;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) body[k] = body2[k];
+        store_body(rb, D, t, body2);
+        current_gate = 0; latch = 0;
+        episode += 1;
+        sh_gate = -1;
+        restage = 1;                                          // this env's track was re-randomised in HBM
+    }
+    counter = done ? 0 : counter + P.S;                                                  // BaseAviary.py:386
+    }   // control steps of this launch
+
     if (valid) {
-        if (done) {
-            // reset into copies: the out-of-line call takes addresses, and the live state must stay in registers
-            Drone<T> d2;
-            Mel<T> m2;
-            T body2[4];
-            race_reset_drone(P, RP, rb, env, i, episode, (const T*)nullptr, d2, m2, body2);
-            d = d2; m = m2;
-            store_body(rb, D, t, body2);
-            current_gate = 0; latch = 0;
-            if (i == 0) rb.episode[env] = episode + 1;
-        }
-        if (i == 0) b.step_counter[env] = done ? 0 : counter + P.S;                      // BaseAviary.py:386
+        if (i == 0) { b.step_counter[env] = counter; rb.episode[env] = episode; }
         if (shaper) {
-            rb.shape_gate[env] = done ? -1 : sh_gate;
+            rb.shape_gate[env] = sh_gate;
 #pragma unroll
             for (int k = 0; k < 6; ++k) rb.shape_vec[(long long)k * P.N + env] = sh[k];
         }

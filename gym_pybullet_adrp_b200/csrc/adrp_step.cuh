@@ -99,14 +99,16 @@ __device__ __forceinline__ int group_or(int v, int Mpad)
 // ENVK: -1 = env kind read from the params; 0 = CtrlAviary-kind (20-float rows, no reward / action buffer) compiled in;
 // 1 = an RL aviary (Hover / MultiHover, told apart at run time) compiled in.  The epilogues of the two families differ
 // a lot (5 stores vs. the action-buffer copy), and the registers of the larger one count for the whole kernel.
-template <typename T, int PHY_CT, int ACTC, int MP, int ENVK = -1>
+// MULTI: adrp_step_n instances -- P.K control steps per launch (the single-step instances compile the loop away and are
+// the code they were before it existed: the loop costs the all-forces instances 12 registers, i.e. one resident block).
+template <typename T, int PHY_CT, int ACTC, int MP, int ENVK = -1, bool MULTI = false>
 __global__ void __launch_bounds__(kStepBlock, ADRP_STEP_MINB)
 step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* __restrict__ action,
             T* __restrict__ obs, T* __restrict__ reward, uint8_t* __restrict__ terminated,
             uint8_t* __restrict__ truncated, uint8_t* __restrict__ drone_flags)
 {
     const int mpad = MP > 0 ? MP : P.Mpad;
-    const long long t = (long long)P.env_begin * mpad + (long long)blockIdx.x * kStepBlock + threadIdx.x;
+    const long long t = (long long)P.env_begin * mpad + (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
     const int i = (int)(t & (mpad - 1));
     const long long env = t / mpad;
@@ -121,10 +123,28 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
 
     Drone<T> d;
     if (valid) load_drone(b, D, t, d); else init_drone(P, 0, d);
+    PidState<T> pc;
+    if (ACTC == 1) {
+        const T* pb = b.pid;
+        pc.ipos = {ld(pb, D, 0, t), ld(pb, D, 1, t), ld(pb, D, 2, t)};
+        pc.irpy = {ld(pb, D, 3, t), ld(pb, D, 4, t), ld(pb, D, 5, t)};
+        pc.last_rpy = {ld(pb, D, 6, t), ld(pb, D, 7, t), ld(pb, D, 8, t)};
+    }
+    // (single-step instances fetch these two where they are first used, after the substep loop: two registers less in it)
+    int counter = 0, head = 0;
+    if (MULTI) {
+        counter = env < P.env_end ? b.step_counter[env] : 0;
+        head = (!is_ctrl && valid) ? b.ring_head[env] : 0;
+    }
 
+    // ---- K control steps per launch (adrp_step_n; K = 1 for adrp_step): the rigid-body / controller state, the step counter
+    // and the ring head stay in registers from one control step to the next
+    const int K = MULTI ? P.K : 1;
+    for (int ks = 0; ks < K; ++ks) {
+    const int kv = ks;
     // ---- action -> RPM (CtrlAviary.py:140; BaseRLAviary.py:160-239)
     T rpm[4];
-    const T* a = action + od * P.A;
+    const T* a = action + (long long)kv * P.act_step + od * P.A;
     constexpr int AMAX = ACTC == 0 ? 4 : 12;             // RPM-type actions have at most 4 components
     T act_in[AMAX];
     if (M<T>::fast && P.act_vec && AMAX == 4) {               // one 16-byte load per drone instead of four strided ones
@@ -134,7 +154,6 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
 #pragma unroll
         for (int k = 0; k < AMAX; ++k) act_in[k] = (valid && k < P.A) ? a[k] : T(0);
     }
-    PidState<T> pc;
     if (ACTC == 0) {
         if (P.action_type == ADRP_ACT_RPM_RAW) {
 #pragma unroll
@@ -148,10 +167,6 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
             }
         }
     } else {
-        const T* pb = b.pid;
-        pc.ipos = {ld(pb, D, 0, t), ld(pb, D, 1, t), ld(pb, D, 2, t)};
-        pc.irpy = {ld(pb, D, 3, t), ld(pb, D, 4, t), ld(pb, D, 5, t)};
-        pc.last_rpy = {ld(pb, D, 6, t), ld(pb, D, 7, t), ld(pb, D, 8, t)};
         V3<T> tpos, trpy = {T(0), T(0), T(0)}, tvel = {T(0), T(0), T(0)}, trates = {T(0), T(0), T(0)};
         if (P.action_type == ADRP_ACT_PID) {
             // BaseAviary._calculateNextStep (:1112-1154), step_size = 1
@@ -224,7 +239,7 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
 #pragma unroll
         for (int k = 0; k < 4; ++k) d.last_rpm[k] = rpm[k];                      // :376 (S >= 1)
     }
-    pdl_launch_dependents();                             // the next step's blocks may be scheduled while this one writes out
+    if (ks == K - 1) pdl_launch_dependents();          // the next launch's blocks may be scheduled while this one writes out
     if (M<T>::fast) d.q = canon_quat_loop(d.q);          // once per control step in the product build (adrp_physics.cuh)
     if (body_rates) d.w = pyb_world_rates(rotmat_loop(d.q), wl);
 
@@ -232,8 +247,7 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
     // Euler angles, so the product build may use the loop's polynomial atan2 there (1 ulp); the RL aviaries threshold
     // |roll|, |pitch| and keep libm, so that their flags stay a bit-exact function of the stored state
     const V3<T> rpy = is_ctrl ? euler_rpy_loop(d.q) : euler_rpy(d.q);
-    T* o = obs + od * P.O;
-    int head = 0;
+    T* o = obs + (long long)kv * P.obs_step + od * P.O;
     // fp32 build: rows whose length is a multiple of 4 floats go out as 16-byte stores (a warp's scalar store of one
     // column touches 32 sectors for 128 useful bytes; the float4 form moves 4x the payload per sector access)
     const bool vec = M<T>::fast && P.obs_vec;
@@ -264,7 +278,7 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
         }
         // action buffer (deque(maxlen=ctrl_freq//2), BaseRLAviary.py:66-67,187): the newest action
         // overwrites the oldest ring slot; the observation lists the slots oldest -> newest
-        head = b.ring_head[env];
+        if (!MULTI) head = b.ring_head[env];
         const int nh = head + 1 == P.B ? 0 : head + 1;
         if (vec) {                                             // P.A == 4: one 16-byte access per ring slot
             float4* r4 = reinterpret_cast<float4*>(b.ring);
@@ -303,7 +317,7 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
     // ---- reward and flags (HoverAviary.py:68-117; MultiHoverAviary.py:75-130; CtrlAviary.py:144-200)
     T rew = T(-1);
     int term = 0, trunc = 0;
-    const int counter = env < P.env_end ? b.step_counter[env] : 0;
+    if (!MULTI) counter = env < P.env_end ? b.step_counter[env] : 0;
     if (!is_ctrl) {
         T r = T(0), dist = T(0);
         int tr = 0;
@@ -321,22 +335,24 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
     }
     const bool done = P.auto_reset && (term || trunc);
     if (valid && i == 0) {
-        reward[env] = rew;
-        terminated[env] = (uint8_t)term;
-        truncated[env] = (uint8_t)trunc;
-        b.step_counter[env] = done ? 0 : counter + P.S;                          // BaseAviary.py:386
-        if (!is_ctrl) b.ring_head[env] = done ? 0 : head;
+        const long long eo = (long long)kv * P.env_step + env;
+        reward[eo] = rew;
+        terminated[eo] = (uint8_t)term;
+        truncated[eo] = (uint8_t)trunc;
     }
-    if (valid && drone_flags) drone_flags[od] = 0;
+    counter = done ? 0 : counter + P.S;                                          // BaseAviary.py:386
+    if (valid && drone_flags) drone_flags[(long long)kv * P.drone_step + od] = 0;
+    if (done) {                                          // the next episode starts from the initial pose (auto_reset)
+        init_drone(P, valid ? i : 0, d);
+        pc.ipos = pc.irpy = pc.last_rpy = {T(0), T(0), T(0)};
+    }
+    }   // control steps of this launch
 
-    // ---- write the state back (re-initialised when the episode ended and auto_reset is on)
+    // ---- write the state back
     if (valid) {
-        if (done) {
-            init_drone(P, i, d);
-            pc.ipos = pc.irpy = pc.last_rpy = {T(0), T(0), T(0)};
-            if (!is_ctrl)
-                for (int sl = 0; sl < P.B; ++sl)
-                    for (int k = 0; k < P.A; ++k) b.ring[ring_idx(D, P.A, sl, k, t)] = T(0);
+        if (i == 0) {
+            b.step_counter[env] = counter;
+            if (!is_ctrl) b.ring_head[env] = head;         // the action buffer survives a reset (BaseRLAviary.py:66-67)
         }
         store_drone(b, D, t, d);
         if (ACTC == 1) {
@@ -384,9 +400,10 @@ __global__ void reset_kernel(const KParams<T> P, KBuffers<T> b, const uint8_t* _
     init_drone(P, i, d);
     store_drone(b, P.Dpad, t, d);
     for (int k = 0; k < 9; ++k) b.pid[(long long)k * P.Dpad + t] = T(0);
-    for (int sl = 0; sl < P.B; ++sl)
-        for (int k = 0; k < P.A; ++k) b.ring[ring_idx(P.Dpad, P.A, sl, k, t)] = T(0);
-    if (i == 0) { b.step_counter[env] = 0; b.ring_head[env] = 0; }
+    // the action buffer is filled once in BaseRLAviary.__init__ (:66-67) and reset() never touches it: the ring (zeroed
+    // by adrp_create) and its head survive, so the observation below and the next B - 1 steps still list the previous
+    // episode's actions (golden hover_pyb_rpm_reset)
+    if (i == 0) b.step_counter[env] = 0;
     if (obs) {
         T* o = obs + (env * P.M + i) * P.O;
         const V3<T> rpy = euler_rpy(d.q);
@@ -397,7 +414,11 @@ __global__ void reset_kernel(const KParams<T> P, KBuffers<T> b, const uint8_t* _
         } else {
             o[0] = d.p.x; o[1] = d.p.y; o[2] = d.p.z; o[3] = rpy.x; o[4] = rpy.y; o[5] = rpy.z;
             o[6] = d.v.x; o[7] = d.v.y; o[8] = d.v.z; o[9] = d.w.x; o[10] = d.w.y; o[11] = d.w.z;
-            for (int k = 12; k < P.O; ++k) o[k] = T(0);
+            const int head = b.ring_head[env];                 // oldest slot first (BaseRLAviary.py:315-322)
+            for (int j = 0; j < P.B; ++j) {
+                const int slot = head + j >= P.B ? head + j - P.B : head + j;
+                for (int k = 0; k < P.A; ++k) o[12 + j * P.A + k] = b.ring[ring_idx(P.Dpad, P.A, slot, k, t)];
+            }
         }
     }
 }

@@ -7,26 +7,31 @@
 
 namespace adrp {
 
-template <int PHY, int ENVK>
+template <int PHY, int ENVK, bool MULTI>
 StepFnF32 step_special_mp(int mpad)
 {
     switch (mpad) {
-        case 1: return step_kernel<float, PHY, 0, 1, ENVK>;
-        case 2: return step_kernel<float, PHY, 0, 2, ENVK>;
-        case 4: return step_kernel<float, PHY, 0, 4, ENVK>;
-        case 8: return step_kernel<float, PHY, 0, 8, ENVK>;
+        case 1: return step_kernel<float, PHY, 0, 1, ENVK, MULTI>;
+        case 2: return step_kernel<float, PHY, 0, 2, ENVK, MULTI>;
+        case 4: return step_kernel<float, PHY, 0, 4, ENVK, MULTI>;
+        case 8: return step_kernel<float, PHY, 0, 8, ENVK, MULTI>;
         default: return nullptr;
     }
 }
 
 // ctrl: CtrlAviary-kind env; rl_too: this mask also has RL-aviary instances (the plain masks: learn.py / HoverAviary shapes)
-template <int PHY>
-StepFnF32 step_special(int mpad, bool ctrl)
+template <int PHY, bool MULTI>
+StepFnF32 step_special_impl(int mpad, bool ctrl)
 {
     constexpr bool rl_too = PHY == ADRP_PHY_DYN || PHY == ADRP_PHY_GROUND;
-    if (ctrl) return step_special_mp<PHY, 0>(mpad);
-    if constexpr (rl_too) return step_special_mp<PHY, 1>(mpad);
+    if (ctrl) return step_special_mp<PHY, 0, MULTI>(mpad);
+    if constexpr (rl_too) return step_special_mp<PHY, 1, MULTI>(mpad);
     return nullptr;
 }
+#ifdef ADRP_MULTI_TU
+template <int PHY> StepFnF32 step_special_multi(int mpad, bool ctrl) { return step_special_impl<PHY, true>(mpad, ctrl); }
+#else
+template <int PHY> StepFnF32 step_special(int mpad, bool ctrl) { return step_special_impl<PHY, false>(mpad, ctrl); }
+#endif
 
 }  // namespace adrp

@@ -18,7 +18,7 @@
 extern "C" {
 #endif
 
-#define ADRP_ABI_VERSION 4
+#define ADRP_ABI_VERSION 5
 #define ADRP_MAX_DRONES 32      /* drones per env: one env lives inside one warp */
 #define ADRP_MAX_GATES 8
 #define ADRP_MAX_OBSTACLES 8
@@ -49,8 +49,20 @@ enum adrp_action_type {          /* utils/enums.py:40-47 + CtrlAviary */
     ADRP_ACT_MEL = 6,            /* [x,y,z,yaw] full-state setpoint -> Mellinger per substep (MultiRaceAviary.py:190-254) */
     ADRP_ACT_PID_FULL = 7,       /* [target_pos3, target_rpy3, target_vel3, target_rates3] -> DSLPIDControl.computeControl
                                     (control/DSLPIDControl.py:82-145), the examples/pid.py:138-147 driver loop fused */
-    ADRP_ACT_MEL_FULL = 8        /* (Command.FULLSTATE, args) tuples (MultiRaceAviary.py:198-205; MellingerControl.sendFullStateCmd,
+    ADRP_ACT_MEL_FULL = 8,       /* (Command.FULLSTATE, args) tuples (MultiRaceAviary.py:198-205; MellingerControl.sendFullStateCmd,
                                     :510-543): [pos3, vel3, acc3, yaw, rpy_rates3 (rad/s)] -> Mellinger per substep */
+    ADRP_ACT_MEL_CMD = 9         /* any (Command, args) tuple (utils/enums.py:58-70; low_level_control,
+                                    MellingerControl.py:32-57): 16-float rows [adrp_command, args..., 0 padding] -- the
+                                    high-level commander (take-off / land / go-to planner, :547-699) runs on the device */
+};
+
+/* Command (utils/enums.py:58-70) as the first float of an ADRP_ACT_MEL_CMD row, followed by the reference's args:
+ *   FULLSTATE  pos3, vel3, acc3, yaw, rpy_rates3, t        TAKEOFF / LAND        height, duration
+ *   TAKEOFFYAW / LANDYAW  height, duration, yaw            TAKEOFFVEL / LANDVEL  height, velocity, relative
+ *   GOTO       pos3, yaw, duration, relative               STOP / NOTIFY         t          NONE  -            */
+enum adrp_command {
+    ADRP_CMD_NONE = 0, ADRP_CMD_FULLSTATE = 1, ADRP_CMD_TAKEOFF = 2, ADRP_CMD_TAKEOFFYAW = 3, ADRP_CMD_TAKEOFFVEL = 4,
+    ADRP_CMD_LAND = 5, ADRP_CMD_LANDYAW = 6, ADRP_CMD_LANDVEL = 7, ADRP_CMD_STOP = 8, ADRP_CMD_GOTO = 9, ADRP_CMD_NOTIFY = 10
 };
 
 enum adrp_env_kind {
@@ -180,6 +192,22 @@ int adrp_get_state(adrp_handle* h, void* state, void* stream);
  *   terminated, truncated (N) bytes; drone_flags (N, M) bytes (may be NULL) */
 int adrp_step(adrp_handle* h, const void* action, const void* noise, void* obs, void* reward,
               uint8_t* terminated, uint8_t* truncated, uint8_t* drone_flags, void* stream);
+
+/* n_steps consecutive Env.step calls in ONE launch: the rigid-body and controller state of every drone stays in
+ * registers from one control step to the next, and per-launch costs (launch latency, state load / store, block
+ * scheduling) are paid once per n_steps -- what a scripted rollout (examples/pid.py:138-147: a fixed DSLPID target;
+ * user_controller/HardCodedController.py:166-176: a precomputed setpoint sequence) or a random-action rollout
+ * (examples/learn.py's shape) needs.  Results equal those of n_steps adrp_step calls: bit for bit in the fp64 build, to
+ * rounding in the fp32 build (its n-step kernels are separate instances, so that the single-step ones keep their
+ * register count; nvcc contracts a few multiply-adds differently); flags, counters and reset draws are the same.
+ *   actions_per_step  != 0: action is (n_steps, N, M, action_dim) and noise (n_steps, N, M, S, noise_dim);
+ *                     == 0: one (N, M, action_dim) slice is held for every step
+ *   outputs_per_step  != 0: obs (n_steps, N, M, obs_dim), reward / terminated / truncated (n_steps, N),
+ *                           drone_flags (n_steps, N, M): every step's outputs are kept;
+ *                     == 0: the same (N, M, obs_dim) ... buffers are overwritten every step (the last step's remain) */
+int adrp_step_n(adrp_handle* h, int n_steps, int actions_per_step, int outputs_per_step, const void* action,
+                const void* noise, void* obs, void* reward, uint8_t* terminated, uint8_t* truncated,
+                uint8_t* drone_flags, void* stream);
 
 /* Same call with HOST buffers (the path a NumPy user of the reference takes): copies the action to the
  * device, launches, copies obs / reward / flags back and synchronises. */

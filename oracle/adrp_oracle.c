@@ -179,3 +179,37 @@ void fw_controller_mellinger(float statics[10], const float sp[16], const float 
     statics[8] = m.prev_setpoint_omega_roll; statics[9] = m.prev_setpoint_omega_pitch;
     out[0] = (float)m.ctl_roll; out[1] = (float)m.ctl_pitch; out[2] = (float)m.ctl_yaw; out[3] = m.ctl_thrust;
 }
+
+/* sp[16] as above plus the high-level commander's form of the yaw setpoint (mode.yaw == modeAbs, attitude.yaw in degrees) */
+void fw_controller_mellinger_yaw(float statics[10], const float sp[16], int yaw_abs, float yaw_deg, const float pos[3],
+                                 const float vel[3], const float q[4], const float gyro_deg[3], float mass, float out[4])
+{
+    mel_state_f64 m;
+    memset(&m, 0, sizeof(m));
+    m.i_error_x = statics[0]; m.i_error_y = statics[1]; m.i_error_z = statics[2];
+    m.i_error_m_x = statics[3]; m.i_error_m_y = statics[4]; m.i_error_m_z = statics[5];
+    m.prev_omega_roll = statics[6]; m.prev_omega_pitch = statics[7];
+    m.prev_setpoint_omega_roll = statics[8]; m.prev_setpoint_omega_pitch = statics[9];
+    memcpy(m.sp_pos, sp, 12); memcpy(m.sp_vel, sp + 3, 12); memcpy(m.sp_acc, sp + 6, 12);
+    memcpy(m.sp_rate_deg, sp + 9, 12); memcpy(m.sp_quat, sp + 12, 16);
+    m.sp_yaw_abs = yaw_abs; m.sp_yaw_deg = yaw_deg;
+    controller_mellinger_f64(&m, mass, pos, vel, q, gyro_deg);
+    statics[0] = m.i_error_x; statics[1] = m.i_error_y; statics[2] = m.i_error_z;
+    statics[3] = m.i_error_m_x; statics[4] = m.i_error_m_y; statics[5] = m.i_error_m_z;
+    statics[6] = m.prev_omega_roll; statics[7] = m.prev_omega_pitch;
+    statics[8] = m.prev_setpoint_omega_roll; statics[9] = m.prev_setpoint_omega_pitch;
+    out[0] = (float)m.ctl_roll; out[1] = (float)m.ctl_pitch; out[2] = (float)m.ctl_yaw; out[3] = m.ctl_thrust;
+}
+
+/* ---- high-level commander (adrp_oracle_planner.h) for firmware_stub.py: `p` is fw_hl_sizeof() bytes owned by the stub */
+int fw_hl_sizeof(void) { return (int)sizeof(planner_f64); }
+void fw_hl_init(void* p) { hl_init_f64((planner_f64*)p); }
+void fw_hl_stop(void* p) { hl_stop_f64((planner_f64*)p); }
+void fw_hl_update_time(void* p, float t) { hl_update_time_f64((planner_f64*)p, t); }
+void fw_hl_tell_state(void* p, const float pos[3], const float vel[3], float yaw_deg) { hl_tell_state_f64((planner_f64*)p, pos, vel, yaw_deg); }
+int fw_hl_takeoff(void* p, float height, float duration, int use_current_yaw, float yaw) { return hl_takeoff_f64((planner_f64*)p, height, duration, use_current_yaw, yaw); }
+int fw_hl_land(void* p, float height, float duration, int use_current_yaw, float yaw) { return hl_land_f64((planner_f64*)p, height, duration, use_current_yaw, yaw); }
+int fw_hl_takeoff_vel(void* p, float height, float velocity, int relative) { return hl_takeoff_vel_f64((planner_f64*)p, height, velocity, relative); }
+int fw_hl_land_vel(void* p, float height, float velocity, int relative) { return hl_land_vel_f64((planner_f64*)p, height, velocity, relative); }
+int fw_hl_go_to(void* p, float x, float y, float z, float yaw, float duration, int relative) { return hl_go_to_f64((planner_f64*)p, x, y, z, yaw, duration, relative); }
+int fw_hl_get_setpoint(void* p, const float pos[3], const float vel[3], float yaw_deg, float out[13]) { return hl_get_setpoint_f64((planner_f64*)p, pos, vel, yaw_deg, out); }

@@ -77,6 +77,9 @@ static inline CF tanf(CF x) { return c_tan(x); }
 static inline CF cosf(CF x) { return c_cos(x); }
 static inline CF sinf(CF x) { return c_sin(x); }
 static inline CF fabsf(CF x) { return c_fabs(x); }
+static inline CF copysignf(CF a, CF b) { return CF(::copysignf(a.v, b.v)); }      /* high-level commander (adrp_oracle_planner.h) */
+static inline CF fmodf(CF a, CF b) { cnt::c[cnt::DIV]++; return CF(::fmodf(a.v, b.v)); }
+static inline CF floorf(CF a) { return CF(::floorf(a.v)); }
 static inline bool isfinite(CF x) { return ::isfinite(x.v); }
 static inline bool isfinite(CD x) { return ::isfinite(x.v); }
 

@@ -20,6 +20,8 @@ static void FN(philox)(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint6
 static REAL FN(u01)(uint32_t x) { return (REAL)(x >> 8) * (REAL)5.9604644775390625e-08; }          /* [0,1) */
 static REAL FN(u01_open)(uint32_t x) { return (REAL)((x >> 8) + 1) * (REAL)5.9604644775390625e-08; } /* (0,1] */
 
+#include "adrp_oracle_planner.h"
+
 /* ---------------------------------------------------------------- firmware core (float32, declared) */
 typedef struct FN(mel_state) {
     /* wrapper state (MellingerControl.reset, :99-150) */
@@ -35,6 +37,15 @@ typedef struct FN(mel_state) {
     float ctl_thrust;
     /* setpoint_t (full-state command, :510-543) */
     float sp_pos[3], sp_vel[3], sp_acc[3], sp_rate_deg[3], sp_quat[4];
+    /* ... as the high-level commander leaves it (crtpCommanderHighLevelGetSetpoint): mode.yaw = modeAbs with
+     * attitude.yaw in degrees, mode.quat = modeDisable */
+    float sp_yaw_deg;
+    int32_t sp_yaw_abs;
+    /* high-level commander (MellingerControl.py:292-303,:369-374,:547-699) */
+    int32_t hl_active;             /* not full_state_cmd_override */
+    FN(planner) plan;
+    /* state_t as last written by _update_state (:446-471; C floats): what _notifySetpointStop hands to TellState */
+    float st_pos[3], st_vel[3], st_yaw_deg;
     /* motor commands: what MultiRaceAviary keeps in self.rpms (prev_rpms lives in the state row 16:20) */
     REAL rpms[4];
     /* state_t.acc.z as stored (float) for the tumble check (:382) */
@@ -95,6 +106,7 @@ static void FN(controller_mellinger)(FN(mel_state)* m, float mass, const float p
     /* desired yaw from the setpoint quaternion (mode.quat == modeAbs): quat2rpy().z in degrees */
     const float sx = m->sp_quat[0], sy = m->sp_quat[1], sz = m->sp_quat[2], sw = m->sp_quat[3];
     float desiredYaw = FN(degreesf)(FW_ATAN2F(2.0f * (sw * sz + sx * sy), 1 - 2 * (sy * sy + sz * sz)));
+    if (m->sp_yaw_abs) desiredYaw = m->sp_yaw_deg;                 /* mode.yaw == modeAbs: setpoint->attitude.yaw */
     /* R = quat2rotmat(state quaternion) */
     const float x = q[0], y = q[1], z = q[2], w = q[3];
     float R[3][3] = {{1 - 2 * y * y - 2 * z * z, 2 * x * y - 2 * z * w, 2 * x * z + 2 * y * w},
@@ -254,6 +266,12 @@ static void FN(race_init_env)(FN(orc)* h, int n, const REAL* draws)
         memset(m, 0, sizeof(*m));
         for (int k = 0; k < 3; ++k) { m->prev_rpy[k] = (REAL)(c->init_rpy[i][k] * (M_PI / 180.0)); m->prev_vel[k] = 0; }
         m->state_acc_z = 1.0f;                                       /* _update_state(0, pos, vel, VEC3_UP, rpy) */
+        {   /* crtpCommanderHighLevelInit(); ...TellState(self.state): the NOMINAL initial pose (initial_obs, E17) */
+            FN(hl_init)(&m->plan);
+            for (int k = 0; k < 3; ++k) { m->st_pos[k] = (float)(REAL)c->init_xyz[i][k]; m->st_vel[k] = 0; }
+            m->st_yaw_deg = (float)(m->prev_rpy[2] * (REAL)(180.0 / M_PI));
+            FN(hl_tell_state)(&m->plan, m->st_pos, m->st_vel, m->st_yaw_deg);
+        }
         r->current_gate[(size_t)n * M + i] = 0;
         r->latch[(size_t)n * M + i] = 0;
     }
@@ -284,6 +302,21 @@ static void FN(mellinger_tick)(FN(orc)* h, FN(mel_state)* m, const REAL* st, con
     float gyro[3];
     for (int k = 0; k < 3; ++k)
         gyro[k] = FN(lpf2p_apply)(&h->race->gyro_lpf, &m->gyro_d1[k], &m->gyro_d2[k], (float)(rates[k] * RAD_TO_DEG));
+    /* _update_setpoint (:369-374): while no full-state command overrides it, the high-level commander writes the setpoint.
+     * state_t fields are C floats: position, velocity, attitude.yaw = yaw in degrees (_update_state, :446-471) */
+    for (int k = 0; k < 3; ++k) { m->st_pos[k] = pos[k]; m->st_vel[k] = vel[k]; }
+    m->st_yaw_deg = (float)(rpy[2] * RAD_TO_DEG);
+    if (m->hl_active) {
+        float sp13[13];
+        const float yaw_deg = m->st_yaw_deg;
+        FN(hl_tell_state)(&m->plan, pos, vel, yaw_deg);
+        FN(hl_update_time)(&m->plan, (float)((double)m->tick / 500.0));
+        if (FN(hl_get_setpoint)(&m->plan, pos, vel, yaw_deg, sp13)) {
+            for (int k = 0; k < 3; ++k) { m->sp_pos[k] = sp13[k]; m->sp_vel[k] = sp13[3 + k]; m->sp_acc[k] = sp13[6 + k]; m->sp_rate_deg[k] = sp13[9 + k]; }
+            m->sp_yaw_deg = sp13[12];
+            m->sp_yaw_abs = 1;
+        }
+    }
     /* _step_controller (:378-419) */
     REAL pwms[4] = {0, 0, 0, 0};
     if (m->state_acc_z < -0.5f) m->tumble_counter += 1; else m->tumble_counter = 0;   /* :382-385 */
@@ -536,8 +569,36 @@ static void FN(race_step_env)(FN(orc)* h, int n, const REAL* action, const REAL*
     for (int i = 0; i < M; ++i) {
         FN(mel_state)* m = r->mel + (size_t)n * M + i;
         if (r->latch[(size_t)n * M + i] & ADRP_FLAG_ELIMINATED) continue;
-        const int full = c->action_type == ADRP_ACT_MEL_FULL;         /* (Command.FULLSTATE, (pos, vel, acc, yaw, rpy_rate, t)) */
         const REAL* a = action + ((size_t)n * M + i) * h->A;
+        if (c->action_type == ADRP_ACT_MEL_CMD) {
+            /* (Command, args) tuples (MultiRaceAviary.py:197-205 -> low_level_control, MellingerControl.py:32-57): the send*
+             * call queues the command and process_command_queue(args[-1]) (:292-303) pops it at once -- Stop(), then
+             * UpdateTime(args[-1]) (the LAST argument, whatever it means for that command), then the command itself */
+            const int cmd = (int)a[0];
+            const REAL* g = a + 1;
+            if (cmd == ADRP_CMD_NONE) continue;                      /* `else: continue`: no queue processing */
+            static const int last_arg[] = {0, 13, 1, 2, 2, 1, 2, 2, 0, 5, 0};   /* index of args[-1] per command */
+            FN(hl_stop)(&m->plan);
+            FN(hl_update_time)(&m->plan, (float)g[last_arg[cmd]]);
+            switch (cmd) {
+            case ADRP_CMD_TAKEOFF: FN(hl_takeoff)(&m->plan, (float)g[0], (float)g[1], 1, 0.0f); m->hl_active = 1; continue;
+            case ADRP_CMD_TAKEOFFYAW: FN(hl_takeoff)(&m->plan, (float)g[0], (float)g[1], 0, (float)g[2]); m->hl_active = 1; continue;
+            case ADRP_CMD_TAKEOFFVEL: FN(hl_takeoff_vel)(&m->plan, (float)g[0], (float)g[1], g[2] != 0); m->hl_active = 1; continue;
+            case ADRP_CMD_LAND: FN(hl_land)(&m->plan, (float)g[0], (float)g[1], 1, 0.0f); m->hl_active = 1; continue;
+            case ADRP_CMD_LANDYAW: FN(hl_land)(&m->plan, (float)g[0], (float)g[1], 0, (float)g[2]); m->hl_active = 1; continue;
+            case ADRP_CMD_LANDVEL: FN(hl_land_vel)(&m->plan, (float)g[0], (float)g[1], g[2] != 0); m->hl_active = 1; continue;
+            case ADRP_CMD_STOP: FN(hl_stop)(&m->plan); m->hl_active = 1; continue;
+            case ADRP_CMD_GOTO: FN(hl_go_to)(&m->plan, (float)g[0], (float)g[1], (float)g[2], (float)g[3], (float)g[4], g[5] != 0); m->hl_active = 1; continue;
+            case ADRP_CMD_NOTIFY:                                    /* _notifySetpointStop (:693-699): TellState(self.state), */
+                FN(hl_tell_state)(&m->plan, m->st_pos, m->st_vel, m->st_yaw_deg);   /* the state the last tick stored */
+                m->hl_active = 1;
+                continue;
+            default: break;                                          /* ADRP_CMD_FULLSTATE: the 14 arguments follow */
+            }
+            a = g;
+            m->hl_active = 0;                                        /* full_state_cmd_override = True (:543) */
+        }
+        const int full = c->action_type == ADRP_ACT_MEL_FULL || c->action_type == ADRP_ACT_MEL_CMD;   /* (Command.FULLSTATE, (pos, vel, acc, yaw, rpy_rate, t)) */
         for (int k = 0; k < 3; ++k) { m->sp_pos[k] = (float)a[k]; m->sp_vel[k] = 0; m->sp_acc[k] = 0; m->sp_rate_deg[k] = 0; }
         if (full)                                                    /* _sendFullStateCmd (MellingerControl.py:510-527) */
             for (int k = 0; k < 3; ++k) {
@@ -549,6 +610,7 @@ static void FN(race_step_env)(FN(orc)* h, int n, const REAL* action, const REAL*
         m->sp_quat[1] = (float)(COS((REAL)0) * SIN((REAL)0) * COS(yaw / 2) + SIN((REAL)0) * COS((REAL)0) * SIN(yaw / 2));
         m->sp_quat[2] = (float)(COS((REAL)0) * COS((REAL)0) * SIN(yaw / 2) - SIN((REAL)0) * SIN((REAL)0) * COS(yaw / 2));
         m->sp_quat[3] = (float)(COS((REAL)0) * COS((REAL)0) * COS(yaw / 2) + SIN((REAL)0) * SIN((REAL)0) * SIN(yaw / 2));
+        m->sp_yaw_abs = 0;                                           /* mode.quat = modeAbs, mode.yaw = modeDisable (:536-540) */
     }
     /* RewardWrapper.reset (wrapper.py:96-101) reads the reset observation of drone 0: current gate id, the
      * observed pose of gate 0 and the position.  Evaluated here, on the state the episode starts from. */

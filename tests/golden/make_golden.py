@@ -23,6 +23,7 @@ import warnings
 warnings.filterwarnings("ignore")
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
+OUT = os.environ.get("ADRP_GOLDEN_OUT", HERE)      # tests/test_golden_regen.py regenerates into a scratch directory
 sys.path.insert(0, os.path.join(ROOT, "oracle", "refstub"))
 sys.path.insert(0, os.environ.get("ADRP_REFERENCE_ROOT", "/root/reference"))
 sys.path.insert(0, ROOT)
@@ -38,7 +39,7 @@ from gym_pybullet_adrp.utils.enums import ActionType, DroneModel, ObservationTyp
 
 
 def _save(name, meta, **arrays):
-    path = os.path.join(HERE, name + ".npz")
+    path = os.path.join(OUT, name + ".npz")
     np.savez_compressed(path, meta=json.dumps(meta), **arrays)
     print(f"{name}: " + ", ".join(f"{k}{tuple(v.shape)}" for k, v in arrays.items()))
 
@@ -89,6 +90,31 @@ def rl_case(name, cls, M, physics, act, pyb, ctrl, steps, seed, scale=1.0):
     env.close()
     _save(name, meta, obs0=np.asarray(obs0, dtype=np.float64), actions=actions, obs=obs, reward=rew,
           terminated=term, truncated=trunc)
+
+
+def rl_reset_case(name, physics, act, pyb, ctrl, steps, reset_at, seed):
+    """HoverAviary with a reset() in the middle of the run: BaseRLAviary fills action_buffer once in __init__
+    (BaseRLAviary.py:66-67) and neither BaseAviary.reset nor _housekeeping touches it, so the observation reset()
+    returns and the following ctrl_freq//2 - 1 steps still carry the previous episode's actions in obs[12:]."""
+    rng = np.random.default_rng(seed)
+    env = HoverAviary(physics=physics, pyb_freq=pyb, ctrl_freq=ctrl, gui=False, obs=ObservationType.KIN, act=act)
+    obs0, _ = env.reset()
+    A = env.action_space.shape[1]
+    actions = (0.5 * rng.uniform(-1, 1, size=(steps, 1, A))).astype(np.float32)
+    obs = np.zeros((steps,) + tuple(np.asarray(obs0).shape))
+    rew, term, trunc = np.zeros(steps), np.zeros(steps, bool), np.zeros(steps, bool)
+    obs_reset = None
+    for k in range(steps):
+        if k == reset_at:
+            obs_reset, _ = env.reset()
+        o, r, te, tr, _ = env.step(actions[k])
+        obs[k], rew[k], term[k], trunc[k] = o, r, te, tr
+    meta = dict(env="hover", model="CF2X", physics=physics.name, M=1, act=act.name, pyb_freq=pyb, ctrl_freq=ctrl,
+                steps=steps, reset_at=reset_at, init_xyz=np.asarray(env.INIT_XYZS).tolist(),
+                init_rpy=np.asarray(env.INIT_RPYS).tolist(), target=np.asarray(env.TARGET_POS).tolist())
+    env.close()
+    _save(name, meta, obs0=np.asarray(obs0, dtype=np.float64), obs_reset=np.asarray(obs_reset, dtype=np.float64),
+          actions=actions, obs=obs, reward=rew, terminated=term, truncated=trunc)
 
 
 def vel_case(name, physics, M, pyb, ctrl, steps, seed, xyz=None):
@@ -166,6 +192,14 @@ def main():
         vel_case("vel_pyb_m2", Physics.PYB, 2, 240, 48, 60, 51, xyz=np.array([[0, 0, 0.5], [0.6, 0, 0.8]]))
         vel_case("vel_dyn_m1", Physics.DYN, 1, 240, 240, 120, 52, xyz=np.array([[0, 0, 0.4]]))
         rl_case("hover_pyb_vel", HoverAviary, 1, Physics.PYB, ActionType.VEL, 240, 30, 30, 53, scale=0.05)
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == "--r2":
+        # round 2: BASELINE config 4's formation as bench.py flies it (examples/downwash.py:45 generalised to 8 drones on a
+        # 1.2 m grid, heights 0.5 + 0.25 (k mod 4)): every downwash pair is evaluated, none sits on the formula's 1/dz^2
+        # singularity, so the fp32 build can be compared with the reference's own run over the whole second
+        ctrl_case("ctrl_pyb_all_s5_m8_wide", X, Physics.PYB_GND_DRAG_DW, 8, 240, 48, 48, 61, 0.005,
+                  xyz=np.array([[1.2 * (k % 3), 1.2 * (k // 3), 0.5 + 0.25 * (k % 4)] for k in range(8)]))
+        rl_reset_case("hover_pyb_rpm_reset", Physics.PYB, ActionType.RPM, 240, 30, 36, 12, 62)
         return
     # per-substep pins (S = 1) and 1 s flights (S = 8 / 5)
     ctrl_case("ctrl_dyn_cf2x_s1", X, Physics.DYN, 1, 240, 240, 240, 11, 0.03)

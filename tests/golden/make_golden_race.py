@@ -21,6 +21,7 @@ import warnings
 warnings.filterwarnings("ignore")
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
+OUT = os.environ.get("ADRP_GOLDEN_OUT", HERE)      # tests/test_golden_regen.py regenerates into a scratch directory
 REF = os.environ.get("ADRP_REFERENCE_ROOT", "/root/reference")
 sys.path.insert(0, os.path.join(ROOT, "oracle", "refstub"))
 sys.path.insert(0, REF)
@@ -131,7 +132,7 @@ def race_case(name, level, physics, racemode, M, steps, seed, actions=None):
         np.random.uniform = orig_uniform
         env.close()
     meta = dict(env="race", level=level, physics=physics.name, racemode=racemode.name, M=M, steps=steps)
-    np.savez_compressed(os.path.join(HERE, name + ".npz"), meta=json.dumps(meta), draws=draws, state0=state0,
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), meta=json.dumps(meta), draws=draws, state0=state0,
                         obs0=obs0, actions=actions, noise=noise, obs=obs, terminated=term, truncated=trunc,
                         current_gate=gate, eliminated=elim, finished=fin)
     print(name, "gates passed:", gate[-1].tolist(), "eliminated:", elim[-1].tolist(), "terminated at:",
@@ -167,7 +168,7 @@ def wrapper_case(name, level, M, steps, seed):
         np.random.uniform = orig_uniform
         base.close()
     meta = dict(env="race", level=level, physics="PYB", racemode="COMPARE", M=M, steps=n, wrappers=3)
-    np.savez_compressed(os.path.join(HERE, name + ".npz"), meta=json.dumps(meta), draws=draws, obs0=obs0,
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), meta=json.dumps(meta), draws=draws, obs0=obs0,
                         actions=actions[:n], obs=obs[:n], reward=rew[:n], terminated=term[:n], truncated=trunc[:n],
                         current_gate=gate[:n])
     print(name, "steps:", n, "gates:", gate[n - 1].tolist(), "return:", rew[:n].sum(), "terminated:", term[n - 1])
@@ -205,12 +206,110 @@ def fullstate_case(name, level, M, steps, seed):
         np.random.uniform = orig_uniform
         env.close()
     meta = dict(env="race", level=level, physics="PYB", racemode="COMPARE", M=M, steps=steps, full_state_actions=True)
-    np.savez_compressed(os.path.join(HERE, name + ".npz"), meta=json.dumps(meta), draws=draws, obs0=obs0, actions=act,
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), meta=json.dumps(meta), draws=draws, obs0=obs0, actions=act,
                         obs=obs, terminated=term, truncated=trunc, current_gate=gate)
     print(name, "gates:", gate[-1].tolist(), "terminated:", term[-1])
 
 
+CMD_ID = {"non": 0, "fst": 1, "tko": 2, "toy": 3, "tov": 4, "lnd": 5, "ldy": 6, "ldv": 7, "stp": 8, "gto": 9, "ntf": 10}
+
+
+def command_row(cmd, args):
+    """(Command, args) -> the 16-float row of ADRP_ACT_MEL_CMD (include/adrp.h): [command id, flattened args, 0...]."""
+    row = np.zeros(16)
+    row[0] = CMD_ID[cmd.value]
+    flat = np.concatenate([np.atleast_1d(np.asarray(a, dtype=float)) for a in args]) if len(args) else np.zeros(0)
+    row[1:1 + len(flat)] = flat
+    return row
+
+
+def _commander_run(name, level, M, steps, seed, policy):
+    """The driver loop of scripts/sim.py (:68-100) around the reference's MultiRaceAviary: policy(i, obs_i, sim_time) returns
+    what BaseController.predict returns.  Every (Command, args) sent is recorded as a 16-float row."""
+    cfg = munchify(json.loads(json.dumps(configs.builtin_config(level))))
+    rec = RecordingRNG(seed)
+    orig_uniform = np.random.uniform
+    np.random.uniform = rec.uniform
+    env = MultiRaceAviary(cfg, drone_model=DroneModel.CF2X, num_drones=M, physics=Physics.PYB, racemode=RaceMode.COMPARE)
+    env.np_random = rec
+    try:
+        obs, info = env.reset()
+        obs0, draws = obs.copy(), np.array(rec.uniforms)
+        agents = policy(obs, info)
+        rows = np.zeros((steps, M, 16))
+        out = np.zeros((steps,) + obs.shape)
+        term, trunc, gate = np.zeros(steps, bool), np.zeros(steps, bool), np.zeros((steps, M))
+        n = 0
+        for k in range(steps):
+            sim_time = k / cfg.ctrl_freq                                  # sim.py:75 (the CONFIG's ctrl_freq)
+            actions = [a(obs[i], sim_time) for i, a in enumerate(agents)]
+            for i, (cmd, args) in enumerate(actions):
+                rows[k, i] = command_row(cmd, args)
+            obs, r, te, tr, _ = env.step(actions)
+            out[k], term[k], trunc[k], gate[k] = obs, te, tr, env.current_gate
+            n = k + 1
+            if te or tr:
+                break
+    finally:
+        np.random.uniform = orig_uniform
+        env.close()
+    meta = dict(env="race", level=level, physics="PYB", racemode="COMPARE", M=M, steps=n, command_actions=True)
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), meta=json.dumps(meta), draws=draws, obs0=obs0, actions=rows[:n],
+                        obs=out[:n], terminated=term[:n], truncated=trunc[:n], current_gate=gate[:n])
+    print(name, "steps:", n, "gates:", gate[n - 1].tolist(), "terminated:", bool(term[n - 1]),
+          "commands:", sorted(set(rows[:n, :, 0].astype(int).ravel().tolist())))
+
+
+def commander_hardcoded_case(name, level, M, steps, seed):
+    """user_controller/HardCodedController.py, UNMODIFIED: TAKEOFF [0.3, 2] -> FULLSTATE along its spline -> NOTIFY -> LAND ->
+    NONE (:158-188), one instance per drone with info["delay"] = drone id (sim.py:70-72)."""
+    from user_controller.HardCodedController import HardCodedController
+
+    def policy(obs, info):
+        agents = []
+        for i in range(M):
+            info = dict(info or {})
+            info["delay"] = i
+            c = HardCodedController(i, obs[i], info)
+            agents.append(lambda o, t, c=c: c.predict(o, ep_time=t))
+        return agents
+    _commander_run(name, level, M, steps, seed, policy)
+
+
+def commander_script_case(name, level, M, steps, seed):
+    """Every Command of utils/enums.py:58-70 through the reference's low_level_control dispatch (MellingerControl.py:32-57):
+    take-off variants, go-to (absolute / relative), the land variants (which the firmware's planner refuses after the
+    Stop() that process_command_queue issues first), STOP, NOTIFY, NONE, and FULLSTATE in between."""
+    from gym_pybullet_adrp.utils.enums import Command
+
+    def script(i):
+        x0 = [1.0, 1.0][i % 2] + 0.0
+        def act(o, t, i=i):
+            k = int(round(t * 30))
+            p = np.array(o[0:3])
+            if i % 2 == 0:
+                plan = {0: (Command.TAKEOFFYAW, [0.4, 1.5, 0.3]), 12: (Command.NOTIFY, [t]), 14: (Command.GOTO, [[1.2, 1.1, 0.6], 0.2, 1.0, False]),
+                        40: (Command.GOTO, [[0.1, -0.1, 0.1], -0.1, 2.0, True]), 70: (Command.LANDVEL, [0.1, 0.3, False]),
+                        90: (Command.STOP, [t]), 100: (Command.TAKEOFFVEL, [0.2, 0.4, True]), 130: (Command.LANDYAW, [0.0, 2.0, 0.0])}
+            else:
+                plan = {0: (Command.TAKEOFFVEL, [0.5, 0.4, False]), 25: (Command.NOTIFY, [t]), 26: (Command.LAND, [0.0, 2.0]),
+                        40: (Command.GOTO, [[0.8, 0.7, 0.5], 0.0, 1.5, False]), 120: (Command.TAKEOFF, [0.6, 2.0]),
+                        140: (Command.TAKEOFFVEL, [0.1, 0.0, True])}
+            if k in plan:
+                return plan[k]
+            if i % 2 == 0 and 20 <= k < 38 or i % 2 == 1 and (95 <= k < 110 or 121 <= k < 125):
+                return (Command.FULLSTATE, [p + [0.0, 0.0, 0.02], np.zeros(3), np.zeros(3), 0.1, np.zeros(3), t])
+            return (Command.NONE, [])
+        return act
+
+    _commander_run(name, level, M, steps, seed, lambda obs, info: [script(i) for i in range(M)])
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "--commander":
+        commander_hardcoded_case("race_commander_hardcoded_gs", "getting_started", 2, 520, 8)
+        commander_script_case("race_commander_script_gs", "getting_started", 2, 160, 9)
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "--fullstate":
         fullstate_case("race_fullstate_compare_gs", "getting_started", 2, 200, 6)
         return

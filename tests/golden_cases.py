@@ -15,9 +15,10 @@ GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 CTRL_CASES = ["ctrl_dyn_cf2x_s1", "ctrl_dyn_cf2x_s8_m3", "ctrl_dyn_cf2p_s8", "ctrl_dyn_race_s8",
               "ctrl_dyn_cf2x_tilted", "ctrl_pyb_cf2x_s1", "ctrl_pyb_cf2x_s8_m2", "ctrl_pyb_cf2p_s8",
               "ctrl_pyb_race_s8", "ctrl_pyb_gnd_s8", "ctrl_pyb_drag_s8", "ctrl_pyb_dw_s5_m4",
-              "ctrl_pyb_all_s5_m8", "ctrl_pyb_ground_contact"]
+              "ctrl_pyb_all_s5_m8", "ctrl_pyb_ground_contact", "ctrl_pyb_all_s5_m8_wide"]
 RL_CASES = ["hover_pyb_rpm", "hover_dyn_one_d_rpm", "hover_dyn_pid", "hover_pyb_one_d_pid",
             "multihover_pyb_rpm_m2", "hover_pyb_rpm_long"]
+RL_RESET_CASES = ["hover_pyb_rpm_reset"]                 # reset() in the middle of a run: the action buffer survives it
 PID_CASES = ["pid_dyn_c1", "pid_pyb_c1"]
 VEL_CASES = ["vel_pyb_m2", "vel_dyn_m1"]                 # VelocityAviary (ActionType.VEL through the env's own DSLPID)
 RL_VEL_CASES = ["hover_pyb_vel"]                         # BaseRLAviary ActionType.VEL (:208-223)
@@ -56,6 +57,7 @@ def rel_err(a, b, floor=1.0):
     return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), floor)))
 
 FULLSTATE_CASES = ["race_fullstate_compare_gs"]          # (Command.FULLSTATE, args) tuples with vel / acc / yaw / rates
+COMMANDER_CASES = ["race_commander_hardcoded_gs", "race_commander_script_gs"]   # every Command through the high-level commander
 WRAPPER_CASES = ["race_wrappers_compare_gs"]             # DroneObservationWrapper(RewardWrapper(MultiRaceAviary))
 RACE_CASES = ["race_pyb_compete_gs", "race_pyb_compare_level3", "race_dyn_compete_level1", "race_pyb_all_compete_level3"]
 

@@ -22,6 +22,7 @@ def lib():
     if _LIB is None:
         path = os.path.join(ORACLE_DIR, "liboracle.so")
         srcs = [os.path.join(ORACLE_DIR, f) for f in os.listdir(ORACLE_DIR) if f.endswith((".c", ".h"))]
+        srcs.append(os.path.join(ROOT, "include", "adrp.h"))
         if not os.path.exists(path) or any(os.path.getmtime(s) > os.path.getmtime(path) for s in srcs):
             build_oracle()
         _LIB = C.CDLL(path)

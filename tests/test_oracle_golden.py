@@ -41,6 +41,25 @@ def test_velocity_aviary_fp64(name):
     assert worst < TOL64, f"{name}: {worst:.3e}"
 
 
+@pytest.mark.parametrize("name", gc.RL_RESET_CASES)
+def test_rl_reset_keeps_action_buffer(name):
+    """reset() after `reset_at` steps: BaseRLAviary.action_buffer is created in __init__ (:66-67) and never cleared, so
+    the reference's reset observation and the following steps list the previous episode's actions."""
+    meta, z = gc.load(name)
+    env = OracleEnv(gc.config_for(meta))
+    assert gc.rel_err(env.reset()[0], z["obs0"]) < 1e-6
+    for k in range(meta["steps"]):
+        if k == meta["reset_at"]:
+            o = env.reset()
+            assert gc.rel_err(o[0, :, :12], z["obs_reset"][:, :12]) < 1e-6
+            np.testing.assert_array_equal(o[0, :, 12:], z["obs_reset"][:, 12:])
+            assert np.abs(o[0, :, 12:]).max() > 0                               # (it really carries old actions)
+        obs, rew, te, tr, _ = env.step(z["actions"][k][None].astype(np.float64))
+        assert gc.rel_err(obs[0, :, :12], z["obs"][k][:, :12]) < 1e-6, (name, k)
+        np.testing.assert_array_equal(obs[0, :, 12:], z["obs"][k][:, 12:])
+        assert abs(rew[0] - z["reward"][k]) < 1e-9 and bool(tr[0]) == bool(z["truncated"][k])
+
+
 @pytest.mark.parametrize("name", gc.RL_CASES + gc.RL_VEL_CASES)
 def test_rl_aviaries_fp64(name):
     meta, z = gc.load(name)
@@ -137,6 +156,27 @@ def test_race_fullstate_commands_fp64(name):
         np.testing.assert_array_equal(obs[0][:, 48], z["current_gate"][k])
         assert bool(te[0]) == bool(z["terminated"][k]) and bool(tr[0]) == bool(z["truncated"][k])
     assert z["current_gate"][-1].max() >= 1                      # the recorded flight does pass a gate
+
+
+@pytest.mark.parametrize("name", gc.COMMANDER_CASES)
+def test_race_commander_fp64(name):
+    """(Command, args) tuples of every kind through the reference's own low_level_control / process_command_queue /
+    _update_setpoint (MellingerControl.py:32-57,:292-303,:369-374,:547-699) over the declared planner restatement:
+    `hardcoded` is user_controller/HardCodedController.py, unmodified, driven by the loop of scripts/sim.py (TAKEOFF ->
+    FULLSTATE -> NOTIFY -> LAND -> NONE; both drones pass all four gates); `script` sends every other Command."""
+    meta, z = gc.load(name)
+    rc, cfg = gc.race_config_for(meta, command_actions=True)
+    env = OracleEnv(cfg)
+    env.reset(draws=gc.place_draws(rc, z["draws"], meta["M"])[None])
+    for k in range(meta["steps"]):
+        obs, rew, te, tr, fl = env.step(z["actions"][k][None])
+        assert gc.rel_err(obs[0], z["obs"][k]) < TOL64, (name, k, gc.rel_err(obs[0], z["obs"][k]))
+        np.testing.assert_array_equal(obs[0][:, 48], z["current_gate"][k])
+        assert bool(te[0]) == bool(z["terminated"][k]) and bool(tr[0]) == bool(z["truncated"][k])
+    if "hardcoded" in name:
+        assert z["current_gate"][-1].min() == 4 and z["terminated"][-1]      # the scripted flight finishes the track
+    else:
+        assert set(z["actions"][:, :, 0].astype(int).ravel()) == set(range(11))   # every Command occurs
 
 
 @pytest.mark.parametrize("name", gc.WRAPPER_CASES)
