@@ -17,7 +17,8 @@ LIB_PATH = os.path.join(PKG_DIR, "libadrp_b200.so")
 EXPORTS = ["adrp_create", "adrp_destroy", "adrp_obs_dim", "adrp_action_dim", "adrp_noise_dim",
            "adrp_reset_draws_dim", "adrp_substeps", "adrp_reset", "adrp_set_state", "adrp_get_state",
            "adrp_step", "adrp_step_n", "adrp_step_host", "adrp_dslpid_control", "adrp_launch_count", "adrp_set_profiling",
-           "adrp_step_kernel_ms", "adrp_fp32_peak_tflops", "adrp_last_error", "adrp_abi_version", "adrp_config_size"]
+           "adrp_step_kernel_ms", "adrp_fp32_peak_tflops", "adrp_last_error", "adrp_abi_version", "adrp_config_size",
+           "adrp_step_rows_static"]
 
 _lib = None
 
@@ -48,6 +49,7 @@ def load():
     lib.adrp_step_host.argtypes = [vp, vp, vp, vp, u8p, u8p, u8p]
     lib.adrp_dslpid_control.argtypes = [C.c_int, C.c_int, C.POINTER(_abi.DroneParamsC), C.c_double, C.c_int,
                                         C.c_double] + [vp] * 12
+    lib.adrp_step_rows_static.argtypes = [C.POINTER(_abi.ConfigC), vp, vp, vp, vp, vp, u8p, u8p, vp]
     lib.adrp_launch_count.argtypes = [vp]
     lib.adrp_launch_count.restype = C.c_int64
     lib.adrp_set_profiling.argtypes = [vp, C.c_int]

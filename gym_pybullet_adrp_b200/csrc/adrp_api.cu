@@ -5,6 +5,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 
@@ -697,3 +698,94 @@ double adrp_fp32_peak_tflops(int device)
 const char* adrp_last_error(const adrp_handle* h) { return h ? base(h)->err.c_str() : g_create_error.c_str(); }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// adrp_step_rows_static (include/adrp.h): a control step without a handle and without any allocation.  No counterpart in
+// the reference.
+//
+// The SoA working state of step_kernel lives in this file-scope device array.  In HOST code the name `g_static_scratch`
+// is only a stand-in for the symbol, NOT a device address (a kernel handed it would fault, or silently use host memory
+// where the GPU can reach it): the address comes from cudaGetSymbolAddress, once per device, with that device current.
+static __device__ __align__(256) unsigned char g_static_scratch[ADRP_STATIC_SCRATCH_BYTES];
+
+namespace {
+
+constexpr int kMaxStaticDevices = 64;
+std::mutex g_static_mu;
+unsigned char* g_static_ptr[kMaxStaticDevices] = {};      // device address of g_static_scratch on each device
+
+// Must be called with `device` current (DeviceGuard).
+int static_scratch_ptr(int device, unsigned char** out)
+{
+    if (device < 0 || device >= kMaxStaticDevices) { g_create_error = "adrp_step_rows_static: device ordinal out of range"; return ADRP_EINVAL; }
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_ptr[device]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess || !p) {
+            g_create_error = std::string("adrp_step_rows_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e);
+            return ADRP_ECUDA;
+        }
+        g_static_ptr[device] = (unsigned char*)p;
+    }
+    *out = g_static_ptr[device];
+    return ADRP_OK;
+}
+
+template <typename T>
+int step_rows_static(const adrp_config* cfg, const T* state_in, const T* action, T* state_out, T* obs, T* reward,
+                     uint8_t* te, uint8_t* tr, cudaStream_t s)
+{
+    KParams<T> P;
+    derive_params<T>(*cfg, P);
+    const size_t state_bytes = sizeof(T) * (size_t)F_COUNT * (size_t)P.Dpad;
+    const size_t counter_off = (state_bytes + 255) & ~(size_t)255;
+    const size_t need = counter_off + sizeof(int32_t) * (size_t)P.N;
+    if (need > (size_t)ADRP_STATIC_SCRATCH_BYTES) {
+        char msg[256];
+        snprintf(msg, sizeof(msg), "adrp_step_rows_static: %d envs x %d lanes need %zu bytes of scratch, the static array holds %u "
+                 "(ADRP_STATIC_SCRATCH_BYTES): use a handle (adrp_create) for batches of this size", P.N, P.Mpad, need,
+                 (unsigned)ADRP_STATIC_SCRATCH_BYTES);
+        g_create_error = msg;
+        return ADRP_EINVAL;
+    }
+    unsigned char* base_ptr = nullptr;
+    const int rc = static_scratch_ptr(cfg->device, &base_ptr);
+    if (rc != ADRP_OK) return rc;
+    KBuffers<T> B;
+    B.state = reinterpret_cast<T*>(base_ptr);
+    B.pid = nullptr; B.ring = nullptr; B.ring_head = nullptr;        // never touched by RPM-type actions on a CtrlAviary-kind env
+    B.step_counter = reinterpret_cast<int32_t*>(base_ptr + counter_off);
+    auto fail = [](const char* what, cudaError_t e) { g_create_error = std::string("adrp_step_rows_static: ") + what + ": " + cudaGetErrorString(e); return ADRP_ECUDA; };
+    cudaError_t e;
+    // the array keeps the last call's contents: the step counters must start at zero, the state part is overwritten below
+    if ((e = cudaMemsetAsync(B.step_counter, 0, sizeof(int32_t) * (size_t)P.N, s)) != cudaSuccess) return fail("cudaMemsetAsync", e);
+    if ((e = Launch<T>::set_state(P, B, state_in, s)) != cudaSuccess) return fail("set_state", e);
+    P.obs_vec = sizeof(T) == 4 && (P.O % 4) == 0 && ((uintptr_t)obs & 15) == 0;          // as do_step decides it
+    P.act_vec = sizeof(T) == 4 && P.A == 4 && ((uintptr_t)action & 15) == 0;
+    if ((e = Launch<T>::step(P, B, action, obs, reward, te, tr, nullptr, s)) != cudaSuccess) return fail("step", e);
+    P.obs_vec = P.act_vec = 0;
+    if ((e = Launch<T>::get_state(P, B, state_out, s)) != cudaSuccess) return fail("get_state", e);
+    return ADRP_OK;
+}
+
+}  // namespace
+
+extern "C" int adrp_step_rows_static(const adrp_config* cfg, const void* state_in, const void* action, void* state_out,
+                                     void* obs, void* reward, uint8_t* terminated, uint8_t* truncated, void* stream)
+{
+    int rc = validate(cfg);
+    if (rc != ADRP_OK) return rc;
+    if (!state_in || !action || !state_out || !obs || !reward || !terminated || !truncated) { g_create_error = "adrp_step_rows_static: NULL buffer"; return ADRP_EINVAL; }
+    if (cfg->env_kind != ADRP_ENV_CTRL || cfg->action_type != ADRP_ACT_RPM_RAW) {
+        g_create_error = "adrp_step_rows_static: env_kind must be ADRP_ENV_CTRL and action_type ADRP_ACT_RPM_RAW";
+        return ADRP_EUNSUPPORTED;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || cfg->device < 0 || cfg->device >= ndev) { g_create_error = "adrp_step_rows_static: invalid device ordinal"; return ADRP_ECUDA; }
+    DeviceGuard dg(cfg->device);
+    cudaStream_t s = (cudaStream_t)stream;
+    return cfg->precision == ADRP_F64
+        ? step_rows_static<double>(cfg, (const double*)state_in, (const double*)action, (double*)state_out, (double*)obs, (double*)reward, terminated, truncated, s)
+        : step_rows_static<float>(cfg, (const float*)state_in, (const float*)action, (float*)state_out, (float*)obs, (float*)reward, terminated, truncated, s);
+}

@@ -236,6 +236,31 @@ double adrp_step_kernel_ms(adrp_handle* h, int reset);
  * Returns a negative value on error. */
 double adrp_fp32_peak_tflops(int device);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * One control step of Env.step on caller-owned rows, WITHOUT a handle and WITHOUT any allocation: the structure-of-arrays
+ * working copy of the state that step_kernel runs on (what adrp_create cudaMallocs for a handle) lives in a file-scope
+ * `static __device__` array of ADRP_STATIC_SCRATCH_BYTES inside the library, which every GPU that loads the library holds
+ * until the process exits.  The call enqueues, on `stream`: rows -> SoA scratch, the step kernel (the same instances adrp_step
+ * launches, so results are bit-identical to adrp_set_state + adrp_step + adrp_get_state on a handle of the same config),
+ * SoA scratch -> rows.  It calls no cudaMalloc / cudaFree / cudaMallocHost and no allocating library routine.
+ *   cfg         env_kind must be ADRP_ENV_CTRL and action_type ADRP_ACT_RPM_RAW (any physics mask, drone model, M <= 32,
+ *               either precision); num_envs * lanes-per-env (M rounded up to a power of two) * 20 * sizeof(element)
+ *               + 4 * num_envs must not exceed ADRP_STATIC_SCRATCH_BYTES (fp32: about 100 000 padded drones), else
+ *               ADRP_EINVAL with a message naming the need and the limit (adrp_last_error(NULL))
+ *   state_in    (N, M, ADRP_STATE_DIM) device, cfg->precision        action  (N, M, 4) device
+ *   state_out   (N, M, ADRP_STATE_DIM) device (may alias state_in)   obs     (N, M, 20) device
+ *   reward      (N) device; terminated, truncated (N) bytes device
+ * The scratch is SHARED by every call in the process and keeps the last call's contents: the call overwrites all of it that
+ * it reads (the per-env step counters are cleared to zero first), so successive calls are independent of each other, but
+ * two calls that overlap on the GPU (different streams, or graphs replayed concurrently) RACE on it -- serialise them.
+ * First use on a device resolves the array's device address (cudaGetSymbolAddress) and loads the kernels: make one warm-up
+ * call outside a graph capture. */
+#define ADRP_STATIC_SCRATCH_BYTES (8u << 20)
+int adrp_step_rows_static(const adrp_config* cfg, const void* state_in, const void* action, void* state_out, void* obs,
+                          void* reward, uint8_t* terminated, uint8_t* truncated, void* stream);
+
 const char* adrp_last_error(const adrp_handle* h);   /* h may be NULL: error of the last failed adrp_create */
 int adrp_abi_version(void);
 int adrp_config_size(void);                           /* sizeof(adrp_config) for binding sanity checks */
