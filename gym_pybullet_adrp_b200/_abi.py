@@ -6,6 +6,8 @@ CUDA library (``_lib.py``) and, in tests, to the CPU oracle -- both take ``adrp_
 from __future__ import annotations
 
 import ctypes as C
+
+import numpy as np
 import math
 
 from .assets import DroneParams, drone_params
@@ -144,6 +146,19 @@ def make_config(*, num_envs, num_drones=1, drone_model=DroneModel.CF2X, physics=
     c.dslpid_drone = drone_params_c(drone_params(DroneModel.CF2X))
     c.track.contact_margin, c.track.visibility_range = 0.02, 0.45
     return c
+
+
+def command_row(cmd, args):
+    """``(Command, args)`` as ``BaseController.predict`` returns it -> the 16-float row of ``ACT_MEL_CMD`` (include/adrp.h):
+    ``[adrp_command, flattened args, 0 ...]``.  ``cmd``: the ``Command`` enum member (or its value string)."""
+    row = np.zeros(16)
+    row[0] = CMD_ID[getattr(cmd, "value", cmd)]
+    flat = [np.atleast_1d(np.asarray(a, dtype=float)) for a in args]
+    flat = np.concatenate(flat) if flat else np.zeros(0)
+    if len(flat) > 15:
+        raise ValueError(f"{cmd}: too many arguments")
+    row[1:1 + len(flat)] = flat
+    return row
 
 
 def make_race_config(race_config, *, num_envs, num_drones=2, drone_model=DroneModel.CF2X, physics=Physics.PYB,

@@ -96,6 +96,7 @@ int action_dim(int act)
     switch (act) {
     case ADRP_ACT_RPM_RAW: case ADRP_ACT_RPM: case ADRP_ACT_VEL: case ADRP_ACT_MEL: return 4;
     case ADRP_ACT_MEL_FULL: return 13;
+    case ADRP_ACT_MEL_CMD: return 16;
     case ADRP_ACT_PID: return 3;
     case ADRP_ACT_ONE_D_RPM: case ADRP_ACT_ONE_D_PID: return 1;
     case ADRP_ACT_PID_FULL: return 12;
@@ -276,6 +277,11 @@ int alloc_buffers(Handle<T>* h)
         CUDA_TRY(h, cudaMemset(rb.mel_f, 0, sizeof(float) * MF_COUNT * D));
         CUDA_TRY(h, cudaMemset(rb.mel_i, 0, sizeof(int32_t) * MI_COUNT * D));
         CUDA_TRY(h, cudaMemset(rb.gate_latch, 0, sizeof(int32_t) * D));
+        rb.hl = nullptr;
+        if (h->cfg.action_type == ADRP_ACT_MEL_CMD) {         // high-level commander state (planner, setpoint memory) per drone
+            CUDA_TRY(h, cudaMalloc(&rb.hl, sizeof(uint32_t) * kHlWordsMax * D));
+            CUDA_TRY(h, cudaMemset(rb.hl, 0, sizeof(uint32_t) * kHlWordsMax * D));
+        }
         // sub-rate schedule (MellingerControl.py:395-411): bit t <=> (t/500 - (t-1)/500 > 0.002) in float64
         std::vector<uint32_t> lut((size_t)R.lut_ticks / 32, 0u);
         for (int t = 1; t < R.lut_ticks; ++t) {
@@ -298,6 +304,7 @@ void free_buffers(Handle<T>* h)
     if (h->race) {
         RaceBuffers<T>& rb = h->RB;
         cudaFree(rb.track); cudaFree(rb.body); cudaFree(rb.mel_t); cudaFree(rb.mel_f); cudaFree(rb.mel_i);
+        cudaFree(rb.hl);
         cudaFree(rb.gate_latch); cudaFree(rb.episode); cudaFree(rb.shape_gate); cudaFree(rb.shape_vec);
         cudaFree(const_cast<uint32_t*>(rb.lut));
     }
@@ -380,7 +387,7 @@ int validate(const adrp_config* c)
     if (c->ctrl_freq < 1 || c->pyb_freq % c->ctrl_freq != 0) { g_create_error = "[ERROR] in BaseAviary.__init__(), pyb_freq is not divisible by env_freq."; return ADRP_EINVAL; }
     if (c->precision != ADRP_F32 && c->precision != ADRP_F64) { g_create_error = "unknown precision"; return ADRP_EINVAL; }
     if (action_dim(c->action_type) == 0) { g_create_error = "unknown action_type"; return ADRP_EINVAL; }
-    if ((c->env_kind == ADRP_ENV_RACE) != (c->action_type == ADRP_ACT_MEL || c->action_type == ADRP_ACT_MEL_FULL)) { g_create_error = "ADRP_ACT_MEL / ADRP_ACT_MEL_FULL (Mellinger full-state setpoints) are the race env's action types, and its only ones"; return ADRP_EINVAL; }
+    if ((c->env_kind == ADRP_ENV_RACE) != (c->action_type == ADRP_ACT_MEL || c->action_type == ADRP_ACT_MEL_FULL || c->action_type == ADRP_ACT_MEL_CMD)) { g_create_error = "ADRP_ACT_MEL / ADRP_ACT_MEL_FULL / ADRP_ACT_MEL_CMD (Mellinger setpoints and commands) are the race env's action types, and its only ones"; return ADRP_EINVAL; }
     if (c->wrappers & ~(ADRP_WRAP_OBS | ADRP_WRAP_REWARD)) { g_create_error = "unknown bit in wrappers"; return ADRP_EINVAL; }
     if (c->wrappers && c->env_kind != ADRP_ENV_RACE) { g_create_error = "wrappers (utils/wrapper.py) apply to the race env"; return ADRP_EINVAL; }
     if (c->env_kind == ADRP_ENV_RACE && (c->track.num_gates < 0 || c->track.num_gates > ADRP_MAX_GATES || c->track.num_obstacles < 0 || c->track.num_obstacles > ADRP_MAX_OBSTACLES)) { g_create_error = "too many gates / obstacles"; return ADRP_EINVAL; }

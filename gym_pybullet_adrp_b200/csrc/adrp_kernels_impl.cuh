@@ -173,9 +173,11 @@ using RaceStepFn = void (*)(KParams<T>, RaceParams<T>, KBuffers<T>, RaceBuffers<
 // then runs the instance without the wind / motor-noise terms; phy: the physics mask, for which the product build has
 // instances in their own translation units (race_step_special).
 template <typename T>
-inline RaceStepFn<T> race_step_fn(int mpad, bool full, bool quiet, int phy, bool multi = false)
+inline RaceStepFn<T> race_step_fn(int mpad, int action_type, bool quiet, int phy, bool multi = false)
 {
-    if (full) return multi ? race_step_kernel<T, 0, true, false, -1, true> : race_step_kernel<T, 0, true, false, -1>;    // (Command.FULLSTATE, args) actions: scripted controllers
+    // (Command, args) actions: scripted controllers -- 13-float FULLSTATE rows, or 16-float rows of any command
+    if (action_type == ADRP_ACT_MEL_FULL) return multi ? race_step_kernel<T, 0, 1, false, -1, true> : race_step_kernel<T, 0, 1, false, -1>;
+    if (action_type == ADRP_ACT_MEL_CMD) return multi ? race_step_kernel<T, 0, 2, false, -1, true> : race_step_kernel<T, 0, 2, false, -1>;
     if constexpr (M<T>::fast) {
         RaceStepFn<T> f = nullptr;
         constexpr int ALL = ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW | ADRP_PHY_GROUND;
@@ -183,17 +185,17 @@ inline RaceStepFn<T> race_step_fn(int mpad, bool full, bool quiet, int phy, bool
         if (phy == ALL) f = multi ? race_step_special_multi<ALL>(mpad, quiet) : race_step_special<ALL>(mpad, quiet);
         if (f) return f;
     }
-    if (multi) return race_step_kernel<T, 0, false, false, -1, true>;
+    if (multi) return race_step_kernel<T, 0, 0, false, -1, true>;
     if constexpr (M<T>::fast) {
         switch (mpad) {
-            case 1: return quiet ? race_step_kernel<T, 1, false, true, -1> : race_step_kernel<T, 1, false, false, -1>;
-            case 2: return quiet ? race_step_kernel<T, 2, false, true, -1> : race_step_kernel<T, 2, false, false, -1>;
-            case 4: return quiet ? race_step_kernel<T, 4, false, true, -1> : race_step_kernel<T, 4, false, false, -1>;
-            case 8: return quiet ? race_step_kernel<T, 8, false, true, -1> : race_step_kernel<T, 8, false, false, -1>;
+            case 1: return quiet ? race_step_kernel<T, 1, 0, true, -1> : race_step_kernel<T, 1, 0, false, -1>;
+            case 2: return quiet ? race_step_kernel<T, 2, 0, true, -1> : race_step_kernel<T, 2, 0, false, -1>;
+            case 4: return quiet ? race_step_kernel<T, 4, 0, true, -1> : race_step_kernel<T, 4, 0, false, -1>;
+            case 8: return quiet ? race_step_kernel<T, 8, 0, true, -1> : race_step_kernel<T, 8, 0, false, -1>;
             default: break;
         }
     }
-    return race_step_kernel<T, 0, false, false, -1>;
+    return race_step_kernel<T, 0, 0, false, -1>;
 }
 
 template <typename T>
@@ -203,7 +205,7 @@ cudaError_t Launch<T>::race_prepare(const RaceParams<T>& RP, const KParams<T>& P
     if (bytes <= 48 * 1024) return cudaSuccess;
     cudaError_t e = cudaSuccess;
     for (int v = 0; v < 4 && e == cudaSuccess; ++v)
-        e = cudaFuncSetAttribute(race_step_fn<T>(P.Mpad, P.action_type == ADRP_ACT_MEL_FULL, (v & 1) != 0, P.physics, (v & 2) != 0), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)race_smem_bytes(P, RP, kRaceBlock));
+        e = cudaFuncSetAttribute(race_step_fn<T>(P.Mpad, P.action_type, (v & 1) != 0, P.physics, (v & 2) != 0), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)race_smem_bytes(P, RP, kRaceBlock));
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(race_reset_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
 }
@@ -221,7 +223,7 @@ cudaError_t Launch<T>::race_step(const KParams<T>& P, const RaceParams<T>& RP, c
                                  const T* action, const T* noise, T* obs, T* reward, uint8_t* te, uint8_t* tr,
                                  uint8_t* fl, cudaStream_t s)
 {
-    launch_pdl(race_step_fn<T>(P.Mpad, P.action_type == ADRP_ACT_MEL_FULL, !noise && !RP.disturbances, P.physics, P.K > 1),
+    launch_pdl(race_step_fn<T>(P.Mpad, P.action_type, !noise && !RP.disturbances, P.physics, P.K > 1),
                (long long)(P.env_end - P.env_begin) * P.Mpad, kRaceBlock,
                race_smem_bytes(P, RP, kRaceBlock), s, P, RP, b, rb, action, noise, obs, reward, te, tr, fl);
     return cudaGetLastError();

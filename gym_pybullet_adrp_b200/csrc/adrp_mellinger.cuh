@@ -48,7 +48,12 @@ struct Mel {
 
 // Full-state command (MellingerControl._sendFullStateCmd, :510-543): yaw-only quaternion; vel / acc / attitude rates
 // (deg/s) are zero for ndarray actions (MultiRaceAviary.py:190-195) and literal zeros in those kernels.
-struct MelSetpoint { float pos[3], qz, qw, vel[3], acc[3], rate_deg[3], xc0, xc1; };
+// yaw_abs / yaw_deg: the setpoint as the high-level commander leaves it (crtpCommanderHighLevelGetSetpoint: mode.yaw = modeAbs
+// with attitude.yaw in degrees, mode.quat = modeDisable); only the ADRP_ACT_MEL_CMD instances (HL) read them.
+struct MelSetpoint { float pos[3], qz, qw, vel[3], acc[3], rate_deg[3], xc0, xc1, yaw_deg; int yaw_abs; };
+struct HlState;                      // adrp_planner.cuh
+template <typename T> __device__ inline void hl_update_setpoint(HlState& h, const float pos[3], const float vel[3], float yaw_deg, int tick);
+__device__ inline MelSetpoint& hl_setpoint(HlState& h);
 
 // fast build: heading of the desired x axis, constant over the control step.  The yaw-only setpoint quaternion is
 // (0, 0, sin(yaw/2), cos(yaw/2)): the firmware's atan2 arguments (dy_s, dy_c) ARE (sin yaw, cos yaw) up to their norm, so
@@ -81,7 +86,7 @@ __device__ __forceinline__ float fw_lpf2p(float b0, float b1, float b2, float a1
 }
 
 // controllerMellinger() with mode.x/y/z/quat = modeAbs, roll/pitch/yaw = modeDisable.
-template <typename T>
+template <typename T, bool HL = false>
 __device__ __forceinline__ void fw_mellinger(MelFw& m, const MelSetpoint& sp, float mass, const float pos[3],
                                              const float vel[3], const float q[4], const Mat3<T>& Rq, const float gyro_deg[3])
 {
@@ -123,10 +128,11 @@ __device__ __forceinline__ void fw_mellinger(MelFw& m, const MelSetpoint& sp, fl
     if (M<T>::fast) { const float in = M<float>::rcp(nt); zd0 = tt[0] * in; zd1 = tt[1] * in; zd2 = tt[2] * in; }
     else { zd0 = tt[0] / nt; zd1 = tt[1] / nt; zd2 = tt[2] / nt; }
     float xc0, xc1;
-    if (M<T>::fast) {
+    if (M<T>::fast && !HL) {
         xc0 = sp.xc0; xc1 = sp.xc1;                           // mel_setpoint_heading, once per control step
     } else {
-        const float desiredYaw = fw_degrees(FwMath<T>::atan2(dy_s, dy_c));
+        float desiredYaw = fw_degrees(FwMath<T>::atan2(dy_s, dy_c));
+        if (HL && sp.yaw_abs) desiredYaw = sp.yaw_deg;        // mode.yaw == modeAbs: setpoint->attitude.yaw (the planner's, per tick)
         FwMath<T>::sincos(fw_radians(desiredYaw), &xc1, &xc0);
     }
     const float xc2 = 0.0f;
@@ -205,10 +211,12 @@ __device__ __forceinline__ bool mel_schedule_fires(const RaceParams<T>& RP, cons
 }
 
 // One 500 Hz tick.  p, q, v: the drone's state AFTER this substep's physics.  noise4: motor thrust noise (N).
-template <typename T>
+// HL (ADRP_ACT_MEL_CMD): the high-level commander's _update_setpoint runs before the controller and the setpoint is hl's.
+template <typename T, bool HL = false>
 __device__ __forceinline__ void mellinger_tick(const RaceParams<T>& RP, const uint32_t* __restrict__ lut, Mel<T>& m,
-                                               const MelSetpoint& sp, const V3<T>& p, const Q4<T>& q, const V3<T>& v,
-                                               const T noise4[4], const Mat3<T>& Rq, const MelWindow win, int s)
+                                               const MelSetpoint& sp_in, const V3<T>& p, const Q4<T>& q, const V3<T>& v,
+                                               const T noise4[4], const Mat3<T>& Rq, const MelWindow win, int s,
+                                               HlState* hl = nullptr)
 {
     const T FIRMWARE_DT = (T)(1.0 / 500), RAD_TO_DEG = (T)(180.0 / 3.14159265358979323846), DEG_TO_RAD = (T)(3.14159265358979323846 / 180.0);
     // obs[i, 3:6] (:242); Rq: rotmat_loop(q), valid in the fast build only
@@ -245,6 +253,10 @@ __device__ __forceinline__ void mellinger_tick(const RaceParams<T>& RP, const ui
 #pragma unroll
     for (int k = 0; k < 3; ++k)
         gyro[k] = fw_lpf2p(RP.lpf_b0, RP.lpf_b1, RP.lpf_b2, RP.lpf_a1, RP.lpf_a2, m.gd1[k], m.gd2[k], (float)(M<T>::fast ? rates[k] : rates[k] * RAD_TO_DEG));
+    // _update_setpoint (:369-374): while no full-state command overrides it, the high-level commander writes the setpoint
+    // (state_t fields are C floats: position, velocity, attitude.yaw in degrees)
+    if (HL) hl_update_setpoint<T>(*hl, pos, vel, (float)(rpy.z * RAD_TO_DEG), m.tick);
+    const MelSetpoint& sp = HL ? hl_setpoint(*hl) : sp_in;
     // _step_controller (:378-419)
     if (m.acc_z < -0.5f) m.tumble += 1; else m.tumble = 0;                       // :382-385
     const bool stop = m.tumble >= 30;
@@ -256,7 +268,7 @@ __device__ __forceinline__ void mellinger_tick(const RaceParams<T>& RP, const ui
                                                   : mel_schedule_fires(RP, lut, m.tick, m.last_att);
         if (fires) {
             m.last_att = m.tick;
-            fw_mellinger<T>(m.fw, sp, RP.mel_mass, pos, vel, qf, Rq, gyro);
+            fw_mellinger<T, HL>(m.fw, sp, RP.mel_mass, pos, vel, qf, Rq, gyro);
         }
         m.tick += 1;
     }

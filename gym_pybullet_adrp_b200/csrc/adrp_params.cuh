@@ -74,6 +74,7 @@ enum MelF { MF_GD1X = 0, MF_GD1Y, MF_GD1Z, MF_GD2X, MF_GD2Y, MF_GD2Z, MF_IEX, MF
             MF_POR, MF_POP, MF_PSR, MF_PSP, MF_THRUST, MF_ACCZ, MF_COUNT };
 enum MelI { MI_TICK = 0, MI_TUMBLE, MI_LAST_ATT, MI_CTL_RP, MI_CTL_Y_ERR, MI_COUNT };   // CTL_RP = roll | pitch<<16; CTL_Y_ERR = yaw | error<<16
 
+constexpr int kHlWordsMax = 80;          // >= sizeof(HlState) / 4 (adrp_planner.cuh): what the host allocates per padded drone
 template <typename T>
 struct RaceBuffers {
     T* track;               // [TF][N]      actual gates / obstacles of each env
@@ -85,6 +86,7 @@ struct RaceBuffers {
     int32_t* episode;       // [N]          resets so far (Philox counter word)
     int32_t* shape_gate;    // [N]          RewardWrapper.current_gate_id, -1 = read it on the next step (wrapper.py:96-101)
     T* shape_vec;           // [6][N]       RewardWrapper.current_target xyz, previous_pos xyz
+    uint32_t* hl;           // [kHlWords][Dpad] high-level commander state (HlState, word by word); ADRP_ACT_MEL_CMD handles only
     const uint32_t* lut;    // [lut_ticks/32] bit t: (t/500 - (t-1)/500 > 0.002) in float64 (MellingerControl.py:395-411)
 };
 

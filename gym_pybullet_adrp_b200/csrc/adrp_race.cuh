@@ -8,6 +8,7 @@
 // one warp, the block's track instances staged in shared memory.
 #pragma once
 #include "adrp_mellinger.cuh"
+#include "adrp_planner.cuh"
 #include "adrp_step.cuh"
 #include "adrp_track.cuh"
 
@@ -140,6 +141,20 @@ __device__ __noinline__ void race_reset_drone(const KParams<T>& P, const RacePar
     m.fw = MelFw{};
     m.acc_z = 1.0f;                                                 // _update_state(0, pos, vel, VEC3_UP, rpy)
     m.tick = m.tumble = m.last_att = m.error = 0;
+}
+
+static_assert(kHlWords <= kHlWordsMax, "the host allocates kHlWordsMax words per padded drone");
+template <typename T>
+__device__ inline void load_hl(const RaceBuffers<T>& rb, long long D, long long t, HlState& h)
+{
+    uint32_t* w = reinterpret_cast<uint32_t*>(&h);
+    for (int k = 0; k < kHlWords; ++k) w[k] = rb.hl[(long long)k * D + t];
+}
+template <typename T>
+__device__ inline void store_hl(const RaceBuffers<T>& rb, long long D, long long t, const HlState& h)
+{
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(&h);
+    for (int k = 0; k < kHlWords; ++k) rb.hl[(long long)k * D + t] = w[k];
 }
 
 template <typename T>

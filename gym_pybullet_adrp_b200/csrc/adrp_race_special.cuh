@@ -10,10 +10,10 @@ template <int PHY, bool MULTI>
 RaceStepFnF32 race_step_special_impl(int mpad, bool quiet)
 {
     switch (mpad) {
-        case 1: return quiet ? race_step_kernel<float, 1, false, true, PHY, MULTI> : race_step_kernel<float, 1, false, false, PHY, MULTI>;
-        case 2: return quiet ? race_step_kernel<float, 2, false, true, PHY, MULTI> : race_step_kernel<float, 2, false, false, PHY, MULTI>;
-        case 4: return quiet ? race_step_kernel<float, 4, false, true, PHY, MULTI> : race_step_kernel<float, 4, false, false, PHY, MULTI>;
-        case 8: return quiet ? race_step_kernel<float, 8, false, true, PHY, MULTI> : race_step_kernel<float, 8, false, false, PHY, MULTI>;
+        case 1: return quiet ? race_step_kernel<float, 1, 0, true, PHY, MULTI> : race_step_kernel<float, 1, 0, false, PHY, MULTI>;
+        case 2: return quiet ? race_step_kernel<float, 2, 0, true, PHY, MULTI> : race_step_kernel<float, 2, 0, false, PHY, MULTI>;
+        case 4: return quiet ? race_step_kernel<float, 4, 0, true, PHY, MULTI> : race_step_kernel<float, 4, 0, false, PHY, MULTI>;
+        case 8: return quiet ? race_step_kernel<float, 8, 0, true, PHY, MULTI> : race_step_kernel<float, 8, 0, false, PHY, MULTI>;
         default: return nullptr;
     }
 }

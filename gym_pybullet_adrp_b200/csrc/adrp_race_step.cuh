@@ -46,6 +46,11 @@ race_reset_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ 
         store_drone(b, P.Dpad, t, d);
         store_mel(rb, P.Dpad, t, m);
         store_body(rb, P.Dpad, t, body);
+        if (rb.hl) {                                           // ADRP_ACT_MEL_CMD: crtpCommanderHighLevelInit + TellState
+            HlState hl;
+            hl_reset(P, RP, i, hl);
+            store_hl(rb, P.Dpad, t, hl);
+        }
         rb.gate_latch[t] = 0;
         if (i == 0) { rb.episode[env] = episode + 1; b.step_counter[env] = 0; rb.shape_gate[env] = -1; }
     }
@@ -73,11 +78,12 @@ race_reset_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ 
 
 // MultiRaceAviary.step (:171-270).  noise: NULL or (N, M, S, 7) = [wind force xyz (N), motor thrust noise x4 (N)].
 // MP: lanes per env at compile time (unrolled neighbour loops), 0 = read from the params.
-// FULL: 13-float (Command.FULLSTATE, args) actions (ADRP_ACT_MEL_FULL) instead of [x, y, z, yaw].
+// ACTM: action rows -- 0: [x, y, z, yaw] (ADRP_ACT_MEL); 1: 13-float (Command.FULLSTATE, args) rows (ADRP_ACT_MEL_FULL);
+// 2: 16-float (Command, args) rows of any command, the high-level commander on the device (ADRP_ACT_MEL_CMD).
 // QUIET: the launch has no disturbance draws (noise == NULL and RaceParams::disturbances == 0).
 // PHY_CT >= 0: physics mask known at compile time (no per-substep mask tests: +6 % on C5M); -1: read from the params.
 // MULTI: adrp_step_n instances -- P.K control steps per launch (the single-step instances compile the loop away).
-template <typename T, int MP, bool FULL, bool QUIET, int PHY_CT, bool MULTI = false>
+template <typename T, int MP, int ACTM, bool QUIET, int PHY_CT, bool MULTI = false>
 __global__ void ADRP_RACE_BOUNDS
 race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ RaceParams<T> RP, const KBuffers<T> b,
                  const RaceBuffers<T> rb, const T* __restrict__ action, const T* __restrict__ noise, T* __restrict__ obs,
@@ -86,6 +92,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T* trk = reinterpret_cast<T*>(smem_raw);
+    constexpr bool CMD = ACTM == 2, FULL = ACTM != 0;         // command rows carry the 13 FULLSTATE floats after the command id
     const int mpad = MP > 0 ? MP : P.Mpad;
     const long long t = (long long)P.env_begin * mpad + (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
@@ -117,6 +124,8 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
         init_drone(P, 0, d);
         m = Mel<T>{};
     }
+    HlState hl = {};
+    if (CMD && valid) load_hl(rb, D, t, hl);
     int current_gate = gl & 0xffff, latch = gl >> 16;
     // RewardWrapper state (wrapper.py:78-80) of this env, held by drone 0's thread
     int sh_gate = 0;
@@ -163,8 +172,13 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
 
     // ---- ndarray action -> FULLSTATE(pos, 0, 0, yaw, 0, step_counter) (:190-202)
     MelSetpoint sp = {{0.0f, 0.0f, 0.0f}, 0.0f, 1.0f, {0.0f, 0.0f, 0.0f}, {0.0f, 0.0f, 0.0f}, {0.0f, 0.0f, 0.0f}, 1.0f, 0.0f};
-    if (valid && !eliminated) {
-        const T* a = action + (long long)kv * P.act_step + od * (FULL ? 13 : 4);
+    bool new_setpoint = valid && !eliminated;
+    const T* a = action + (long long)kv * P.act_step + od * (CMD ? 16 : (FULL ? 13 : 4));
+    if (CMD && new_setpoint) {                                // any (Command, args) tuple: only FULLSTATE carries a setpoint
+        new_setpoint = hl_command<T>(hl, a);
+        a += 1;
+    }
+    if (new_setpoint) {
         T a_yaw;
         if (M<T>::fast && !FULL && P.act_vec) {               // one 16-byte load per drone instead of four strided ones
             const float4 a4 = *reinterpret_cast<const float4*>(a);
@@ -184,6 +198,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
         M<T>::sincos(yaw / T(2), &sy, &cy);                   // utils.get_quaternion_from_euler(0, 0, yaw)
         sp.qz = (float)sy; sp.qw = (float)cy;
         mel_setpoint_heading<T>(sp);
+        if (CMD) hl.sp = sp;                                  // (yaw_abs = 0: mode.quat = modeAbs, mode.yaw = modeDisable, :536-540)
     }
 
     // ---- RewardWrapper.reset (wrapper.py:96-101) reads drone 0's row of the reset observation: current gate id,
@@ -283,7 +298,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
         } else {
 #pragma unroll
             for (int k = 0; k < 4; ++k) d.last_rpm[k] = m.rpms[k];                       // prev_rpms[i] = rpms[i] (:251)
-            mellinger_tick(RP, rb.lut, m, sp, d.p, d.q, d.v, QUIET ? (const T*)nullptr : nz + 3, R, win, s);                   // rpms[i] = recv() (:254)
+            mellinger_tick<T, CMD>(RP, rb.lut, m, sp, d.p, d.q, d.v, QUIET ? (const T*)nullptr : nz + 3, R, win, s, CMD ? &hl : nullptr);   // rpms[i] = recv() (:254)
         }
     }
     if (ks == K - 1) pdl_launch_dependents();             // the next launch's blocks may be scheduled during the epilogue
@@ -409,6 +424,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
 #pragma unroll
         for (int k = 0; k < 4; ++k) body[k] = body2[k];
         store_body(rb, D, t, body2);
+        if (CMD) hl_reset(P, RP, i, hl);
         current_gate = 0; latch = 0;
         episode += 1;
         sh_gate = -1;
@@ -426,6 +442,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
         }
         store_drone(b, D, t, d);
         store_mel(rb, D, t, m);
+        if (CMD) store_hl(rb, D, t, hl);
         rb.gate_latch[t] = current_gate | (latch << 16);
     }
 }

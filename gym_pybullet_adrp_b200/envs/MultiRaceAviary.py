@@ -38,11 +38,12 @@ class MultiRaceAviary(BaseAviary):
         init_rpys = np.array([race_config["init_states"][d]["rpy"] for d in names], dtype=float) * np.pi / 180   # :95
         self._physics_mask = batch.pop("physics_mask", None)
         self._wrappers = int(batch.pop("wrappers", 0))       # _abi.WRAP_* (utils/wrapper.py fused into the step kernel)
-        # (Command, args) tuple actions need the 13-float FULLSTATE rows (ADRP_ACT_MEL_FULL); the batched default is
-        # the 4-float [x, y, z, yaw] row the reference's ndarray path uses (:190-195)
-        full = batch.pop("full_state_actions", None)
-        self._full = (batch.get("num_envs", 1) == 1) if full is None else bool(full)
-        self._last_cmd = None
+        # (Command, args) tuple actions are 16-float command rows (ADRP_ACT_MEL_CMD: the firmware's high-level commander runs
+        # on the device) -- the default for a single env, like the reference; full_state_actions: 13-float FULLSTATE rows
+        # (ADRP_ACT_MEL_FULL); the batched default is the 4-float [x, y, z, yaw] row of the reference's ndarray path (:190-195)
+        full, cmd = batch.pop("full_state_actions", None), batch.pop("command_actions", None)
+        self._cmd = (batch.get("num_envs", 1) == 1 and not full) if cmd is None else bool(cmd)
+        self._full = bool(full) and not self._cmd
         super().__init__(drone_model=drone_model, num_drones=num_drones, initial_xyzs=init_xyzs, initial_rpys=init_rpys,
                          physics=physics, pyb_freq=pyb_freq, ctrl_freq=ctrl_freq, gui=gui, record=record, **batch)
 
@@ -52,7 +53,7 @@ class MultiRaceAviary(BaseAviary):
                                      ctrl_freq=self.CTRL_FREQ, racemode=self.racemode, precision=self.PRECISION,
                                      device=self.DEVICE, seed=self._seed or None, env_offset=self._env_offset,
                                      auto_reset=self._auto_reset, physics_mask=self._physics_mask,
-                                     wrappers=self._wrappers, full_state_actions=self._full)
+                                     wrappers=self._wrappers, full_state_actions=self._full, command_actions=self._cmd)
 
     # ------------------------------------------------------------------ spaces (:284-343)
     def _actionSpace(self):
@@ -79,43 +80,31 @@ class MultiRaceAviary(BaseAviary):
         return self._out_obs(obs), self._computeInfo()
 
     def _rows_from_commands(self, action):
-        """[(Command, args)] per drone -> (NUM_DRONES, 13) FULLSTATE rows (MultiRaceAviary.py:198-205)."""
-        if not self._full:
-            raise ValueError("(Command, args) actions need full_state_actions=True (13-float FULLSTATE rows)")
-        rows = np.zeros((self.NUM_DRONES, 13))
-        for i, (cmd, args) in enumerate(action):
-            if cmd == Command.FULLSTATE:                           # MellingerControl.sendFullStateCmd (:492-543)
-                pos, vel, acc, yaw, rpy_rate = args[:5]
-                rows[i] = np.r_[np.asarray(pos, float), np.asarray(vel, float), np.asarray(acc, float), float(yaw),
-                                np.asarray(rpy_rate, float)]
-            elif cmd in (Command.NONE, Command.STOP) and self._last_cmd is not None:
-                rows[i] = self._last_cmd[i]                        # no new command: the firmware keeps its setpoint
-            elif cmd in (Command.NONE, Command.STOP):
-                raise ValueError("Command.NONE before any FULLSTATE command: the firmware's power-on setpoint is not restated")
-            else:
-                # TAKEOFF / LAND / GOTO / NOTIFY run pycffirmware's high-level commander (crtpCommanderHighLevel*), which
-                # is not in the reference tree and whose planner is not restated (DESIGN.md section 9)
-                raise NotImplementedError(f"{cmd}: the firmware's high-level commander planner is not on this path")
-        self._last_cmd = rows.copy()
-        return rows
+        """[(Command, args)] per drone -> (NUM_DRONES, 16) command rows (MultiRaceAviary.py:197-205): every Command of
+        utils/enums.py:58-70 -- FULLSTATE, the TAKEOFF / LAND variants, GOTO, STOP, NOTIFY, NONE."""
+        if not self._cmd:
+            raise ValueError("(Command, args) actions need command_actions=True (16-float ADRP_ACT_MEL_CMD rows)")
+        return np.stack([_abi.command_row(cmd, args) for cmd, args in action])
 
     def step(self, action, noise=None):
         """MultiRaceAviary.step (:171-270).  ``action``: ``(NUM_DRONES, 4)`` full-state setpoints [x, y, z, yaw]
-        (``(num_envs, NUM_DRONES, 4)`` when batched), ``(..., 13)`` rows [pos, vel, acc, yaw, rpy_rates] with
-        ``full_state_actions=True``, or -- single env -- the reference's list of ``(Command.FULLSTATE, args)`` tuples."""
+        (``(num_envs, NUM_DRONES, 4)`` when batched); ``(..., 13)`` rows [pos, vel, acc, yaw, rpy_rates] with
+        ``full_state_actions=True``; ``(..., 16)`` command rows (``_abi.command_row``) with ``command_actions=True``; or --
+        single env -- the reference's list of ``(Command, args)`` tuples, one per drone."""
         if isinstance(action, (list, tuple)) and len(action) and isinstance(action[0], (list, tuple)) \
                 and len(action[0]) == 2 and isinstance(action[0][0], Command):
             if not self._single:
-                raise ValueError("(Command, args) tuples are the single-env interface; pass (num_envs, NUM_DRONES, 13) rows")
+                raise ValueError("(Command, args) tuples are the single-env interface; pass (num_envs, NUM_DRONES, 16) rows")
             action = self._rows_from_commands(action)
-        elif self._full:
+        elif self._full or self._cmd:
             a = np.asarray(action.cpu() if hasattr(action, "cpu") else action, dtype=float)
-            if a.shape[-1] == 4:                                   # ndarray path: FULLSTATE(pos, 0, 0, yaw, 0) (:190-195)
-                full = np.zeros(a.shape[:-1] + (13,))
-                full[..., 0:3], full[..., 9] = a[..., 0:3], a[..., 3]
+            if a.shape[-1] == 4:                                   # ndarray path: FULLSTATE(pos, 0, 0, yaw, 0, step_counter) (:190-195)
+                full = np.zeros(a.shape[:-1] + ((16,) if self._cmd else (13,)))
+                o = 1 if self._cmd else 0
+                full[..., o:o + 3], full[..., o + 9] = a[..., 0:3], a[..., 3]
+                if self._cmd:
+                    full[..., 0], full[..., 14] = _abi.CMD_ID["fst"], self.step_counter
                 action = full
-            if self._single:
-                self._last_cmd = np.asarray(action, float).reshape(self.NUM_DRONES, 13).copy()
         h = self.handle
         obs, reward, terminated, truncated, self._last_flags = h.step(self._in_action(action), noise=noise)
         self.step_counter += self.PYB_STEPS_PER_CTRL

@@ -19,24 +19,20 @@ from typing import List
 
 import numpy as np
 
+from .. import _abi
 from ..envs import MultiRaceAviary
 from ..utils.enums import Command, Physics, RaceMode
 from ..utils.logger import Logger
 from ..utils.utils import load_config, load_controller
 
 
-def _row(action):
-    """One controller output -> 13-float FULLSTATE row (MultiRaceAviary.py:190-205)."""
+def _row(action, step_counter=0):
+    """One controller output -> 16-float command row (MultiRaceAviary.py:190-205): a ``(Command, args)`` tuple of any
+    Command, or an ndarray [x, y, z, yaw] = FULLSTATE(pos, 0, 0, yaw, 0, step_counter)."""
     if isinstance(action, tuple) and len(action) == 2 and isinstance(action[0], Command):
-        cmd, args = action
-        if cmd != Command.FULLSTATE:
-            raise NotImplementedError(f"{cmd}: only FULLSTATE commands and [x, y, z, yaw] setpoints are on this path")
-        pos, vel, acc, yaw, rates = args[:5]
-        return np.r_[np.asarray(pos, float), np.asarray(vel, float), np.asarray(acc, float), float(yaw), np.asarray(rates, float)]
+        return _abi.command_row(*action)
     a = np.asarray(action, float)
-    out = np.zeros(13)
-    out[0:3], out[9] = a[0:3], a[3]
-    return out
+    return _abi.command_row(Command.FULLSTATE, [a[0:3], np.zeros(3), np.zeros(3), a[3], np.zeros(3), step_counter])
 
 
 def simulate(config: str = "config/getting_started.yaml", controller: str | List[str] = None, n_runs: int = 10,
@@ -58,7 +54,7 @@ def simulate(config: str = "config/getting_started.yaml", controller: str | List
     batch_ctrl = all(hasattr(c, "predict_batch") for c in classes) and len(set(classes)) == 1
     env = MultiRaceAviary(cfg, num_drones=n_drones, physics=physics, racemode=racemode, num_envs=max(n_runs, 2),
                           device=device, precision=precision, auto_reset=False, seed=seed or 0,
-                          full_state_actions=not batch_ctrl)
+                          command_actions=not batch_ctrl)
     N, M, ctrl_freq = env.NUM_ENVS, n_drones, cfg["ctrl_freq"]
     import torch
     obs, info = env.reset()
@@ -84,7 +80,7 @@ def simulate(config: str = "config/getting_started.yaml", controller: str | List
             for r in range(n_runs):
                 if not done_h[r]:
                     for i in range(M):
-                        rows[r, i] = _row(agents[r][i].predict(obs_h[r, i], ep_time=sim_time))
+                        rows[r, i] = _row(agents[r][i].predict(obs_h[r, i], ep_time=sim_time), env.step_counter)
             actions = torch.as_tensor(rows, dtype=obs.dtype, device=obs.device)
         if logger is not None and not bool(done[log_env]):
             state = env.handle.get_state()[log_env].cpu().numpy()

@@ -162,6 +162,60 @@ def test_race_fullstate_commands_golden(name, precision):
     h.close()
 
 
+@pytest.mark.parametrize("name", gc.COMMANDER_CASES)
+@pytest.mark.parametrize("precision", [_abi.F64, _abi.F32])
+def test_race_commander_golden(name, precision):
+    """ADRP_ACT_MEL_CMD: (Command, args) rows of every Command through the high-level commander on the device (take-off /
+    land / go-to planner, command queue semantics of MellingerControl.py:32-57,:292-303,:369-374) against the reference's
+    own loop -- `hardcoded`: the unmodified user_controller/HardCodedController.py flying all four gates.
+    fp64: 1e-9 over the whole run; fp32: 1e-4 m / rad over the first second (25 control steps)."""
+    meta, z = gc.load(name)
+    rc, cfg = gc.race_config_for(meta, precision=precision, command_actions=True)
+    h = _handle(cfg)
+    assert h.A == 16
+    h.reset(draws=gc.place_draws(rc, z["draws"], meta["M"])[None])
+    for k in range(meta["steps"] if precision == _abi.F64 else 25):
+        obs, rew, te, tr, fl = h.step(z["actions"][k][None])
+        o = obs.cpu().numpy()[0].astype(np.float64)
+        if precision == _abi.F64:
+            assert gc.rel_err(o, z["obs"][k]) < TOL64, (name, k, gc.rel_err(o, z["obs"][k]))
+            np.testing.assert_array_equal(o[:, 48], z["current_gate"][k])
+            assert bool(te[0]) == bool(z["terminated"][k]) and bool(tr[0]) == bool(z["truncated"][k])
+        else:
+            assert np.abs(o[:, 0:3] - z["obs"][k][:, 0:3]).max() < TOL32, (name, k)
+            assert _ang_diff(o[:, 3:6], z["obs"][k][:, 3:6]).max() < TOL32, (name, k)
+    h.close()
+
+
+def test_race_commander_batched_and_step_n():
+    """Command rows over a batch (every env its own take-off height and go-to target), single steps vs one adrp_step_n launch,
+    with in-kernel auto-resets: the planner state lives in HBM between launches and is re-initialised with the env."""
+    import torch
+    from gym_pybullet_adrp_b200 import configs
+    N, M, K = 96, 2, 40
+    rng = np.random.default_rng(4)
+    rc = configs.load_config("getting_started")
+    rc["episode_len_sec"] = 1.0
+    cfg = _abi.make_race_config(rc, num_envs=N, num_drones=M, precision=_abi.F64, seed=2, auto_reset=True, command_actions=True)
+    rows = np.zeros((K, N, M, 16))
+    rows[0, :, :, 0] = _abi.CMD_ID["tko"]
+    rows[0, :, :, 1] = rng.uniform(0.3, 0.8, (N, M))
+    rows[0, :, :, 2] = 1.5
+    rows[12, :, :, 0] = _abi.CMD_ID["gto"]
+    rows[12, :, :, 1:4] = rng.uniform(-0.2, 0.2, (N, M, 3))
+    rows[12, :, :, 5], rows[12, :, :, 6] = 1.0, 1.0             # duration, relative
+    rows[30] = rows[0]                                            # after the in-kernel reset at 1 s: take off again
+    a, b = _handle(cfg), _handle(cfg)
+    outs = [[t.clone() for t in a.step(rows[k])] for k in range(K)]
+    got = b.step_n(rows, keep_outputs=True)
+    for j in range(5):
+        assert torch.equal(torch.stack([o[j] for o in outs]), got[j]), j
+    assert torch.equal(a.get_state(), b.get_state())
+    z = torch.stack([o[0] for o in outs])[:, :, :, 2]
+    assert float(z[11].min()) > 0.15 and int(torch.stack([o[3] for o in outs]).sum()) >= N    # they flew; every env was truncated
+    a.close(); b.close()
+
+
 @pytest.mark.parametrize("name", gc.WRAPPER_CASES)
 @pytest.mark.parametrize("precision", [_abi.F64, _abi.F32])
 def test_race_wrappers_golden(name, precision):

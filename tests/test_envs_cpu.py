@@ -118,9 +118,11 @@ def test_eval_driver_host_pieces(tmp_path):
     here = os.path.dirname(os.path.abspath(sim.__file__))
     cls = load_controller(os.path.join(here, "..", "user_controller", "HoverController.py"))
     assert cls(1).predict(None).tolist() == [1.5, 0.5, 2, 0]
-    row = sim._row((Command.FULLSTATE, [[1, 2, 3], [4, 5, 6], [7, 8, 9], 0.25, [0.1, 0.2, 0.3], 0.0]))
-    assert row.tolist() == [1, 2, 3, 4, 5, 6, 7, 8, 9, 0.25, 0.1, 0.2, 0.3]
-    assert sim._row(np.array([1.0, 2.0, 3.0, 0.5])).tolist() == [1, 2, 3] + [0] * 6 + [0.5, 0, 0, 0]
-    with pytest.raises(NotImplementedError):
-        sim._row((Command.TAKEOFF, [0.3, 2]))
+    # 16-float command rows (ADRP_ACT_MEL_CMD): [adrp_command, args..., 0 padding]
+    row = sim._row((Command.FULLSTATE, [[1, 2, 3], [4, 5, 6], [7, 8, 9], 0.25, [0.1, 0.2, 0.3], 0.5]))
+    assert row.tolist() == [1, 1, 2, 3, 4, 5, 6, 7, 8, 9, 0.25, 0.1, 0.2, 0.3, 0.5, 0]
+    assert sim._row(np.array([1.0, 2.0, 3.0, 0.5]), 40).tolist() == [1, 1, 2, 3] + [0] * 6 + [0.5, 0, 0, 0, 40, 0]
+    assert sim._row((Command.TAKEOFF, [0.3, 2])).tolist() == [2, 0.3, 2] + [0] * 13
+    assert sim._row((Command.GOTO, [[1, 2, 3], 0.1, 2.5, True])).tolist() == [9, 1, 2, 3, 0.1, 2.5, 1] + [0] * 9
+    assert sim._row((Command.NONE, [])).tolist() == [0] * 16
     assert abs(map2pi(3 * np.pi / 2) + np.pi / 2) < 1e-12

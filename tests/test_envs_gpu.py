@@ -3,7 +3,7 @@ reference's own classes produced -- the tests read like the reference's usage (e
 import numpy as np
 import pytest
 
-from gym_pybullet_adrp_b200 import configs
+from gym_pybullet_adrp_b200 import _abi, configs
 from gym_pybullet_adrp_b200.control import DSLPIDControl
 from gym_pybullet_adrp_b200.envs import CtrlAviary, HoverAviary, MultiHoverAviary, MultiRaceAviary, VelocityAviary
 from gym_pybullet_adrp_b200.utils.enums import ActionType, Command, DroneModel, Physics, RaceMode
@@ -103,8 +103,8 @@ def test_multi_race_aviary_matches_reference_run():
         np.testing.assert_array_equal(env.drones_eliminated, z["eliminated"][k])
         np.testing.assert_array_equal(env.current_gate, z["current_gate"][k])
         assert reward == 0 and terminated == bool(z["terminated"][k]) and truncated == bool(z["truncated"][k])
-    with pytest.raises(NotImplementedError, match="high-level commander"):
-        env.step([(Command.TAKEOFF, [0.3, 2])] * 2)                # the planner is not restated
+    obs, *_ = env.step([(Command.TAKEOFF, [0.3, 2])] * 2)          # the high-level commander runs on the device
+    assert np.isfinite(obs).all()
     env.close()
 
 
@@ -122,13 +122,57 @@ def test_multi_race_aviary_command_tuples_match_reference_run():
         assert gc.rel_err(obs, z["obs"][k]) < 1e-9, k
     obs_none, *_ = env.step([(Command.NONE, [])] * meta["M"])           # no new command: the last setpoint stays
     env.close()
-    env2 = MultiRaceAviary(rc, num_drones=meta["M"], physics=Physics.PYB, racemode=RaceMode.COMPARE, precision="fp64")
+    env2 = MultiRaceAviary(rc, num_drones=meta["M"], physics=Physics.PYB, racemode=RaceMode.COMPARE, precision="fp64",
+                           full_state_actions=True)
     env2.reset(draws=gc.place_draws(rc, z["draws"], meta["M"])[None])
     for k in range(60):
-        env2.step(a[k])                                                  # (M, 13) rows, same thing
+        env2.step(a[k])                                                  # (M, 13) FULLSTATE rows, same thing
     obs_rep, *_ = env2.step(a[59])
     np.testing.assert_array_equal(obs_none, obs_rep)
     env2.close()
+
+
+def _tuple_from_row(row):
+    """16-float command row -> (Command, args) as user_controller/HardCodedController.py:158-188 returns them."""
+    by_id = {v: k for k, v in _abi.CMD_ID.items()}
+    cmd = Command(by_id[int(row[0])])
+    g = row[1:]
+    if cmd == Command.FULLSTATE:
+        return cmd, [g[0:3].copy(), g[3:6].copy(), g[6:9].copy(), float(g[9]), g[10:13].copy(), float(g[13])]
+    n = {Command.NONE: 0, Command.TAKEOFF: 2, Command.LAND: 2, Command.NOTIFY: 1, Command.STOP: 1, Command.TAKEOFFYAW: 3,
+         Command.LANDYAW: 3, Command.TAKEOFFVEL: 3, Command.LANDVEL: 3}[cmd]
+    return cmd, [float(v) for v in g[:n]]
+
+
+def test_multi_race_aviary_runs_hardcoded_controller_commands():
+    """The command stream of the UNMODIFIED user_controller/HardCodedController.py (TAKEOFF [0.3, 2] -> FULLSTATE along its
+    spline -> NOTIFY -> LAND, recorded while it drove the reference's own env: tests/golden/make_golden_race.py --commander)
+    as (Command, args) tuples into the env mirror, and through the batched driver of scripts/sim.py: same observations as
+    the reference's run, all four gates passed by both drones, same episode time."""
+    from gym_pybullet_adrp_b200.scripts.sim import simulate
+    from gym_pybullet_adrp_b200.user_controller import BaseController
+    meta, z = gc.load("race_commander_hardcoded_gs")
+    rc = configs.load_config(meta["level"])
+    M, steps = meta["M"], meta["steps"]
+    env = MultiRaceAviary(rc, num_drones=M, physics=Physics.PYB, racemode=RaceMode.COMPARE, precision="fp64")
+    env.reset(draws=gc.place_draws(rc, z["draws"], M)[None])
+    for k in range(steps):
+        obs, reward, terminated, truncated, info = env.step([_tuple_from_row(z["actions"][k, i]) for i in range(M)])
+        assert gc.rel_err(obs, z["obs"][k]) < 1e-9, k
+        np.testing.assert_array_equal(env.current_gate, z["current_gate"][k])
+    assert terminated and env.current_gate.min() == 4 and env.drones_finished.all()
+    env.close()
+
+    class Replay(BaseController):                              # the recorded stream, one instance per run and drone
+        def predict(self, obs, reward=None, done=None, info=None, ep_time=None):
+            k = min(int(round(ep_time * rc["ctrl_freq"])), steps - 1)
+            return _tuple_from_row(z["actions"][k, self.drone_id])
+
+    rc2 = configs.load_config(meta["level"])
+    for key in ("random_gates_obstacles", "random_drone_state", "random_drone_inertia", "disturbances"):
+        assert not rc2.get(key), "getting_started has no randomisation: the runs of the batch equal the golden run"
+    stats = simulate(rc2, Replay, n_runs=3, n_drones=M, precision="fp64", return_stats=True)
+    assert stats["episode_times"] == [(steps - 1) / rc["ctrl_freq"]] * 3      # sim.py:79,104: time of the last step taken
 
 
 def test_wrapper_classes_match_reference_run():
