@@ -235,7 +235,7 @@ def test_flop_table_is_the_mechanical_count():
     rows = json.loads(out)
     sys.path.insert(0, root)
     import bench
-    key = {"c5": "C5:", "c4": "C4:", "c2": "C2:", "c3": "C3:", "c5m": "C5M:"}
+    key = {"c1": "C1:", "c5": "C5:", "c4": "C4:", "c2": "C2:", "c3": "C3:", "c5m": "C5M:"}
     for wl, (sub_f, sub_s, step_f, step_s) in bench.MECHANICAL_OPS.items():
         r = next(v for k, v in rows.items() if k.startswith(key[wl]))
         got = (r["per_substep_update"]["flops"], r["per_substep_update"]["sfu"], r["per_control_step"]["flops"], r["per_control_step"]["sfu"])
