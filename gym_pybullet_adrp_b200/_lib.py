@@ -145,7 +145,12 @@ class Handle:
         return s
 
     def step(self, action, noise=None):
-        """Device path: ``action`` is (or is copied to) a CUDA tensor; outputs are the handle's tensors."""
+        """Device path: ``action`` is (or is copied to) a CUDA tensor; outputs are the handle's tensors.
+
+        ALIASING: ``obs, reward, terminated, truncated, flags`` are the handle's PERSISTENT output tensors; the next ``step``
+        / ``reset`` overwrites them in place.  Rollout code that keeps a reference across steps (``obs_list.append(obs)``,
+        ``next_obs`` vs ``obs``) must ``clone()``; ``step_n(..., keep_outputs=True)`` and ``vec_env.TorchVecEnv`` return
+        fresh tensors."""
         a = self._dev(action, (self.N, self.M, self.A))
         nz = None if noise is None else self._dev(noise, (self.N, self.M, self.S, 7))
         self._check(self.lib.adrp_step(self._h, a.data_ptr(), None if nz is None else nz.data_ptr(),

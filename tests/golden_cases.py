@@ -56,6 +56,32 @@ def rel_err(a, b, floor=1.0):
     a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
     return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), floor)))
 
+# ---- fp32 product build vs a float64 / fp32-oracle run: BASELINE.json north_star's terms
+POS_TOL32, ANG_TOL32, REST_TOL32 = 1e-4, 1e-4, 2e-4       # metres, radians (absolute); every other column relative above 1
+MARGINS = {}                                              # test id -> worst (pos, ang, rest) seen: conftest writes them out
+
+
+def assert_fp32_north_star(o, g, layout, what):
+    """``o``: fp32 kernel observation rows (..., O); ``g``: the reference rows.  north_star: "the fp32 build must agree within
+    1e-4 m and 1e-4 rad" -- absolute on the position columns and on the (wrapped) Euler angles.  The remaining columns
+    (velocities, body rates, RPM, action buffer: not part of north_star's statement) keep the 2e-4 relative bound.
+    layout "ctrl": 20-float CtrlAviary rows (rpy at 7:10); "kin": rows starting [pos3, rpy3, vel3, ang_v3]."""
+    o, g = np.asarray(o, np.float64), np.asarray(g, np.float64)
+    a0 = 7 if layout == "ctrl" else 3
+    pos = float(np.abs(o[..., 0:3] - g[..., 0:3]).max())
+    d = np.abs(o[..., a0:a0 + 3] - g[..., a0:a0 + 3])
+    ang = float(np.minimum(d, 2 * np.pi - d).max())
+    keep = np.ones(o.shape[-1], bool)
+    keep[0:3] = keep[a0:a0 + 3] = False
+    rest = rel_err(o[..., keep], g[..., keep]) if keep.any() else 0.0
+    key = str(what[0]) if isinstance(what, tuple) else str(what)
+    w = MARGINS.get(key, (0.0, 0.0, 0.0))
+    MARGINS[key] = (max(w[0], pos), max(w[1], ang), max(w[2], rest))
+    assert pos < POS_TOL32, (what, "position", pos)
+    assert ang < ANG_TOL32, (what, "angle", ang)
+    assert rest < REST_TOL32, (what, "other columns (relative)", rest)
+
+
 FULLSTATE_CASES = ["race_fullstate_compare_gs"]          # (Command.FULLSTATE, args) tuples with vel / acc / yaw / rates
 COMMANDER_CASES = ["race_commander_hardcoded_gs", "race_commander_script_gs"]   # every Command through the high-level commander
 WRAPPER_CASES = ["race_wrappers_compare_gs"]             # DroneObservationWrapper(RewardWrapper(MultiRaceAviary))

@@ -48,7 +48,7 @@ def test_full_size_batch_is_K_independent_templates(wl):
         assert torch.equal(ff.view(N // K, K, M), fs.unsqueeze(0).expand(N // K, -1, -1))
         assert torch.equal(tf.view(N // K, K), ts.unsqueeze(0).expand(N // K, -1))
         oc = oracle.step(acts[k].astype(np.float64), nthreads=4)[0]
-        assert gc.rel_err(os_.cpu().numpy(), oc) < 2e-4, (wl, k, gc.rel_err(os_.cpu().numpy(), oc))
+        gc.assert_fp32_north_star(os_.cpu().numpy(), oc, "ctrl", (f"full_size_templates[{wl}]", k))   # 1e-4 m / 1e-4 rad
     assert full.launch_count >= steps and S >= 5
     full.close(); small.close(); oracle.close()
 
@@ -72,7 +72,7 @@ def test_full_size_hover_aviary_c2():
         assert torch.equal(tf.view(N // K, K), ts.unsqueeze(0).expand(N // K, -1))
         assert torch.equal(uf.view(N // K, K), us.unsqueeze(0).expand(N // K, -1))
         oc, rc, tc, uc, _ = oracle.step(acts[k].astype(np.float64), nthreads=4)
-        assert gc.rel_err(os_.cpu().numpy(), oc) < 2e-4, (k, gc.rel_err(os_.cpu().numpy(), oc))
+        gc.assert_fp32_north_star(os_.cpu().numpy(), oc, "kin", ("full_size_hover_c2", k))            # 1e-4 m / 1e-4 rad
         np.testing.assert_array_equal(us.cpu().numpy(), uc)
     full.close(); small.close(); oracle.close()
 

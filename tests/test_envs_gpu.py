@@ -196,25 +196,65 @@ def test_wrapper_classes_match_reference_run():
 
 
 def test_torch_vec_env_rollout():
-    """SB3-style rollout loop on device tensors: shapes, done bookkeeping, auto-reset keeps every env alive."""
+    """SB3-style rollout loop on device tensors: shapes, done bookkeeping, and SB3's episode-end contract -- obs[dones] is
+    the FIRST observation of the next episode, infos["terminal_observation"][dones] the last one of the finished episode."""
     import torch
     from gym_pybullet_adrp_b200.vec_env import TorchVecEnv
     N = 64
-    env = HoverAviary(physics=Physics.PYB, act=ActionType.RPM, num_envs=N, auto_reset=True)
+    with pytest.raises(ValueError, match="auto_reset=False"):
+        TorchVecEnv(HoverAviary(physics=Physics.PYB, act=ActionType.RPM, num_envs=N, auto_reset=True))
+    env = HoverAviary(physics=Physics.PYB, act=ActionType.RPM, num_envs=N, auto_reset=False)
     env.EPISODE_LEN_SEC = 1.0
     venv = TorchVecEnv(env)
-    obs = venv.reset()
-    assert obs.shape == (N, int(np.prod(env.observation_space.shape))) and obs.is_cuda
+    obs0 = venv.reset()
+    assert obs0.shape == (N, int(np.prod(env.observation_space.shape))) and obs0.is_cuda
     g = torch.Generator(device="cuda").manual_seed(0)
     finished = torch.zeros(N, dtype=torch.int64, device="cuda")
+    kept = []
     for k in range(80):
         actions = 0.2 * (2 * torch.rand((N,) + env.action_space.shape, device="cuda", generator=g) - 1)
         obs, rewards, dones, infos = venv.step(actions)
+        kept.append(obs)
         assert rewards.shape == (N,) and dones.shape == (N,) and dones.dtype == torch.bool
         finished += dones
         assert torch.all(infos["episode_length"][dones] > 0)
+        if bool(dones.any()):
+            # the reset observation: initial pose at rest (columns 0:12 of the very first observation)
+            assert torch.equal(obs[dones][:, :12], obs0[dones][:, :12])
+            term = infos["terminal_observation"][dones]
+            assert (term[:, :12] - obs0[dones][:, :12]).abs().max() > 1e-3     # the finished episode's last row is elsewhere
+            # the action buffer survives the reset, like the reference's (BaseRLAviary.py:66-67)
+            assert torch.equal(obs[dones][:, 12:], term[:, 12:])
+        assert torch.equal(obs[~dones], infos["terminal_observation"][~dones])
     assert int(finished.min()) >= 1 and torch.isfinite(obs).all()      # 80 steps at 30 Hz > 1 s episodes: everyone reset
     assert int(venv.episode_lengths.max()) <= 31
+    assert not torch.equal(kept[0], kept[1]) and kept[0].data_ptr() != kept[1].data_ptr()   # returned tensors are copies
+    venv.close()
+
+
+def test_torch_vec_env_race_shows_the_new_track_after_an_episode():
+    """Race env through TorchVecEnv: the observation returned for a finished env is the reset observation of its NEXT
+    episode -- nominal start poses seen against the re-randomised track."""
+    import torch
+    from gym_pybullet_adrp_b200.vec_env import TorchVecEnv
+    N, M = 48, 2
+    rc = configs.load_config("level3")
+    rc["episode_len_sec"] = 0.3
+    env = MultiRaceAviary(rc, num_drones=M, physics=Physics.PYB, racemode=RaceMode.COMPARE, num_envs=N, auto_reset=False, seed=3)
+    venv = TorchVecEnv(env, flatten=False)
+    obs0 = venv.reset()
+    init = torch.as_tensor(np.array([rc["init_states"][f"drone{i}"]["pos"] for i in range(M)]), dtype=obs0.dtype, device=obs0.device)
+    a = torch.zeros((N, M, 4), device="cuda")
+    a[..., 0:3] = init + torch.tensor([0.0, 0.0, 0.4], device="cuda")
+    seen = 0
+    for k in range(12):
+        obs, rewards, dones, infos = venv.step(a)
+        if bool(dones.any()):
+            seen += int(dones.sum())
+            assert torch.allclose(obs[dones][:, :, 0:3], init.expand(int(dones.sum()), M, 3), atol=1e-6)
+            assert (infos["terminal_observation"][dones][:, :, 2] > 0.08).all()          # they had climbed
+            assert (obs[dones][:, :, 48] == 0).all()                                      # current gate of the new episode
+    assert seen >= N
     venv.close()
 
 
