@@ -283,6 +283,38 @@ def test_host_path_matches_device_path():
     a_h.close(); b_h.close()
 
 
+def test_host_path_is_ordered_after_device_path_calls():
+    """adrp_step_host runs on the handle's own non-blocking streams: it must wait for reset / set_state / step work that the
+    caller enqueued on ITS stream before (an event recorded by every device-path entry point).  Staging is allocated by the
+    first call, so the later rounds have no implicit synchronisation from cudaMalloc to hide a missing dependency."""
+    import torch
+    N, M = 8192, 8
+    xyz = [[1.2 * (k % 3), 1.2 * (k // 3), 0.5 + 0.25 * (k % 4)] for k in range(M)]
+    cfg = _abi.make_config(num_envs=N, num_drones=M, physics=Physics.DYN_GND_DRAG_DW, pyb_freq=240, ctrl_freq=30,
+                           action_type=_abi.ACT_RPM_RAW, env_kind=_abi.ENV_CTRL, precision=_abi.F32, initial_xyzs=xyz)
+    h, ref = _handle(cfg), _handle(cfg)
+    rng = np.random.default_rng(8)
+    hover = float(np.sqrt(9.8 * 0.03454 / (4 * 3.16e-10)))
+    a = (hover * (1 + 0.01 * rng.uniform(-1, 1, (N, M, 4)))).astype(np.float32)
+    h.step_host(a)                                        # allocates the staging buffers and the private streams
+    base = ref.get_state().clone()
+    for k in range(6):
+        st = base.clone()
+        st[:, :, 2] += torch.as_tensor(rng.uniform(0.0, 1.0, (N, M)), dtype=st.dtype, device=st.device)
+        big = torch.randn(1 << 24, device=st.device).sin_().sum()      # keeps the caller's stream busy ahead of set_state
+        h.set_state(st)
+        if k % 2:
+            h.step(a)                                     # device-path step, then the host path right behind it
+            ref.set_state(st); ref.step(a)
+        else:
+            ref.set_state(st)
+        got = h.step_host(a)[0]
+        want = ref.step(a)[0].cpu().numpy()
+        np.testing.assert_array_equal(got, want)
+        assert torch.isfinite(big)
+    h.close(); ref.close()
+
+
 def test_auto_reset_and_truncation():
     cfg = _abi.make_config(num_envs=4, num_drones=1, physics=Physics.PYB, pyb_freq=240, ctrl_freq=30,
                            action_type=_abi.ACT_RPM, env_kind=_abi.ENV_HOVER, precision=_abi.F32, auto_reset=True,
