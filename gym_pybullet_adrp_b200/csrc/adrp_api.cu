@@ -159,6 +159,15 @@ void derive_params(const adrp_config& c, KParams<T>& P)
         P.dwf_l2c = (T)(c0 > 0 ? log2(c0) : -1e30);
         P.half_dt = (T)(0.5 / c.pyb_freq); P.qr4 = (T)(0.25 * p.prop_radius);
     }
+    {
+        const double dt = 1.0 / c.pyb_freq, arm = c.drone_model == ADRP_CF2P ? p.arm : p.arm / sqrt(2.0);
+        P.k_tx = (T)(dt / p.ixx * arm); P.k_ty = (T)(dt / p.iyy * arm);
+        P.k_tz = (T)((c.drone_model == ADRP_RACE ? -1.0 : 1.0) * dt / p.izz);          // BaseAviary.py:850-852
+        P.k_gx = (T)(dt / p.ixx * (p.izz - p.iyy)); P.k_gy = (T)(dt / p.iyy * (p.ixx - p.izz)); P.k_gz = (T)(dt / p.izz * (p.iyy - p.ixx));
+        P.k_m = (T)(dt / p.mass); P.k_grav = (T)(dt * c.g);                            // GRAVITY / M = g
+        P.k_drag_xy = (T)(dt / p.mass * p.drag_coeff_xy * (2.0 * M_PI / 60.0));
+        P.k_drag_z = (T)(dt / p.mass * p.drag_coeff_z * (2.0 * M_PI / 60.0));
+    }
     P.speed_limit = (T)(0.03 * p.max_speed_kmh * (1000.0 / 3600.0));
     for (int k = 0; k < 4; ++k) { P.prop_x[k] = (T)p.prop_x[k]; P.prop_y[k] = (T)p.prop_y[k]; }
     P.pyb_mass = (T)p.pyb_mass; P.pyb_jx = (T)p.pyb_ixx; P.pyb_jy = (T)p.pyb_iyy; P.pyb_jz = (T)p.pyb_izz;

@@ -119,7 +119,7 @@ cudaError_t Launch<T>::step(const KParams<T>& P, const KBuffers<T>& b, const T* 
     // compiled in their own translation units (step_special)
     if constexpr (M<T>::fast) {
         static const bool generic = [] { const char* e = getenv("ADRP_STEP_GENERIC"); return e && e[0] == '1'; }();   // diagnostic
-        if (!pid && !generic) {
+        if (!pid && !generic && P.drone_model != ADRP_CF2P) {      // (the instances have the X prop layout compiled in)
             StepFnF32 f = nullptr;
             const bool ctrl = P.env_kind == ADRP_ENV_CTRL;
             constexpr int ALL = ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW;

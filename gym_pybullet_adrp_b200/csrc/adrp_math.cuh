@@ -205,6 +205,23 @@ template <typename T> __device__ __forceinline__ Mat3<T> rotmat_loop(const Q4<T>
     return {T(1) - (yy + zz), xy - wz, xz + wy, xy + wz, T(1) - (xx + zz), yz - wx, xz - wy, yz + wx, T(1) - (xx + yy)};
 }
 
+// Rotation matrix of a UNIT quaternion (no division by |q|^2): the product build normalises the pose when it loads it and
+// once per control step afterwards; inside the substep loop the polynomial cos / sinc updates keep |q| = 1 to ~1e-7 per
+// substep, which is the rounding level of the matrix entries themselves.
+template <typename T> __device__ __forceinline__ Mat3<T> rotmat_unit(const Q4<T>& q)
+{
+    const T xs = q.x + q.x, ys = q.y + q.y, zs = q.z + q.z;
+    const T wx = q.w * xs, wy = q.w * ys, wz = q.w * zs;
+    const T xx = q.x * xs, xy = q.x * ys, xz = q.x * zs;
+    const T yy = q.y * ys, yz = q.y * zs, zz = q.z * zs;
+    return {T(1) - (yy + zz), xy - wz, xz + wy, xy + wz, T(1) - (xx + zz), yz - wx, xz - wy, yz + wx, T(1) - (xx + yy)};
+}
+template <typename T> __device__ __forceinline__ Q4<T> unit_quat_loop(const Q4<T>& q)
+{
+    const T inv = M<T>::frsqrt(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
+    return {q.x * inv, q.y * inv, q.z * inv, q.w * inv};
+}
+
 // canon_quat for the substep loop (normalisation through the build's frsqrt)
 template <typename T> __device__ __forceinline__ Q4<T> canon_quat_loop(const Q4<T>& q);
 

@@ -34,6 +34,11 @@ struct KParams {
     // fp32 product build, downwash in base-2 form: term = 2^(dwf_l2c - dxy^2 / (dwf_a dz + dwf_b)^2) / dz^2 with
     // dwf_l2c = log2(dw1 (prop_radius/4)^2) and (dwf_a, dwf_b) = (dw2, dw3) / sqrt(log2(e) / 2)
     T dwf_a, dwf_b, dwf_l2c, half_dt, qr4;
+    // fp32 product build, explicit model (dyn_substep_fast), folded on the host in double: body-rate update
+    //   rt += k_t * (signed prop-force sums) - k_g * (products of the other two rates)
+    // with k_t = dt J^-1 arm (z: dt Jz^-1, sign of the RACE model folded in), k_g = dt J^-1 (J_next - J_prev);
+    // velocity update v = v * (1 - k_drag * sum_rpm) + (dt / m) thrust * R[:, 2] - (0, 0, dt g)
+    T k_tx, k_ty, k_tz, k_gx, k_gy, k_gz, k_m, k_grav, k_drag_xy, k_drag_z;
     T prop_x[4], prop_y[4], pyb_mass, pyb_jx, pyb_jy, pyb_jz, lin_damp, ang_damp, coll_r, coll_h;
     T dt, ctrl_dt, g;
     T pid_gravity, pid_kf;                // DSLPIDControl's own URDF constants (control/BaseControl.py:35-39)

@@ -114,10 +114,9 @@ __device__ __forceinline__ void downwash_pair_sym(const KParams<T>& P, T dx, T d
     const T rz = M<T>::rcp(az);
     const T ib = M<T>::rcp(P.dwf_a * az + P.dwf_b);
     const T e = M<T>::fexp2(P.dwf_l2c - (dxy2 * ib) * ib);
-    const T term = (e * rz) * rz;
-    const bool near = dxy2 < T(100);
-    mine = (near && dz > T(0)) ? term : T(0);
-    theirs = (near && dz < T(0)) ? term : T(0);
+    const T term = dxy2 < T(100) ? (e * rz) * rz : T(0);
+    mine = dz > T(0) ? term : T(0);
+    theirs = dz < T(0) ? term : T(0);
 }
 
 template <typename T, int MP>
@@ -245,6 +244,49 @@ __device__ __forceinline__ void dyn_substep(const KParams<T>& P, Drone<T>& d, co
     }
     d.q = canon_quat(d.q);
     d.w = mul(R, d.rt);                                                          // :875-879 (pre-update R)
+}
+
+// Explicit model, fp32 product build: the same update with the constants folded on the host (KParams::k_*): the body-rate
+// derivative written per axis -- J^-1 (tau - w x J w) = J^-1 tau - J^-1 (J_c - J_b) w_b w_c for a diagonal inertia -- and the
+// drag force -c sum_rpm v folded into a per-axis gain on the old velocity (axy, az: 1 - dt/m c sum_rpm, the caller keeps the
+// value for last_clipped_action's RPMs of this substep).
+// DM: prop layout at compile time -- 0: X (CF2X, RACE), 1: + (CF2P), -1: read from the params.
+template <typename T, int DM = -1>
+__device__ __forceinline__ void dyn_substep_fast(const KParams<T>& P, Drone<T>& d, const Mat3<T>& R, const T f[4],
+                                                 const T tq[4], T extra_z, T axy, T az, bool last)
+{
+    const T kt = ((f[0] + f[1]) + (f[2] + f[3]) + extra_z) * P.k_m;                // dt / m * thrust (:847-848,:862-864)
+    const T zt = (tq[1] - tq[0]) + (tq[3] - tq[2]);                              // :852 (RACE: sign in k_tz)
+    T sx, sy;
+    const bool plus = DM >= 0 ? DM == 1 : P.drone_model == ADRP_CF2P;
+    if (plus) { sx = f[1] - f[3]; sy = f[2] - f[0]; }                            // :857-858
+    else { sx = (f[0] + f[1]) - (f[2] + f[3]); sy = (f[1] + f[2]) - (f[0] + f[3]); }   // :854-855
+    const T px = d.rt.x, qy = d.rt.y, rz = d.rt.z;
+    d.rt = {px + P.k_tx * sx - P.k_gx * (qy * rz), qy + P.k_ty * sy - P.k_gy * (rz * px), rz + P.k_tz * zt - P.k_gz * (px * qy)};   // :860-861,:865
+    d.v = {d.v.x * axy + kt * R.m02, d.v.y * axy + kt * R.m12, d.v.z * az + kt * R.m22 - P.k_grav};
+    d.p = {d.p.x + P.dt * d.v.x, d.p.y + P.dt * d.v.y, d.p.z + P.dt * d.v.z};    // :866
+    // _integrateQ (:883-896) with the NEW rates: cos(th) and sin(th)/|w| = (dt/2) sinc(th) as polynomials in th^2
+    const T nx = d.rt.x, ny = d.rt.y, nz = d.rt.z;
+    const T wn2 = nx * nx + ny * ny + nz * nz;
+    const Q4<T> q = d.q;
+    const T z = wn2 * (P.half_dt * P.half_dt);
+    T c, k;
+    if (z <= T(0.6168502750680849)) {
+        M<T>::cos_sinc_sq(z, &c, &k);
+        k *= P.half_dt;
+    } else {
+        const T wn = M<T>::fsqrt(wn2);
+        T s;
+        M<T>::sincos_small(wn * P.half_dt, &s, &c);
+        k = s * M<T>::rcp(wn);
+    }
+    d.q = {c * q.x + k * (nz * q.y - ny * q.z + nx * q.w), c * q.y + k * (-nz * q.x + nx * q.z + ny * q.w),
+           c * q.z + k * (ny * q.x - nx * q.y + nz * q.w), c * q.w + k * (-nx * q.x - ny * q.y - nz * q.z)};
+    if (last) {                                            // world rates: R of the pose BEFORE this update (:875-879)
+        Q4<T> ql = q;
+        opaque(ql.x); opaque(ql.y); opaque(ql.z); opaque(ql.w);
+        d.w = mul(rotmat_unit(ql), d.rt);
+    }
 }
 
 // Base-frame angular velocity for pyb_substep's fast path, and back (R: rotmat_loop of the pose at that moment).

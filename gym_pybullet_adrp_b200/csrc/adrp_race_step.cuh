@@ -222,7 +222,8 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
     // fast build: one rotation matrix per substep, computed right after the pose update and shared by the controller
     // (Euler angles, firmware attitude error) and the next substep's force models; the controller's schedule bits of
     // the whole control step fetched once
-    Mat3<T> R = rotmat_loop(d.q);
+    if (M<T>::fast) d.q = unit_quat_loop(d.q);                // unit pose inside the loop (rotmat_unit, adrp_math.cuh)
+    Mat3<T> R = M<T>::fast ? rotmat_unit(d.q) : rotmat_loop(d.q);
     const MelWindow win = M<T>::fast ? mel_schedule_window(RP, rb.lut, m.tick, P.S) : MelWindow{0u, false};
     // product build, Bullet free body: the angular velocity stays in the base frame for the whole control step
     const bool body_rates = M<T>::fast && !(phy & ADRP_PHY_DYN);
@@ -290,7 +291,7 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
             const V3<T> fw = QUIET ? fext : V3<T>{fext.x + nz[0], fext.y + nz[1], fext.z + nz[2]};   // drag + wind (:532-544)
             pyb_substep(P, phy, d, wl, R, fz, tb, fw, body[0], body[1], body[2], body[3]);
         }
-        if (M<T>::fast) R = rotmat_loop(d.q);
+        if (M<T>::fast) R = rotmat_unit(d.q);
         // controller round trip (:231-254)
         if (eliminated) {
 #pragma unroll

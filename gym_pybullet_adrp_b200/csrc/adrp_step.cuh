@@ -101,7 +101,8 @@ __device__ __forceinline__ int group_or(int v, int Mpad)
 // a lot (5 stores vs. the action-buffer copy), and the registers of the larger one count for the whole kernel.
 // MULTI: adrp_step_n instances -- P.K control steps per launch (the single-step instances compile the loop away and are
 // the code they were before it existed: the loop costs the all-forces instances 12 registers, i.e. one resident block).
-template <typename T, int PHY_CT, int ACTC, int MP, int ENVK = -1, bool MULTI = false>
+// DM: prop layout compiled in (0: X -- CF2X / RACE; -1: drone model read from the params).
+template <typename T, int PHY_CT, int ACTC, int MP, int ENVK = -1, bool MULTI = false, int DM = -1>
 __global__ void __launch_bounds__(kStepBlock, ADRP_STEP_MINB)
 step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* __restrict__ action,
             T* __restrict__ obs, T* __restrict__ reward, uint8_t* __restrict__ terminated,
@@ -200,9 +201,20 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
     // product build, Bullet free body: the angular velocity stays in the base frame for the whole control step
     const bool body_rates = M<T>::fast && !(phy & ADRP_PHY_DYN);
     V3<T> wl = {T(0), T(0), T(0)};
-    if (body_rates) wl = pyb_body_rates(rotmat_loop(d.q), d.w);
+    // product build: unit pose inside the loop (see rotmat_unit); explicit model: drag as a gain on the old velocity
+    if (M<T>::fast) d.q = unit_quat_loop(d.q);
+    if (body_rates) wl = pyb_body_rates(rotmat_unit(d.q), d.w);
+    const bool dyn_fast = M<T>::fast && (phy & ADRP_PHY_DYN);
+    T axy = T(1), az = T(1), axy_cur = T(1), az_cur = T(1);
+    if (dyn_fast) {
+        if (phy & ADRP_PHY_DRAG) {                         // last_clipped_action: the previous step's RPM during the first substep
+            const T sp = (d.last_rpm[0] + d.last_rpm[1]) + (d.last_rpm[2] + d.last_rpm[3]), sc = (rpm[0] + rpm[1]) + (rpm[2] + rpm[3]);
+            axy = T(1) - P.k_drag_xy * sp; az = T(1) - P.k_drag_z * sp;
+            axy_cur = T(1) - P.k_drag_xy * sc; az_cur = T(1) - P.k_drag_z * sc;
+        }
+    }
     for (int s = 0; s < P.S; ++s) {
-        const Mat3<T> R = rotmat_loop(d.q);
+        const Mat3<T> R = M<T>::fast ? rotmat_unit(d.q) : rotmat_loop(d.q);
         T f[4] = {f0[0], f0[1], f0[2], f0[3]};
         if (phy & ADRP_PHY_GND) {
             if (M<T>::fast) {
@@ -215,13 +227,16 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
             }
         }
         V3<T> fext = {T(0), T(0), T(0)};
-        if (phy & ADRP_PHY_DRAG) {                         // last_clipped_action: the previous step's RPM during the first substep (:363,:376)
+        if ((phy & ADRP_PHY_DRAG) && !dyn_fast) {          // last_clipped_action: the previous step's RPM during the first substep (:363,:376)
             if (M<T>::fast) fext = drag_force_sum(P, d, s == 0 ? drag_sum_prev : drag_sum_cur);
             else fext = drag_force(P, d);
         }
         T dw = T(0);
         if (phy & ADRP_PHY_DW) dw = downwash<T, MP>(P, d.p, lane_base, valid);
-        if (phy & ADRP_PHY_DYN) {
+        if (dyn_fast) {
+            dyn_substep_fast<T, DM>(P, d, R, f, tq, dw, axy, az, s == P.S - 1);
+            axy = axy_cur; az = az_cur;
+        } else if (phy & ADRP_PHY_DYN) {
             dyn_substep(P, d, R, f, tq, dw, fext, s == P.S - 1);
         } else {
             const T fz = (f[0] + f[1] + f[2] + f[3]) + dw;
@@ -241,7 +256,7 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
     }
     if (ks == K - 1) pdl_launch_dependents();          // the next launch's blocks may be scheduled while this one writes out
     if (M<T>::fast) d.q = canon_quat_loop(d.q);          // once per control step in the product build (adrp_physics.cuh)
-    if (body_rates) d.w = pyb_world_rates(rotmat_loop(d.q), wl);
+    if (body_rates) d.w = pyb_world_rates(rotmat_unit(d.q), wl);     // (d.q: normalised on the line above)
 
     // ---- observation (CtrlAviary.py:106-117; BaseRLAviary.py:284-322).  CtrlAviary has no flag that depends on the
     // Euler angles, so the product build may use the loop's polynomial atan2 there (1 ulp); the RL aviaries threshold

@@ -11,14 +11,15 @@ template <int PHY, int ENVK, bool MULTI>
 StepFnF32 step_special_mp(int mpad)
 {
     switch (mpad) {
-        case 1: return step_kernel<float, PHY, 0, 1, ENVK, MULTI>;
-        case 2: return step_kernel<float, PHY, 0, 2, ENVK, MULTI>;
-        case 4: return step_kernel<float, PHY, 0, 4, ENVK, MULTI>;
-        case 8: return step_kernel<float, PHY, 0, 8, ENVK, MULTI>;
+        case 1: return step_kernel<float, PHY, 0, 1, ENVK, MULTI, 0>;
+        case 2: return step_kernel<float, PHY, 0, 2, ENVK, MULTI, 0>;
+        case 4: return step_kernel<float, PHY, 0, 4, ENVK, MULTI, 0>;
+        case 8: return step_kernel<float, PHY, 0, 8, ENVK, MULTI, 0>;
         default: return nullptr;
     }
 }
 
+// (instances for the X prop layout -- CF2X, RACE; a CF2P handle runs the generic kernel)
 // ctrl: CtrlAviary-kind env; rl_too: this mask also has RL-aviary instances (the plain masks: learn.py / HoverAviary shapes)
 template <int PHY, bool MULTI>
 StepFnF32 step_special_impl(int mpad, bool ctrl)
