@@ -408,7 +408,10 @@ def measure(wl, N, args, *, rank=0, world=1, local=0, dist=None, steps=None, min
         h.step(acts_dev[k % pool])
     e1.record()
     torch.cuda.synchronize()
-    est_ms = max(e0.elapsed_time(e1), 1e-3)
+    est = torch.tensor([max(e0.elapsed_time(e1), 1e-3)], device=h.device, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(est, op=dist.ReduceOp.MAX)        # every rank must time the SAME number of blocks (the block times
+    est_ms = float(est.item())                            # are all-reduced element by element below)
     repeats = int(min(max_repeats, max(25, np.ceil(min_time_s * 1e3 / est_ms))))
     restart_every = max(1, 200 // K)                      # blocks between two re-seatings of the formation
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(repeats)]
@@ -560,7 +563,8 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        import datetime
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(seconds=180))
     wl = args.workload
     M = WORKLOADS[wl][1]
     if args.scaling == "strong":

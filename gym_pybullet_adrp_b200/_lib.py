@@ -196,8 +196,11 @@ class Handle:
         a = np.ascontiguousarray(action, self.np_dtype).reshape(self.N, self.M, self.A)
         if not hasattr(self, "_hbuf"):
             # the observation buffer is page-locked, so the library DMAs into it directly (no staging copy)
-            self._hbuf = (self.pinned_empty((self.N, self.M, self.O)), np.empty(self.N, self.np_dtype),
-                          np.empty(self.N, np.uint8), np.empty(self.N, np.uint8), np.empty((self.N, self.M), np.uint8))
+            # every output buffer is page-locked, so the library DMAs into them directly (no staging copy)
+            torch = _torch()
+            u8 = lambda shape: torch.empty(tuple(shape), dtype=torch.uint8, pin_memory=True).numpy()   # noqa: E731
+            self._hbuf = (self.pinned_empty((self.N, self.M, self.O)), self.pinned_empty((self.N,)),
+                          u8((self.N,)), u8((self.N,)), u8((self.N, self.M)))
         o, r, te, tr, fl = self._hbuf
         self._check(self.lib.adrp_step_host(self._h, a.ctypes.data, o.ctypes.data, r.ctypes.data, te.ctypes.data,
                                             tr.ctypes.data, fl.ctypes.data), "adrp_step_host")
