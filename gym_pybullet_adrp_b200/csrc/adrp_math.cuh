@@ -252,12 +252,19 @@ template <typename T> __device__ __forceinline__ V3<T> euler_rpy_loop(const Q4<T
 
 // euler_rpy for the fast build's substep loop, read off R = rotmat_loop(q) (already there for the force models):
 // m21 : m22 = 2(yz + wx) : (w^2 - x^2 - y^2 + z^2), -m20 = sarg / |q|^2, m10 : m00 = 2(xy + wz) : (w^2 + x^2 - y^2 - z^2).
+// The gimbal-lock branches (|pitch| within 0.26 degrees of 90) out of line: they call libm's atan2 and would sit, never
+// executed, inside the substep loop, whose footprint in the instruction cache is what the loop's `no_instruction` stalls
+// pay for (C5M: 0.22 per issued instruction with 975 static instructions in the loop).  Arguments and result by value, so
+// that no live state has its address taken.
+template <typename T> __device__ __noinline__ T euler_gimbal_yaw(T qx, T qy, T sarg)
+{
+    return sarg < T(0) ? T(2) * M<T>::atan2(qx, -qy) : T(2) * M<T>::atan2(-qx, qy);
+}
 template <typename T> __device__ __forceinline__ V3<T> euler_rpy_rot(const Q4<T>& q, const Mat3<T>& R)
 {
     const T sarg = -R.m20;
     const T HALF_PI = T(1.5707963267948966);
-    if (sarg <= T(-0.99999)) return {T(0), -HALF_PI, T(2) * M<T>::atan2(q.x, -q.y)};
-    if (sarg >= T(0.99999)) return {T(0), HALF_PI, T(2) * M<T>::atan2(-q.x, q.y)};
+    if (M<T>::abs(sarg) >= T(0.99999)) return {T(0), sarg < T(0) ? -HALF_PI : HALF_PI, euler_gimbal_yaw<T>(q.x, q.y, sarg)};
     return {M<T>::atan2_loop(R.m21, R.m22), M<T>::asin_loop(sarg), M<T>::atan2_loop(R.m10, R.m00)};
 }
 

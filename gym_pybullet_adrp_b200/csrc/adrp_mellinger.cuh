@@ -201,13 +201,18 @@ __device__ __forceinline__ MelWindow mel_schedule_window(const RaceParams<T>& RP
     return w;
 }
 
+// (beyond the table: the float64 test itself, out of line -- its double-precision arithmetic would otherwise sit in the substep loop)
+static __device__ __noinline__ bool mel_schedule_fires_f64(int tick, int last)
+{
+    return (double)tick / 500.0 - (double)last / 500.0 > 0.002;
+}
 template <typename T>
 __device__ __forceinline__ bool mel_schedule_fires(const RaceParams<T>& RP, const uint32_t* __restrict__ lut, int tick, int last)
 {
     const int gap = tick - last;
     if (gap != 1) return gap > 1;
     if (tick < RP.lut_ticks) return (__ldg(lut + (tick >> 5)) >> (tick & 31)) & 1u;
-    return (double)tick / 500.0 - (double)last / 500.0 > 0.002;
+    return mel_schedule_fires_f64(tick, last);
 }
 
 // One 500 Hz tick.  p, q, v: the drone's state AFTER this substep's physics.  noise4: motor thrust noise (N).

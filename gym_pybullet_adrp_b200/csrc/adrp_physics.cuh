@@ -293,6 +293,26 @@ __device__ __forceinline__ void dyn_substep_fast(const KParams<T>& P, Drone<T>& 
 template <typename T> __device__ __forceinline__ V3<T> pyb_body_rates(const Mat3<T>& R, const V3<T>& w) { return mulT(R, w); }
 template <typename T> __device__ __forceinline__ V3<T> pyb_world_rates(const Mat3<T>& R, const V3<T>& wl) { return mul(R, wl); }
 
+// Declared plane response of the Bullet free body once the collision cylinder has sunk `pen` into z = 0: project back,
+// cancel the approaching normal velocity, Coulomb friction mu = 0.5 on the tangential part.  Product build: out of line
+// (by value; returns the new p.z, v.x, v.y, v.z) -- a drone in flight never executes it, and its IEEE division / square
+// root would otherwise sit inside the substep loop.
+template <typename T> struct PlaneHit { T pz, vx, vy, vz; };
+template <typename T> __device__ __noinline__ PlaneHit<T> plane_response(T pen, T pz, T vx, T vy, T vz)
+{
+    PlaneHit<T> r = {pz + pen, vx, vy, vz};
+    if (vz < T(0)) {
+        const T jn = -vz;
+        r.vz = T(0);
+        const T vt = M<T>::sqrt(vx * vx + vy * vy);
+        if (vt > T(0)) {
+            const T kf = M<T>::fmax(T(0), T(1) - T(0.5) * jn / vt);
+            r.vx = vx * kf; r.vy = vy * kf;
+        }
+    }
+    return r;
+}
+
 // Bullet free body.  fz: total body-z force at the props + downwash; tb: body torque; fext: world force;
 // m, j*: the body's mass and principal inertia (per drone in the race env, changeDynamics).
 // wl (fast build only): the angular velocity in the BASE frame, carried by the caller across the substeps of one
@@ -374,7 +394,12 @@ __device__ __forceinline__ void pyb_substep(const KParams<T>& P, int phy, Drone<
         const T s2 = T(1) - r22 * r22;
         const T hz = T(0.5) * P.coll_h * M<T>::abs(r22) + P.coll_r * M<T>::fsqrt(M<T>::fmax(s2, T(0)));
         const T pen = hz - d.p.z;
-        if (pen > T(0)) {
+        if (M<T>::fast) {
+            if (pen > T(0)) {
+                const PlaneHit<T> r = plane_response<T>(pen, d.p.z, d.v.x, d.v.y, d.v.z);
+                d.p.z = r.pz; d.v.x = r.vx; d.v.y = r.vy; d.v.z = r.vz;
+            }
+        } else if (pen > T(0)) {
             d.p.z += pen;
             if (d.v.z < T(0)) {
                 const T jn = -d.v.z;
