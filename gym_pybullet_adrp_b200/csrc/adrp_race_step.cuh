@@ -264,9 +264,9 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
         }
         // _apply_physics(self.rpms, self.prev_rpms) (:510-548): forces from the substep-start state
         if (!M<T>::fast) R = rotmat_loop(d.q);
-        T f[4], tq[4];
+        T f[4], r2[4];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) { f[k] = mul_rn(m.rpms[k] * m.rpms[k], P.kf); tq[k] = mul_rn(m.rpms[k] * m.rpms[k], P.km); }
+        for (int k = 0; k < 4; ++k) { r2[k] = m.rpms[k] * m.rpms[k]; f[k] = mul_rn(r2[k], P.kf); }
         if (phy & ADRP_PHY_GND) {
             if (M<T>::fast) {
                 ground_effect_total(P, d, R, f, f);
@@ -282,12 +282,19 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
         T dw = T(0);
         if (phy & ADRP_PHY_DW) dw = downwash<T, MP>(P, d.p, lane_base, valid);
         if (phy & ADRP_PHY_DYN) {
+            T tq[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) tq[k] = mul_rn(r2[k], P.km);
             dyn_substep(P, d, R, f, tq, dw, fext, s == P.S - 1);
         } else {
+            // yaw torque +t0 - t1 + t2 - t3 (BaseAviary.py:703): the product build multiplies the signed sum of squares once
+            // (equal commands still cancel exactly); the parity build keeps the reference's four products
+            const T tz = M<T>::fast ? mul_rn((r2[0] - r2[1]) + (r2[2] - r2[3]), P.km)
+                                    : mul_rn(r2[0], P.km) - mul_rn(r2[1], P.km) + mul_rn(r2[2], P.km) - mul_rn(r2[3], P.km);
             const T fz = dw + f[0] + f[1] + f[2] + f[3];
             const V3<T> tb = {mul_rn(P.prop_y[0], f[0]) + mul_rn(P.prop_y[1], f[1]) + mul_rn(P.prop_y[2], f[2]) + mul_rn(P.prop_y[3], f[3]),
                               mul_rn(-P.prop_x[0], f[0]) + mul_rn(-P.prop_x[1], f[1]) + mul_rn(-P.prop_x[2], f[2]) + mul_rn(-P.prop_x[3], f[3]),
-                              tq[0] - tq[1] + tq[2] - tq[3]};                            // BaseAviary.py:703
+                              tz};
             const V3<T> fw = QUIET ? fext : V3<T>{fext.x + nz[0], fext.y + nz[1], fext.z + nz[2]};   // drag + wind (:532-544)
             pyb_substep(P, phy, d, wl, R, fz, tb, fw, body[0], body[1], body[2], body[3]);
         }
