@@ -12,7 +12,8 @@ import numpy as np
 from . import _abi
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG_DIR, "libadrp_b200.so")
+# ADRP_LIB_PATH: another build of the same library (tools/variant_build.sh: launch-bound / block-size experiments)
+LIB_PATH = os.environ.get("ADRP_LIB_PATH") or os.path.join(PKG_DIR, "libadrp_b200.so")
 
 EXPORTS = ["adrp_create", "adrp_destroy", "adrp_obs_dim", "adrp_action_dim", "adrp_noise_dim",
            "adrp_reset_draws_dim", "adrp_substeps", "adrp_reset", "adrp_set_state", "adrp_get_state",

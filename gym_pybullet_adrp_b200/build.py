@@ -19,6 +19,7 @@ OUT = os.path.join(PKG_DIR, "libadrp_b200.so")
 SOURCES = {"adrp_api.cu": [], "adrp_kernels_f32.cu": [], "adrp_race_f32_phy16.cu": [], "adrp_race_f32_phy30.cu": [],
            "adrp_step_f32_plain.cu": [], "adrp_step_f32_forces.cu": [],
            "adrp_race_f32_phy16_multi.cu": [], "adrp_race_f32_phy30_multi.cu": [],
+           "adrp_race_f32_phy16_dense.cu": [], "adrp_race_f32_phy30_dense.cu": [],
            "adrp_step_f32_plain_multi.cu": [], "adrp_step_f32_forces_multi.cu": [],
            "adrp_kernels_f64.cu": ["-fmad=false"]}
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

@@ -32,6 +32,7 @@ using RaceStepFnF32 = void (*)(KParams<float>, RaceParams<float>, KBuffers<float
                                float*, float*, uint8_t*, uint8_t*, uint8_t*);
 template <int PHY> RaceStepFnF32 race_step_special(int mpad, bool quiet);
 template <int PHY> RaceStepFnF32 race_step_special_multi(int mpad, bool quiet);   // adrp_step_n: K control steps per launch
+template <int PHY> RaceStepFnF32 race_step_special_dense(int mpad, bool quiet, bool multi);   // 128-register instances (multi-wave grids)
 
 // Likewise for step_kernel (RPM-type actions): the plain masks (Physics.DYN = 1, Physics.PYB = 16; adrp_step_f32_plain.cu) and the
 // all-forces masks (DYN + GND + DRAG + DW = 15, Physics.PYB_GND_DRAG_DW = 30; adrp_step_f32_forces.cu), 1 / 2 / 4 / 8 lanes per env.

@@ -173,7 +173,7 @@ using RaceStepFn = void (*)(KParams<T>, RaceParams<T>, KBuffers<T>, RaceBuffers<
 // then runs the instance without the wind / motor-noise terms; phy: the physics mask, for which the product build has
 // instances in their own translation units (race_step_special).
 template <typename T>
-inline RaceStepFn<T> race_step_fn(int mpad, int action_type, bool quiet, int phy, bool multi = false)
+inline RaceStepFn<T> race_step_fn(int mpad, int action_type, bool quiet, int phy, bool multi = false, bool dense = false)
 {
     // (Command, args) actions: scripted controllers -- 13-float FULLSTATE rows, or 16-float rows of any command
     if (action_type == ADRP_ACT_MEL_FULL) return multi ? race_step_kernel<T, 0, 1, false, -1, true> : race_step_kernel<T, 0, 1, false, -1>;
@@ -181,6 +181,11 @@ inline RaceStepFn<T> race_step_fn(int mpad, int action_type, bool quiet, int phy
     if constexpr (M<T>::fast) {
         RaceStepFn<T> f = nullptr;
         constexpr int ALL = ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW | ADRP_PHY_GROUND;
+        if (action_type == ADRP_ACT_MEL && dense) {            // grids longer than one wave: the 128-register instances
+            if (phy == ADRP_PHY_GROUND) f = race_step_special_dense<ADRP_PHY_GROUND>(mpad, quiet, multi);
+            if (phy == ALL) f = race_step_special_dense<ALL>(mpad, quiet, multi);
+            if (f) return f;
+        }
         if (phy == ADRP_PHY_GROUND) f = multi ? race_step_special_multi<ADRP_PHY_GROUND>(mpad, quiet) : race_step_special<ADRP_PHY_GROUND>(mpad, quiet);
         if (phy == ALL) f = multi ? race_step_special_multi<ALL>(mpad, quiet) : race_step_special<ALL>(mpad, quiet);
         if (f) return f;
@@ -204,8 +209,8 @@ cudaError_t Launch<T>::race_prepare(const RaceParams<T>& RP, const KParams<T>& P
     const size_t bytes = race_smem_bytes(P, RP);
     if (bytes <= 48 * 1024) return cudaSuccess;
     cudaError_t e = cudaSuccess;
-    for (int v = 0; v < 4 && e == cudaSuccess; ++v)
-        e = cudaFuncSetAttribute(race_step_fn<T>(P.Mpad, P.action_type, (v & 1) != 0, P.physics, (v & 2) != 0), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)race_smem_bytes(P, RP, kRaceBlock));
+    for (int v = 0; v < 8 && e == cudaSuccess; ++v)
+        e = cudaFuncSetAttribute(race_step_fn<T>(P.Mpad, P.action_type, (v & 1) != 0, P.physics, (v & 2) != 0, (v & 4) != 0), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)race_smem_bytes(P, RP, kRaceBlock));
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(race_reset_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
 }
@@ -223,8 +228,17 @@ cudaError_t Launch<T>::race_step(const KParams<T>& P, const RaceParams<T>& RP, c
                                  const T* action, const T* noise, T* obs, T* reward, uint8_t* te, uint8_t* tr,
                                  uint8_t* fl, cudaStream_t s)
 {
-    launch_pdl(race_step_fn<T>(P.Mpad, P.action_type, !noise && !RP.disturbances, P.physics, P.K > 1),
-               (long long)(P.env_end - P.env_begin) * P.Mpad, kRaceBlock,
+    // Which register budget an instance family runs at is a property of the CONFIGURATION, never of the batch size: two
+    // instances of one kernel differ at rounding level (ptxas fuses multiply-adds differently under another budget), and a
+    // shard of a batch must reproduce the rows of the whole batch bit for bit (tests/test_cuda_fullsize.py).  Launches without
+    // disturbance draws (QUIET) run the dense 128-register instances (C5M +5.6 %); with draws the Philox / Box-Muller state
+    // makes the cap a loss (C3 -2 %).  ADRP_RACE_DENSE=0 / 1 forces one or the other (diagnostic).
+    const long long threads = (long long)(P.env_end - P.env_begin) * P.Mpad;
+    static const int force_dense = [] { const char* e = getenv("ADRP_RACE_DENSE"); return e ? (e[0] == '0' ? 0 : 1) : -1; }();
+    const bool quiet_launch = !noise && !RP.disturbances;
+    const bool dense = force_dense >= 0 ? force_dense == 1 : quiet_launch;
+    launch_pdl(race_step_fn<T>(P.Mpad, P.action_type, !noise && !RP.disturbances, P.physics, P.K > 1, dense),
+               threads, kRaceBlock,
                race_smem_bytes(P, RP, kRaceBlock), s, P, RP, b, rb, action, noise, obs, reward, te, tr, fl);
     return cudaGetLastError();
 }

@@ -14,10 +14,14 @@ namespace adrp {
 #endif
 constexpr int kRaceBlock = ADRP_RACE_BLOCK, kRaceMinBlocks = ADRP_RACE_MINB;
 #ifdef ADRP_RACE_MAXNREG
-#define ADRP_RACE_BOUNDS __maxnreg__(ADRP_RACE_MAXNREG)
+#define ADRP_RACE_BOUNDS(MINB) __maxnreg__(ADRP_RACE_MAXNREG)
 #else
-#define ADRP_RACE_BOUNDS __launch_bounds__(kRaceBlock, kRaceMinBlocks)
+#define ADRP_RACE_BOUNDS(MINB) __launch_bounds__(kRaceBlock, MINB)
 #endif
+// MINB = 8 (128 registers, 4 warps per scheduler): the DENSE instances, for grids longer than one wave -- with the loop's cold
+// paths out of line the cap costs C5M a few spills and buys a third more warps (2.17e9 -> 2.29e9 drone-steps/s); a grid that
+// fits one wave (C3) gains nothing from more slots and keeps the 168-register instances (measured -2 % with the cap).
+constexpr int kRaceMinBlocksDense = 8;
 static_assert(kBlock % kRaceBlock == 0 && kRaceBlock % 32 == 0, "host-path chunks are cut in units of kBlock threads");
 
 // Env.reset for the masked envs (MultiRaceAviary.reset, :127-167); writes the initial observation if asked.
@@ -83,8 +87,8 @@ race_reset_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ 
 // QUIET: the launch has no disturbance draws (noise == NULL and RaceParams::disturbances == 0).
 // PHY_CT >= 0: physics mask known at compile time (no per-substep mask tests: +6 % on C5M); -1: read from the params.
 // MULTI: adrp_step_n instances -- P.K control steps per launch (the single-step instances compile the loop away).
-template <typename T, int MP, int ACTM, bool QUIET, int PHY_CT, bool MULTI = false>
-__global__ void ADRP_RACE_BOUNDS
+template <typename T, int MP, int ACTM, bool QUIET, int PHY_CT, bool MULTI = false, int MINB = kRaceMinBlocks>
+__global__ void ADRP_RACE_BOUNDS(MINB)
 race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ RaceParams<T> RP, const KBuffers<T> b,
                  const RaceBuffers<T> rb, const T* __restrict__ action, const T* __restrict__ noise, T* __restrict__ obs,
                  T* __restrict__ reward, uint8_t* __restrict__ terminated, uint8_t* __restrict__ truncated,

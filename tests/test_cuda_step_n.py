@@ -3,8 +3,9 @@ family, both precisions, with in-kernel auto-resets (incl. the race env's re-ran
 re-stage in shared memory) and injected / Philox disturbances.
 
 fp64 parity build (-fmad=false): bit-identical.  fp32 product build: the K-step instances are separately compiled kernels
-(the single-step ones must not pay for the loop's registers), so nvcc contracts multiply-adds differently here and there:
-floats agree to rounding (2e-5, relative above 1), flags and counters exactly."""
+(the single-step ones must not pay for the loop's registers), so multiply-adds are contracted differently here and there:
+floats agree to rounding as the closed loops amplify it -- 1e-3 (relative above 1) over the 9 .. 40 control steps of these
+cases, whose setpoints jump by decimetres every step; 2e-5 where the flight is gentle -- flags and counters exactly."""
 import numpy as np
 import pytest
 
@@ -20,7 +21,7 @@ def _handle(cfg):
     return _lib.Handle(cfg)
 
 
-def _compare(cfg, actions, noise=None, set_state=None):
+def _compare(cfg, actions, noise=None, set_state=None, tol32=2e-5):
     """K single steps on one handle vs one K-step launch on its twin: every step's outputs and the final state."""
     import torch
     K = actions.shape[0]
@@ -41,7 +42,7 @@ def _compare(cfg, actions, noise=None, set_state=None):
             assert torch.equal(x, y), (what, (x != y).nonzero()[:4])
         else:
             err = ((x - y).abs() / x.abs().clamp(min=1.0)).max().item()
-            assert err < 2e-5, (what, err)
+            assert err < tol32, (what, err)
 
     for j in range(5):
         same(torch.stack([o[j] for o in outs]), got[j], j)
@@ -130,7 +131,7 @@ def test_race_env_with_auto_reset(level, mode, M, physics, inject, precision):
         noise = np.zeros((K, N, M, 20, 7))
         noise[..., 0:3] = rng.uniform(-0.05, 0.05, noise[..., 0:3].shape)
         noise[..., 3:7] = 1e-3 * rng.standard_normal(noise[..., 3:7].shape)
-    _compare(cfg, acts, noise)
+    _compare(cfg, acts, noise, tol32=1e-3)
 
 
 def test_race_wrappers_and_fullstate_actions():
@@ -151,7 +152,7 @@ def test_race_wrappers_and_fullstate_actions():
     full[..., 0:3] = acts[..., 0:3]
     full[..., 3:6] = rng.uniform(-0.2, 0.2, (K, N, M, 3))
     full[..., 9] = rng.uniform(-0.3, 0.3, (K, N, M))
-    _compare(cfg, full)
+    _compare(cfg, full, tol32=1e-3)
 
 
 def test_step_n_is_graph_capturable_and_plain_steps_too():
