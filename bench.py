@@ -279,6 +279,7 @@ def cpu_port_rate(wl, n_envs_sample, steps, threads):
     """Oracle (CPU port of the reference arithmetic) on a bounded sample of the same workload."""
     from tests.oracle_lib import OracleEnv
     N, M = n_envs_sample, WORKLOADS[wl][1]
+    threads = max(1, min(threads, N))                   # (envs are what the threads split: one env = one thread)
     cfg = make_cfg(wl, N, precision=_abi.F64)           # the reference computes in numpy float64
     env = OracleEnv(cfg)
     if WORKLOADS[wl][5] == _abi.ENV_CTRL and M > 1:
@@ -615,6 +616,15 @@ def main():
                 r = measure(w, WORKLOADS[w][0], args, steps=max(args.steps, 50), **common)
                 r.pop("episode_stats_local")
                 r["parity"] = p
+                if not args.no_cpu_baseline:               # the CPU port beside it: a bounded sample, ~1 s of all host cores
+                    threads = len(os.sched_getaffinity(0))
+                    n_s = cpu_sample_envs(w)
+                    _, d1 = cpu_port_rate(w, n_s, 2, threads)
+                    k_cpu = int(max(2, min(20000, 1.0 / max(d1 / 2, 1e-6))))
+                    rate, dt = cpu_port_rate(w, n_s, k_cpu, threads)
+                    r["cpu_baseline"] = {"value": rate, "unit": "drone-steps/s", "cores": min(threads, n_s), "kind": "port",
+                                         "sample": f"{n_s} envs x {WORKLOADS[w][1]} drones x {k_cpu} control steps ({dt:.1f} s), fp64, "
+                                                   f"OpenMP threads of one process over envs"}
                 others[w] = r
             line["workloads"] = others
         if world == 1 and not args.no_cpu_baseline:

@@ -168,6 +168,8 @@ void derive_params(const adrp_config& c, KParams<T>& P)
         P.k_m = (T)(dt / p.mass); P.k_grav = (T)(dt * c.g);                            // GRAVITY / M = g
         P.k_drag_xy = (T)(dt / p.mass * p.drag_coeff_xy * (2.0 * M_PI / 60.0));
         P.k_drag_z = (T)(dt / p.mass * p.drag_coeff_z * (2.0 * M_PI / 60.0));
+        P.k_lin = (T)(dt * p.lin_damping); P.k_ang = (T)(dt * p.ang_damping);
+        P.plane_reach = (T)(sqrt(0.25 * p.collision_h * p.collision_h + p.collision_r * p.collision_r) * (1.0 + 1e-5) + 1e-6);
     }
     P.speed_limit = (T)(0.03 * p.max_speed_kmh * (1000.0 / 3600.0));
     for (int k = 0; k < 4; ++k) { P.prop_x[k] = (T)p.prop_x[k]; P.prop_y[k] = (T)p.prop_y[k]; }

@@ -39,6 +39,9 @@ struct KParams {
     // with k_t = dt J^-1 arm (z: dt Jz^-1, sign of the RACE model folded in), k_g = dt J^-1 (J_next - J_prev);
     // velocity update v = v * (1 - k_drag * sum_rpm) + (dt / m) thrust * R[:, 2] - (0, 0, dt g)
     T k_tx, k_ty, k_tz, k_gx, k_gy, k_gz, k_m, k_grav, k_drag_xy, k_drag_z;
+    // ... Bullet free body: dt * damping coefficients; plane_reach: no part of the collision cylinder of a drone whose centre is
+    // higher than this can touch z = 0 (sqrt((h/2)^2 + r^2), a hair more): the plane response is only evaluated below it
+    T k_lin, k_ang, plane_reach;
     T prop_x[4], prop_y[4], pyb_mass, pyb_jx, pyb_jy, pyb_jz, lin_damp, ang_damp, coll_r, coll_h;
     T dt, ctrl_dt, g;
     T pid_gravity, pid_kf;                // DSLPIDControl's own URDF constants (control/BaseControl.py:35-39)

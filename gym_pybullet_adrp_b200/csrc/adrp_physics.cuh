@@ -313,6 +313,15 @@ template <typename T> __device__ __noinline__ PlaneHit<T> plane_response(T pen, 
     return r;
 }
 
+// Per-drone constants of the Bullet free body folded once per launch (product build): dt / m, dt / J and the gyroscopic
+// coefficients dt / J_a (J_c - J_b) of a diagonal inertia (race env: per-drone mass / inertia, changeDynamics).
+template <typename T> struct PybFold { T dim, kx, ky, kz, gx, gy, gz; };
+template <typename T> __device__ __forceinline__ PybFold<T> pyb_fold(const KParams<T>& P, T m, T jx, T jy, T jz)
+{
+    const T ix = P.dt * M<T>::rcp(jx), iy = P.dt * M<T>::rcp(jy), iz = P.dt * M<T>::rcp(jz);
+    return {P.dt * M<T>::rcp(m), ix, iy, iz, ix * (jz - jy), iy * (jx - jz), iz * (jy - jx)};
+}
+
 // Bullet free body.  fz: total body-z force at the props + downwash; tb: body torque; fext: world force;
 // m, j*: the body's mass and principal inertia (per drone in the race env, changeDynamics).
 // wl (fast build only): the angular velocity in the BASE frame, carried by the caller across the substeps of one
@@ -328,13 +337,13 @@ __device__ __forceinline__ void pyb_substep(const KParams<T>& P, int phy, Drone<
         // the new world rate is R u and the pose update is q' = dq(R u dt) q = q dq(u dt), hence R' = R Exp(u dt) and the
         // next substep's base-frame rate R'^T R u = Exp(-u dt) u = u: the base-frame rate integrates without any
         // rotation, and the world rate is only needed once the control step is over.
+        // w + dt J^-1 (tau - ka J w - w x J w) per axis = w (1 - dt ka) + (dt / J) tau - (dt / J (J_c - J_b)) w_b w_c
         const T vn = M<T>::fsqrt(dot(d.v, d.v)), wn = M<T>::fsqrt(dot(wl, wl));
-        const V3<T> Jw = {jx * wl.x, jy * wl.y, jz * wl.z};
-        const V3<T> gy = cross(wl, Jw);
-        const T kl = P.lin_damp + P.lin_damp * vn, ka = P.ang_damp + P.ang_damp * wn;
-        const T im = M<T>::rcp(m), dkl = T(1) - P.dt * kl, dim = P.dt * im;
-        const T dx = P.dt * M<T>::rcp(jx), dy = P.dt * M<T>::rcp(jy), dz = P.dt * M<T>::rcp(jz);
-        wl = {wl.x + dx * (tb.x - Jw.x * ka - gy.x), wl.y + dy * (tb.y - Jw.y * ka - gy.y), wl.z + dz * (tb.z - Jw.z * ka - gy.z)};
+        const PybFold<T> K = pyb_fold(P, m, jx, jy, jz);                 // loop-invariant: hoisted by the compiler
+        const T dkl = (T(1) - P.k_lin) - P.k_lin * vn, dka = (T(1) - P.k_ang) - P.k_ang * wn;
+        const T yz = wl.y * wl.z, zx = wl.z * wl.x, xy = wl.x * wl.y;
+        wl = {wl.x * dka + K.kx * tb.x - K.gx * yz, wl.y * dka + K.ky * tb.y - K.gy * zx, wl.z * dka + K.kz * tb.z - K.gz * xy};
+        const T dim = K.dim;
         d.v = {d.v.x * dkl + dim * fw.x, d.v.y * dkl + dim * fw.y, d.v.z * dkl + dim * fw.z};
         d.p = {d.p.x + P.dt * d.v.x, d.p.y + P.dt * d.v.y, d.p.z + P.dt * d.v.z};
         // exponential map (btMultiBody::stepPositionsMultiDof) in the base frame: q <- q (k u, cos)
@@ -387,7 +396,7 @@ __device__ __forceinline__ void pyb_substep(const KParams<T>& P, int phy, Drone<
     }
     // (the product build renormalises once per control step, in the kernel epilogue: the update is linear in q and
     // rotmat_loop divides by |q|^2)
-    if (phy & ADRP_PHY_GROUND) {
+    if ((phy & ADRP_PHY_GROUND) && (!M<T>::fast || d.p.z < P.plane_reach)) {   // (product build: exact culling, KParams::plane_reach)
         // declared plane response: project the lowest point of the collision cylinder back to z = 0,
         // cancel the approaching normal velocity, Coulomb friction mu = 0.5 on the tangential part
         const T r22 = T(1) - T(2) * (d.q.x * d.q.x + d.q.y * d.q.y);

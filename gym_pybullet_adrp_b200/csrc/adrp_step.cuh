@@ -102,8 +102,11 @@ __device__ __forceinline__ int group_or(int v, int Mpad)
 // MULTI: adrp_step_n instances -- P.K control steps per launch (the single-step instances compile the loop away and are
 // the code they were before it existed: the loop costs the all-forces instances 12 registers, i.e. one resident block).
 // DM: prop layout compiled in (0: X -- CF2X / RACE; -1: drone model read from the params).
+// Launch bounds: the specialised single-step instances (DM >= 0) ask for 6 resident blocks of 128 (<= 85 registers): the all-forces
+// Bullet instance drops from 91 to 85 without spills and C4 gains 3 %; the adrp_step_n instances need their registers for the
+// control-step loop (the same bound costs them 2 - 5 %), the generic ones for the DSLPID state.
 template <typename T, int PHY_CT, int ACTC, int MP, int ENVK = -1, bool MULTI = false, int DM = -1>
-__global__ void __launch_bounds__(kStepBlock, ADRP_STEP_MINB)
+__global__ void __launch_bounds__(kStepBlock, (DM >= 0 && !MULTI && ADRP_STEP_MINB < 6) ? 6 : ADRP_STEP_MINB)
 step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* __restrict__ action,
             T* __restrict__ obs, T* __restrict__ reward, uint8_t* __restrict__ terminated,
             uint8_t* __restrict__ truncated, uint8_t* __restrict__ drone_flags)
