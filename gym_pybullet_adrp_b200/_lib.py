@@ -98,6 +98,9 @@ class Handle:
         self.terminated = torch.zeros(self.N, dtype=torch.uint8, device=self.device)
         self.truncated = torch.zeros(self.N, dtype=torch.uint8, device=self.device)
         self.flags = torch.zeros((self.N, self.M), dtype=torch.uint8, device=self.device)
+        # (the outputs are persistent tensors: their addresses are looked up once, not on every step)
+        self._out_ptrs = tuple(t.data_ptr() for t in (self.obs, self.reward, self.terminated, self.truncated, self.flags))
+        self._act_numel = self.N * self.M * self.A
 
     # ------------------------------------------------------------------ helpers
     def _check(self, rc, what):
@@ -152,11 +155,16 @@ class Handle:
         / ``reset`` overwrites them in place.  Rollout code that keeps a reference across steps (``obs_list.append(obs)``,
         ``next_obs`` vs ``obs``) must ``clone()``; ``step_n(..., keep_outputs=True)`` and ``vec_env.TorchVecEnv`` return
         fresh tensors."""
-        a = self._dev(action, (self.N, self.M, self.A))
+        torch = _torch()
+        if torch.is_tensor(action) and action.dtype == self.dtype and action.device == self.device \
+                and action.is_contiguous() and action.numel() == self._act_numel:
+            a = action                                     # already what the kernel reads: no conversion, no reshape
+        else:
+            a = self._dev(action, (self.N, self.M, self.A))
         nz = None if noise is None else self._dev(noise, (self.N, self.M, self.S, 7))
-        self._check(self.lib.adrp_step(self._h, a.data_ptr(), None if nz is None else nz.data_ptr(),
-                                       self.obs.data_ptr(), self.reward.data_ptr(), self.terminated.data_ptr(),
-                                       self.truncated.data_ptr(), self.flags.data_ptr(), self._stream()), "adrp_step")
+        rc = self.lib.adrp_step(self._h, a.data_ptr(), None if nz is None else nz.data_ptr(), *self._out_ptrs, self._stream())
+        if rc != 0:
+            self._check(rc, "adrp_step")
         return self.obs, self.reward, self.terminated, self.truncated, self.flags
 
     def step_n(self, actions, n_steps=None, noise=None, keep_outputs=False):
