@@ -310,6 +310,13 @@ def main():
         commander_hardcoded_case("race_commander_hardcoded_gs", "getting_started", 2, 520, 8)
         commander_script_case("race_commander_script_gs", "getting_started", 2, 160, 9)
         return
+    if len(sys.argv) > 1 and sys.argv[1] == "--levels":
+        # the remaining level configs: level0 (drone state randomised, nothing else: its own reset-draw layout), level1 on the
+        # Bullet body (inertia + state randomisation and disturbances, nominal track), twogates (another track) with Physics.PYB_GND
+        race_case("race_pyb_compete_level0", "level0", Physics.PYB, RaceMode.COMPETE, 2, 120, 11)
+        race_case("race_pyb_compare_level1", "level1", Physics.PYB, RaceMode.COMPARE, 2, 120, 12)
+        race_case("race_pybgnd_compare_twogates", "twogates", Physics.PYB_GND, RaceMode.COMPARE, 2, 120, 13)
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "--fullstate":
         fullstate_case("race_fullstate_compare_gs", "getting_started", 2, 200, 6)
         return

@@ -85,7 +85,8 @@ def assert_fp32_north_star(o, g, layout, what):
 FULLSTATE_CASES = ["race_fullstate_compare_gs"]          # (Command.FULLSTATE, args) tuples with vel / acc / yaw / rates
 COMMANDER_CASES = ["race_commander_hardcoded_gs", "race_commander_script_gs"]   # every Command through the high-level commander
 WRAPPER_CASES = ["race_wrappers_compare_gs"]             # DroneObservationWrapper(RewardWrapper(MultiRaceAviary))
-RACE_CASES = ["race_pyb_compete_gs", "race_pyb_compare_level3", "race_dyn_compete_level1", "race_pyb_all_compete_level3"]
+RACE_CASES = ["race_pyb_compete_gs", "race_pyb_compare_level3", "race_dyn_compete_level1", "race_pyb_all_compete_level3",
+              "race_pyb_compete_level0", "race_pyb_compare_level1", "race_pybgnd_compare_twogates"]
 
 
 def race_config_for(meta, precision=_abi.F64, num_envs=1, **over):

@@ -16,7 +16,7 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 REF = os.environ.get("ADRP_REFERENCE_ROOT", "/root/reference")
 MODES = [("make_golden.py", []), ("make_golden.py", ["--new"]), ("make_golden.py", ["--r2"]),
          ("make_golden_race.py", []), ("make_golden_race.py", ["--new"]), ("make_golden_race.py", ["--fullstate"]),
-         ("make_golden_race.py", ["--commander"])]
+         ("make_golden_race.py", ["--commander"]), ("make_golden_race.py", ["--levels"])]
 
 
 @pytest.mark.skipif(not os.path.isdir(os.path.join(REF, "gym_pybullet_adrp")), reason="reference tree not present")
