@@ -462,6 +462,25 @@ def measure(wl, N, args, *, rank=0, world=1, local=0, dist=None, steps=None, min
         dist.all_reduce(n_ms, op=dist.ReduceOp.MAX)
     n_med = float(n_ms.median().item())
     del acts_n
+    # ... and, for the RL aviaries, with the random policy's U[-1, 1) actions drawn in the kernel (ADRP_ACTIONS_PHILOX: SURVEY 8d's
+    # own definition of C2's actions; no action tensor is read)
+    rnd_med = None
+    if WORKLOADS[wl][5] in (_abi.ENV_HOVER, _abi.ENV_MULTIHOVER):
+        evr = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps_n)]
+        restart()
+        h.step_n(None, n_steps=step_n_k)
+        barrier()
+        for r in range(reps_n):
+            if r and (r * step_n_k) % 208 < step_n_k:
+                restart()
+            evr[r][0].record()
+            h.step_n(None, n_steps=step_n_k)
+            evr[r][1].record()
+        barrier()
+        r_ms = torch.tensor([a.elapsed_time(b) for a, b in evr], device=h.device, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(r_ms, op=dist.ReduceOp.MAX)
+        rnd_med = float(r_ms.median().item())
 
     # ---------------- kernel time with one event pair around every launch (kept for the record: it adds ~7 us per launch)
     restart()
@@ -526,7 +545,8 @@ def measure(wl, N, args, *, rank=0, world=1, local=0, dist=None, steps=None, min
         "block_ms": {"median": med, "min": float(block_ms.min().item()), "max": float(block_ms.max().item())},
         "substep_updates_per_s": value * S,
         "step_n": {"value": world * N * M * step_n_k / (n_med * 1e-3), "control_steps_per_launch": step_n_k,
-                   "ms_per_step": n_med / step_n_k, "launches": reps_n, "substep_updates_per_s": world * N * M * step_n_k * S / (n_med * 1e-3)},
+                   "ms_per_step": n_med / step_n_k, "launches": reps_n, "substep_updates_per_s": world * N * M * step_n_k * S / (n_med * 1e-3),
+                   "random_policy_value": None if rnd_med is None else world * N * M * step_n_k / (rnd_med * 1e-3)},
         "config": {"workload": WORKLOADS[wl][7], "envs_per_gpu": N, "drones_per_env": M, "substeps_per_step": S,
                    "l2": "working set per step (state+action+obs) exceeds the 126 MB L2" if N * M * bpd > 126e6
                    else "working set fits L2 (small workload)", "action_pool": pool},

@@ -17,7 +17,7 @@ LIB_PATH = os.environ.get("ADRP_LIB_PATH") or os.path.join(PKG_DIR, "libadrp_b20
 
 EXPORTS = ["adrp_create", "adrp_destroy", "adrp_obs_dim", "adrp_action_dim", "adrp_noise_dim",
            "adrp_reset_draws_dim", "adrp_substeps", "adrp_reset", "adrp_set_state", "adrp_get_state",
-           "adrp_step", "adrp_step_n", "adrp_step_host", "adrp_dslpid_control", "adrp_launch_count", "adrp_set_profiling",
+           "adrp_step", "adrp_step_n", "adrp_set_rollout_step", "adrp_step_host", "adrp_dslpid_control", "adrp_launch_count", "adrp_set_profiling",
            "adrp_step_kernel_ms", "adrp_fp32_peak_tflops", "adrp_last_error", "adrp_abi_version", "adrp_config_size",
            "adrp_step_rows_static"]
 
@@ -47,6 +47,7 @@ def load():
     lib.adrp_get_state.argtypes = [vp, vp, vp]
     lib.adrp_step.argtypes = [vp, vp, vp, vp, vp, u8p, u8p, u8p, vp]
     lib.adrp_step_n.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, u8p, u8p, u8p, vp]
+    lib.adrp_set_rollout_step.argtypes = [vp, C.c_uint32]
     lib.adrp_step_host.argtypes = [vp, vp, vp, vp, u8p, u8p, u8p]
     lib.adrp_dslpid_control.argtypes = [C.c_int, C.c_int, C.POINTER(_abi.DroneParamsC), C.c_double, C.c_int,
                                         C.c_double] + [vp] * 12
@@ -172,14 +173,19 @@ class Handle:
 
         ``actions``: (K, N, M, A) -- one slice per step -- or (N, M, A), held for all ``n_steps`` (a fixed DSLPID target, a
         hover setpoint).  ``keep_outputs``: return every step's outputs, shaped (K, N, M, O) / (K, N) / (K, N, M), in
-        fresh tensors; otherwise the handle's own tensors end up holding the last step's."""
+        fresh tensors; otherwise the handle's own tensors end up holding the last step's.  ``actions=None``: a random
+        policy -- every component drawn U[-1, 1) inside the kernel (ADRP_ACTIONS_PHILOX: Philox4x32-10 keyed by the config's
+        seed, counter (global env, 192 + drone, rollout step, 0); ``set_rollout_step`` replays)."""
         torch = _torch()
-        a = torch.as_tensor(actions, dtype=self.dtype, device=self.device).contiguous()
-        per_step = a.dim() == 4
-        K = int(a.shape[0]) if per_step else int(n_steps)
-        if n_steps is not None and per_step and int(n_steps) != K:
-            raise ValueError("n_steps does not match the leading dimension of actions")
-        a = a.reshape((K, self.N, self.M, self.A) if per_step else (self.N, self.M, self.A))
+        if actions is None:
+            a, per_step, K = None, 2, int(n_steps)
+        else:
+            a = torch.as_tensor(actions, dtype=self.dtype, device=self.device).contiguous()
+            per_step = a.dim() == 4
+            K = int(a.shape[0]) if per_step else int(n_steps)
+            if n_steps is not None and per_step and int(n_steps) != K:
+                raise ValueError("n_steps does not match the leading dimension of actions")
+            a = a.reshape((K, self.N, self.M, self.A) if per_step else (self.N, self.M, self.A))
         nz = None
         if noise is not None:
             nz = torch.as_tensor(noise, dtype=self.dtype, device=self.device).contiguous()
@@ -192,13 +198,17 @@ class Handle:
                    torch.empty((K, self.N, self.M), dtype=torch.uint8, device=self.device))
         else:
             out = (self.obs, self.reward, self.terminated, self.truncated, self.flags)
-        self._check(self.lib.adrp_step_n(self._h, K, int(per_step), int(keep_outputs), a.data_ptr(),
+        self._check(self.lib.adrp_step_n(self._h, K, int(per_step), int(keep_outputs), None if a is None else a.data_ptr(),
                                          None if nz is None else nz.data_ptr(), *[t.data_ptr() for t in out],
                                          self._stream()), "adrp_step_n")
         if keep_outputs:                                   # the handle's tensors mirror the last step, as after step()
             for dst, src in zip((self.obs, self.reward, self.terminated, self.truncated, self.flags), out):
                 dst.copy_(src[-1])
         return out
+
+    def set_rollout_step(self, step: int):
+        """Third Philox counter word of the next ``step_n(None, ...)`` draw (adrp_set_rollout_step)."""
+        self._check(self.lib.adrp_set_rollout_step(self._h, int(step)), "adrp_set_rollout_step")
 
     def step_host(self, action: np.ndarray):
         """Host path (NumPy in, NumPy out): H2D, launch, D2H inside the C call."""

@@ -58,6 +58,7 @@ struct HandleBase {
     cudaEvent_t ev_order = nullptr;
     cudaEvent_t ev_join = nullptr;                  // step_host: the second private stream joins the first before the small copies
     bool order_pending = false;
+    uint32_t rollout_step = 0;                      // ADRP_ACTIONS_PHILOX: control steps drawn so far (Philox counter word)
     virtual ~HandleBase() {}
 };
 
@@ -134,6 +135,8 @@ void derive_params(const adrp_config& c, KParams<T>& P)
     P.Dpad = (long long)P.N * P.Mpad;
     P.env_begin = 0; P.env_end = P.N; P.obs_vec = 0; P.act_vec = 0;
     P.K = 1; P.act_step = P.obs_step = P.env_step = P.drone_step = P.noise_step = 0;
+    P.act_rng = 0; P.rng_step0 = 0; P.rng_lo = (unsigned)(c.seed & 0xffffffffu); P.rng_hi = (unsigned)(c.seed >> 32);
+    P.env_offset = c.env_offset;
     P.pyb_freq = c.pyb_freq;
     // step_counter / PYB_FREQ > EPISODE_LEN_SEC, evaluated like Python does (double division)
     int ts = 0;
@@ -335,13 +338,15 @@ int do_reset(Handle<T>* h, const uint8_t* mask, const T* draws, T* obs, cudaStre
 // buffers hold one slice per control step, or one slice that every step reads / overwrites.
 template <typename T>
 int do_step(Handle<T>* h, const T* action, const T* noise, T* obs, T* reward, uint8_t* te, uint8_t* tr, uint8_t* fl, cudaStream_t s,
-            int env_begin = 0, int env_end = -1, int K = 1, bool actions_per_step = false, bool outputs_per_step = false)
+            int env_begin = 0, int env_end = -1, int K = 1, int actions_per_step = ADRP_ACTIONS_HELD, bool outputs_per_step = false)
 {
     KParams<T> P = h->P;
     P.env_begin = env_begin; P.env_end = env_end < 0 ? P.N : env_end;
     P.K = K;
     const long long nd = (long long)P.N * P.M;
-    if (actions_per_step) { P.act_step = nd * P.A; P.noise_step = nd * P.S * 7; }
+    if (actions_per_step == ADRP_ACTIONS_PER_STEP) P.act_step = nd * P.A;
+    if (actions_per_step != ADRP_ACTIONS_HELD) P.noise_step = nd * P.S * 7;
+    if (actions_per_step == ADRP_ACTIONS_PHILOX) { P.act_rng = 1; P.rng_step0 = h->rollout_step; h->rollout_step += (uint32_t)K; }
     if (outputs_per_step) { P.obs_step = nd * P.O; P.env_step = P.N; P.drone_step = nd; }
     P.obs_vec = sizeof(T) == 4 && (P.O % 4) == 0 && (P.A == 4 || P.env_kind == ADRP_ENV_CTRL) && ((uintptr_t)obs & 15) == 0;
     P.act_vec = sizeof(T) == 4 && P.A == 4 && ((uintptr_t)action & 15) == 0;
@@ -512,16 +517,33 @@ int adrp_step(adrp_handle* h, const void* action, const void* noise, void* obs, 
     return rc != ADRP_OK ? rc : mark_order(base(h), s);
 }
 
+int adrp_set_rollout_step(adrp_handle* h, uint32_t step)
+{
+    if (!h) return ADRP_EINVAL;
+    base(h)->rollout_step = step;
+    return ADRP_OK;
+}
+
 int adrp_step_n(adrp_handle* h, int n_steps, int actions_per_step, int outputs_per_step, const void* action, const void* noise,
                 void* obs, void* reward, uint8_t* terminated, uint8_t* truncated, uint8_t* drone_flags, void* stream)
 {
-    if (!h || !action || !obs || !reward || !terminated || !truncated || n_steps < 1) {
+    const bool drawn = actions_per_step == ADRP_ACTIONS_PHILOX;
+    if (!h || (!action && !drawn) || !obs || !reward || !terminated || !truncated || n_steps < 1) {
         if (h) base(h)->err = "adrp_step_n: NULL buffer or n_steps < 1";
         return ADRP_EINVAL;
     }
+    if (actions_per_step < ADRP_ACTIONS_HELD || actions_per_step > ADRP_ACTIONS_PHILOX) {
+        base(h)->err = "adrp_step_n: actions_per_step is ADRP_ACTIONS_HELD, ADRP_ACTIONS_PER_STEP or ADRP_ACTIONS_PHILOX";
+        return ADRP_EINVAL;
+    }
+    if (drawn && action_dim(base(h)->cfg.action_type) > 4) {
+        base(h)->err = "adrp_step_n: ADRP_ACTIONS_PHILOX draws the Box(-1, 1) actions of at most 4 components (not ADRP_ACT_PID_FULL / ADRP_ACT_MEL_FULL / ADRP_ACT_MEL_CMD rows)";
+        return ADRP_EUNSUPPORTED;
+    }
     DeviceGuard dg(base(h)->cfg.device);
     cudaStream_t s = (cudaStream_t)stream;
-    const bool aps = actions_per_step != 0, ops = outputs_per_step != 0;
+    const int aps = actions_per_step;
+    const bool ops = outputs_per_step != 0;
     const int rc = BY_PRECISION(h, do_step<double>(typed<double>(h), (const double*)action, (const double*)noise, (double*)obs, (double*)reward, terminated, truncated, drone_flags, s, 0, -1, n_steps, aps, ops),
                                 do_step<float>(typed<float>(h), (const float*)action, (const float*)noise, (float*)obs, (float*)reward, terminated, truncated, drone_flags, s, 0, -1, n_steps, aps, ops));
     return rc != ADRP_OK ? rc : mark_order(base(h), s);

@@ -112,7 +112,7 @@ cudaError_t Launch<T>::step(const KParams<T>& P, const KBuffers<T>& b, const T* 
 {
     const bool pid = P.action_type == ADRP_ACT_PID || P.action_type == ADRP_ACT_ONE_D_PID ||
                      P.action_type == ADRP_ACT_VEL || P.action_type == ADRP_ACT_PID_FULL;
-    const bool multi = P.K > 1;                               // adrp_step_n: the instances with the control-step loop
+    const bool multi = P.K > 1 || P.act_rng;                  // adrp_step_n: the instances with the control-step loop (and the action draw)
     const long long grid = (long long)(P.env_end - P.env_begin) * P.Mpad;      // threads of this launch
     // product build: the masks the configs use (Physics.DYN, Physics.PYB and the two all-forces masks) have instances with the
     // mask as a template argument (no per-substep mask tests, fewer registers: C5 +2 %, C2 +2 % at every batch size measured),
@@ -237,7 +237,7 @@ cudaError_t Launch<T>::race_step(const KParams<T>& P, const RaceParams<T>& RP, c
     static const int force_dense = [] { const char* e = getenv("ADRP_RACE_DENSE"); return e ? (e[0] == '0' ? 0 : 1) : -1; }();
     const bool quiet_launch = !noise && !RP.disturbances;
     const bool dense = force_dense >= 0 ? force_dense == 1 : quiet_launch;
-    launch_pdl(race_step_fn<T>(P.Mpad, P.action_type, !noise && !RP.disturbances, P.physics, P.K > 1, dense),
+    launch_pdl(race_step_fn<T>(P.Mpad, P.action_type, !noise && !RP.disturbances, P.physics, P.K > 1 || P.act_rng, dense),
                threads, kRaceBlock,
                race_smem_bytes(P, RP, kRaceBlock), s, P, RP, b, rb, action, noise, obs, reward, te, tr, fl);
     return cudaGetLastError();

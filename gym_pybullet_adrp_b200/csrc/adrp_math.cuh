@@ -8,6 +8,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <math.h>
+#include <stdint.h>
 
 namespace adrp {
 
@@ -318,5 +319,23 @@ template <typename T> __device__ __forceinline__ Q4<T> canon_quat_loop(const Q4<
     if (pivot < T(0)) inv = -inv;
     return {q.x * inv, q.y * inv, q.z * inv, q.w * inv};
 }
+
+// ---------------------------------------------------------------- Philox4x32-10 (Salmon et al. 2011)
+__device__ __forceinline__ void philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t out[4])
+{
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        const uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+template <typename T> __device__ __forceinline__ T u01(uint32_t x) { return (T)(x >> 8) * (T)5.9604644775390625e-08; }              // [0,1)
+template <typename T> __device__ __forceinline__ T u01_open(uint32_t x) { return (T)((x >> 8) + 1) * (T)5.9604644775390625e-08; }   // (0,1]
+// [-1, 1): the action draw of adrp_step_n's ADRP_ACTIONS_PHILOX (exact in fp32 and fp64: 24 bits)
+template <typename T> __device__ __forceinline__ T u11(uint32_t x) { return (T)(int)((x >> 8) - 0x800000u) * (T)1.1920928955078125e-07; }
 
 }  // namespace adrp

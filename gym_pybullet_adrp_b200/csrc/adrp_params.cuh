@@ -48,6 +48,12 @@ struct KParams {
     T hover_lim;                          // 1.5 (HoverAviary.py:108) or 2.0 (MultiHoverAviary.py:121)
     T init_xyz[ADRP_MAX_DRONES][3], init_rpy[ADRP_MAX_DRONES][3], init_quat[ADRP_MAX_DRONES][4], init_vel[ADRP_MAX_DRONES][3],
         init_pqr[ADRP_MAX_DRONES][3], target[ADRP_MAX_DRONES][3];
+    // adrp_step_n with ADRP_ACTIONS_PHILOX: every action component is drawn in the kernel, a = u11(Philox4x32-10(key = rng_lo, rng_hi;
+    // counter = (global env, 192 + drone, rng_step0 + control step of this launch, 0))): the draw of a random policy
+    // (action_space.sample() over Box(-1, 1), envs/BaseRLAviary.py:129-135, envs/MultiRaceAviary.py:284-287)
+    int act_rng;
+    unsigned rng_lo, rng_hi, rng_step0;
+    unsigned long long env_offset;        // global index of env 0 of this shard
 };
 
 // Race env constants (envs/MultiRaceAviary.py; config/level*.yaml), by value next to KParams.

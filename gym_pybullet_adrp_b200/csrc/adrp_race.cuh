@@ -14,22 +14,6 @@
 
 namespace adrp {
 
-// ---------------------------------------------------------------- Philox4x32-10 (Salmon et al. 2011)
-__device__ __forceinline__ void philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t out[4])
-{
-#pragma unroll
-    for (int r = 0; r < 10; ++r) {
-        const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
-        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
-        const uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
-        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
-        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
-    }
-    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
-}
-template <typename T> __device__ __forceinline__ T u01(uint32_t x) { return (T)(x >> 8) * (T)5.9604644775390625e-08; }              // [0,1)
-template <typename T> __device__ __forceinline__ T u01_open(uint32_t x) { return (T)((x >> 8) + 1) * (T)5.9604644775390625e-08; }   // (0,1]
-
 // ---------------------------------------------------------------- per-drone race state in HBM (SoA)
 template <typename T>
 __device__ __forceinline__ void load_mel(const RaceBuffers<T>& rb, long long D, long long t, Mel<T>& m)

@@ -184,7 +184,11 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
     }
     if (new_setpoint) {
         T a_yaw;
-        if (M<T>::fast && !FULL && P.act_vec) {               // one 16-byte load per drone instead of four strided ones
+        if (MULTI && !FULL && !CMD && P.act_rng) {            // a random policy's draw, made here (KParams::act_rng)
+            uint32_t o[4];
+            philox4x32((uint32_t)(RP.env_offset + (unsigned long long)env), (uint32_t)(192 + i), P.rng_step0 + (uint32_t)ks, 0u, RP.seed_lo, RP.seed_hi, o);
+            sp.pos[0] = u11<float>(o[0]); sp.pos[1] = u11<float>(o[1]); sp.pos[2] = u11<float>(o[2]); a_yaw = u11<T>(o[3]);
+        } else if (M<T>::fast && !FULL && P.act_vec) {        // one 16-byte load per drone instead of four strided ones
             const float4 a4 = *reinterpret_cast<const float4*>(a);
             sp.pos[0] = a4.x; sp.pos[1] = a4.y; sp.pos[2] = a4.z; a_yaw = (T)a4.w;
         } else {

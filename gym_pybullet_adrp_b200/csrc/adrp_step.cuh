@@ -151,7 +151,12 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
     const T* a = action + (long long)kv * P.act_step + od * P.A;
     constexpr int AMAX = ACTC == 0 ? 4 : 12;             // RPM-type actions have at most 4 components
     T act_in[AMAX];
-    if (M<T>::fast && P.act_vec && AMAX == 4) {               // one 16-byte load per drone instead of four strided ones
+    if (MULTI && P.act_rng) {                                 // a random policy's draw, made here (KParams::act_rng)
+        uint32_t o[4];
+        philox4x32((uint32_t)(P.env_offset + (unsigned long long)env), (uint32_t)(192 + i), P.rng_step0 + (uint32_t)ks, 0u, P.rng_lo, P.rng_hi, o);
+#pragma unroll
+        for (int k = 0; k < AMAX; ++k) act_in[k] = (k < 4 && k < P.A) ? u11<T>(o[k & 3]) : T(0);
+    } else if (M<T>::fast && P.act_vec && AMAX == 4) {        // one 16-byte load per drone instead of four strided ones
         const float4 a4 = valid ? *reinterpret_cast<const float4*>(a) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         act_in[0] = (T)a4.x; act_in[1] = (T)a4.y; act_in[2] = (T)a4.z; act_in[3] = (T)a4.w;
     } else {

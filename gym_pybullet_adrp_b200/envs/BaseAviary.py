@@ -118,6 +118,28 @@ class BaseAviary:
             return (self._out_obs(obs), float(reward[0]), bool(terminated[0]), bool(truncated[0]), self._computeInfo())
         return obs, reward, terminated.bool(), truncated.bool(), self._computeInfo()
 
+    def step_n(self, actions=None, n_steps=None, keep_outputs=False):
+        """``n_steps`` calls of ``step`` in ONE launch (adrp_step_n; no counterpart in the reference, whose loop is one Python
+        call per control step -- examples/pid.py:138-147, examples/learn.py's rollouts).  ``actions``: ``(K, ...)`` slices in
+        the shape ``step`` takes, one per control step; one such slice, held for ``n_steps``; or ``None``: a random policy, every
+        component drawn U[-1, 1) inside the kernel (``action_space.sample()`` without the host).  Returns torch tensors
+        ``(obs, reward, terminated, truncated, info)`` of the last step, or of every step ``(K, num_envs, ...)`` with
+        ``keep_outputs`` (envs that finish inside the launch restart there when ``auto_reset`` is on)."""
+        import torch
+        h = self.handle
+        a = None
+        if actions is not None:
+            a = actions.to(device=h.device, dtype=h.dtype) if isinstance(actions, torch.Tensor) else \
+                torch.tensor(np.asarray(actions), dtype=h.dtype, device=h.device)
+            per_step = a.numel() != h.N * h.M * h.A
+            a = a.reshape((-1, h.N, h.M, h.A) if per_step else (h.N, h.M, h.A))
+            if per_step and n_steps is None:
+                n_steps = int(a.shape[0])
+        obs, reward, terminated, truncated, flags = h.step_n(a, n_steps=n_steps, keep_outputs=keep_outputs)
+        self._last_flags = flags[-1] if keep_outputs else flags
+        self.step_counter += int(n_steps) * self.PYB_STEPS_PER_CTRL
+        return obs, reward, terminated.bool(), truncated.bool(), self._computeInfo()
+
     def render(self, mode='human', close=False):
         """BaseAviary.render (:391-416): text only."""
         t = self.step_counter * self.PYB_TIMESTEP

@@ -200,14 +200,26 @@ int adrp_step(adrp_handle* h, const void* action, const void* noise, void* obs, 
  * (examples/learn.py's shape) needs.  Results equal those of n_steps adrp_step calls: bit for bit in the fp64 build, to
  * rounding in the fp32 build (its n-step kernels are separate instances, so that the single-step ones keep their
  * register count; nvcc contracts a few multiply-adds differently); flags, counters and reset draws are the same.
- *   actions_per_step  != 0: action is (n_steps, N, M, action_dim) and noise (n_steps, N, M, S, noise_dim);
- *                     == 0: one (N, M, action_dim) slice is held for every step
+ *   actions_per_step  ADRP_ACTIONS_PER_STEP: action is (n_steps, N, M, action_dim) and noise (n_steps, N, M, S, noise_dim);
+ *                     ADRP_ACTIONS_HELD: one (N, M, action_dim) slice (and one noise slice) is held for every step;
+ *                     ADRP_ACTIONS_PHILOX: `action` is ignored (may be NULL) and every action component is drawn in the
+ *                       kernel, a ~ U[-1, 1) -- what action_space.sample() of a random policy draws over the reference's
+ *                       Box(-1, 1) spaces (envs/BaseRLAviary.py:129-135, envs/MultiRaceAviary.py:284-287), for action types
+ *                       of at most 4 components: a = ((x >> 8) - 2^23) * 2^-23 with x word k of Philox4x32-10(key =
+ *                       adrp_config.seed; counter = (env_offset + env, 192 + drone, rollout step, 0)), the same in both
+ *                       precisions and on any sharding.  The rollout step counts the control steps drawn on this handle so
+ *                       far (0 at adrp_create, advanced by n_steps per call; adrp_set_rollout_step).  noise: per step.
  *   outputs_per_step  != 0: obs (n_steps, N, M, obs_dim), reward / terminated / truncated (n_steps, N),
  *                           drone_flags (n_steps, N, M): every step's outputs are kept;
  *                     == 0: the same (N, M, obs_dim) ... buffers are overwritten every step (the last step's remain) */
+enum { ADRP_ACTIONS_HELD = 0, ADRP_ACTIONS_PER_STEP = 1, ADRP_ACTIONS_PHILOX = 2 };
 int adrp_step_n(adrp_handle* h, int n_steps, int actions_per_step, int outputs_per_step, const void* action,
                 const void* noise, void* obs, void* reward, uint8_t* terminated, uint8_t* truncated,
                 uint8_t* drone_flags, void* stream);
+
+/* The rollout step of ADRP_ACTIONS_PHILOX (the third Philox counter word of the next draw): set it to replay a rollout or
+ * to continue one from a checkpoint.  No counterpart in the reference, whose action_space.sample() is unseeded. */
+int adrp_set_rollout_step(adrp_handle* h, uint32_t step);
 
 /* Same call with HOST buffers (the path a NumPy user of the reference takes): copies the action to the
  * device, launches, copies obs / reward / flags back and synchronises. */

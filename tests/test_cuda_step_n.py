@@ -182,3 +182,70 @@ def test_step_n_is_graph_capturable_and_plain_steps_too():
     torch.cuda.synchronize()
     assert torch.equal(a.obs, b.obs) and torch.equal(a.get_state(), b.get_state())
     a.close(); b.close()
+
+
+def _random_policy_cfg(case, precision, N, env_offset=0):
+    if case == "race":
+        rc = configs.load_config("level3")
+        rc["episode_len_sec"] = 0.5
+        return _abi.make_race_config(rc, num_envs=N, num_drones=2, physics=Physics.PYB, racemode=RaceMode.COMPETE,
+                                     precision=precision, seed=0x1234567812345, auto_reset=True, env_offset=env_offset), 2, 4
+    kind, M, act, A = {"hover_rpm": (_abi.ENV_HOVER, 1, _abi.ACT_RPM, 4), "multihover_one_d": (_abi.ENV_MULTIHOVER, 3, _abi.ACT_ONE_D_RPM, 1),
+                       "hover_pid": (_abi.ENV_HOVER, 1, _abi.ACT_PID, 3), "multihover_vel": (_abi.ENV_MULTIHOVER, 2, _abi.ACT_VEL, 4)}[case]
+    return _abi.make_config(num_envs=N, num_drones=M, physics=Physics.PYB, pyb_freq=240, ctrl_freq=30, action_type=act, env_kind=kind,
+                            precision=precision, auto_reset=True, episode_len_sec=0.4, seed=0x1234567812345, env_offset=env_offset), M, A
+
+
+@pytest.mark.parametrize("precision", [_abi.F32, _abi.F64])
+@pytest.mark.parametrize("case", ["hover_rpm", "multihover_one_d", "hover_pid", "multihover_vel", "race"])
+def test_random_policy_drawn_in_the_kernel(case, precision):
+    """ADRP_ACTIONS_PHILOX (step_n(None, K)): the launch that draws its own U[-1, 1) actions equals, bit for bit in both builds
+    (the same kernel instance runs both), the launch that is handed those actions -- computed here by the NumPy Philox of
+    tests/philox_np.py (pinned to Random123's known answers on the CPU side); two calls in a row continue the counter, a
+    shard draws the rows of the whole batch, and set_rollout_step replays."""
+    import torch
+    from tests.philox_np import random_policy_actions
+    N, K1, K2, off = 96, 7, 5, 1000
+    cfg, M, A = _random_policy_cfg(case, precision, N, off)
+    a, b = _handle(cfg), _handle(cfg)
+    a.reset(); b.reset()
+    want_actions = random_policy_actions(cfg.seed, off, N, M, A, 0, K1 + K2)
+    got = a.step_n(None, n_steps=K1, keep_outputs=True)
+    want = b.step_n(want_actions[:K1], keep_outputs=True)
+    for x, y in zip(got, want):
+        assert torch.equal(x, y), (x != y).nonzero()[:4]
+    got = a.step_n(None, n_steps=K2, keep_outputs=True)           # continues at rollout step K1
+    want = b.step_n(want_actions[K1:], keep_outputs=True)
+    for x, y in zip(got, want):
+        assert torch.equal(x, y)
+    assert torch.equal(a.get_state(), b.get_state())
+    # a shard of the batch (env_offset = global index of its first env) reproduces those rows
+    lo, hi = 32, 64
+    cfg_s, _, _ = _random_policy_cfg(case, precision, hi - lo, off + lo)
+    s = _handle(cfg_s)
+    s.reset()
+    w = _handle(cfg)                                              # (a fresh one: the RL aviaries' action buffer survives reset())
+    w.reset()
+    whole = w.step_n(None, n_steps=K1, keep_outputs=True)
+    part = s.step_n(None, n_steps=K1, keep_outputs=True)
+    for x, y in zip(whole, part):
+        assert torch.equal(x[:, lo:hi], y)
+    # adrp_set_rollout_step: the draws of rollout steps 5 .. 7 on fresh handles
+    r1, r2 = _handle(cfg), _handle(cfg)
+    r1.reset(); r2.reset()
+    r1.set_rollout_step(5)
+    for x, y in zip(r1.step_n(None, n_steps=3), r2.step_n(want_actions[5:8])):
+        assert torch.equal(x, y)
+    r1.step_n(None, n_steps=1)                                    # K = 1, no action buffer at all
+    r1.close(); r2.close()
+    for h in (a, b, s, w):
+        h.close()
+
+
+def test_random_policy_rejects_wide_action_rows():
+    cfg = _abi.make_config(num_envs=4, num_drones=1, physics=Physics.DYN, pyb_freq=240, ctrl_freq=30,
+                           action_type=_abi.ACT_PID_FULL, env_kind=_abi.ENV_CTRL, precision=_abi.F32)
+    h = _handle(cfg)
+    with pytest.raises(RuntimeError, match="ADRP_ACTIONS_PHILOX"):
+        h.step_n(None, n_steps=2)
+    h.close()

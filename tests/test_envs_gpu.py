@@ -89,6 +89,38 @@ def test_multihover_batched_envs_are_independent_copies():
     env.close()
 
 
+def test_env_step_n_reproduces_the_golden_run_in_one_launch_and_draws_a_random_policy():
+    """BaseAviary.step_n: the golden run's actions handed over at once = the reference's observations of every step; a held
+    slice; and ``None`` = the random policy drawn in the kernel (a second env with the same seed draws the same rollout)."""
+    import torch
+    meta, z = gc.load("multihover_pyb_rpm_m2")
+    N, K = 4, meta["steps"]
+    mk = lambda: MultiHoverAviary(num_drones=2, physics=Physics[meta["physics"]], pyb_freq=meta["pyb_freq"],   # noqa: E731
+                                  ctrl_freq=meta["ctrl_freq"], act=ActionType[meta["act"]], initial_xyzs=np.array(meta["init_xyz"]),
+                                  precision="fp64", num_envs=N, auto_reset=False)
+    env = mk()
+    env.reset()
+    acts = np.broadcast_to(z["actions"][:K, None], (K, N) + z["actions"].shape[1:])
+    obs, rew, te, tr, _ = env.step_n(acts, keep_outputs=True)
+    assert tuple(obs.shape)[:3] == (K, N, 2) and te.dtype == torch.bool
+    o = obs.cpu().numpy()
+    assert gc.rel_err(o[..., :12], np.broadcast_to(z["obs"][:K, None, :, :12], o[..., :12].shape)) < 1e-6
+    assert np.allclose(rew.cpu().numpy(), z["reward"][:K, None], rtol=1e-9)
+    assert env.step_counter == K * env.PYB_STEPS_PER_CTRL
+    env.reset()
+    last = env.step_n(acts[0], n_steps=3)[0].clone()
+    assert tuple(last.shape) == (N, 2, o.shape[-1])
+    other = mk()
+    env.close()
+    env = mk()
+    env.reset(); other.reset()
+    r1 = env.step_n(None, n_steps=6, keep_outputs=True)
+    r2 = other.step_n(None, n_steps=6, keep_outputs=True)
+    assert torch.equal(r1[0], r2[0]) and torch.equal(r1[1], r2[1])
+    assert not torch.equal(r1[0][:, 0], r1[0][:, 1])               # ... and every env draws its own actions
+    env.close(); other.close()
+
+
 def test_multi_race_aviary_matches_reference_run():
     """scripts/sim.py-style loop on the reference's own race run (level3, COMPARE), draws and disturbances injected."""
     meta, z = gc.load("race_pyb_compare_level3")
