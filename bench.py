@@ -74,7 +74,7 @@ def race_rc(wl):
     return rc
 
 
-def make_cfg(wl, n_envs, device=0, env_offset=0, precision=_abi.F32):
+def make_cfg(wl, n_envs, device=0, env_offset=0, precision=_abi.F32, obs_columns=0):
     N, M, phy, pyb, ctrl, kind, act, _ = WORKLOADS[wl]
     if kind == _abi.ENV_RACE:
         from gym_pybullet_adrp_b200.utils.enums import RaceMode
@@ -84,7 +84,8 @@ def make_cfg(wl, n_envs, device=0, env_offset=0, precision=_abi.F32):
     xyz = formation_xyz(M) if M > 1 else None
     return _abi.make_config(num_envs=n_envs, num_drones=M, drone_model=DroneModel.CF2X, physics=phy, pyb_freq=pyb,
                             ctrl_freq=ctrl, action_type=act, env_kind=kind, precision=precision, device=device,
-                            initial_xyzs=xyz, auto_reset=(kind != _abi.ENV_CTRL), seed=5, env_offset=env_offset)
+                            initial_xyzs=xyz, auto_reset=(kind != _abi.ENV_CTRL), seed=5, env_offset=env_offset,
+                            obs_columns=obs_columns)
 
 
 def make_actions(wl, n_envs, M, A, seed, count):
@@ -380,7 +381,8 @@ def measure(wl, N, args, *, rank=0, world=1, local=0, dist=None, steps=None, min
     S = WORKLOADS[wl][3] // WORKLOADS[wl][4]
     K = steps or args.steps
     ctrl = WORKLOADS[wl][5] == _abi.ENV_CTRL
-    h = _lib.Handle(make_cfg(wl, N, device=local, env_offset=rank * N))
+    obs_columns = getattr(args, "obs_columns", 0) if ctrl else 0
+    h = _lib.Handle(make_cfg(wl, N, device=local, env_offset=rank * N, obs_columns=obs_columns))
     pool = 4
     acts_np = make_actions(wl, N, M, h.A, 5 + rank, pool)
     acts_dev = [torch.as_tensor(a, device=h.device) for a in acts_np]
@@ -501,20 +503,33 @@ def measure(wl, N, args, *, rank=0, world=1, local=0, dist=None, steps=None, min
             buf = h.pinned_empty(a.shape)
             buf[...] = a
             acts_pin.append(buf)
-        for k in range(3):
-            h.step_host(acts_pin[k % pool])
-        barrier()
-        t0 = time.perf_counter()
-        for k in range(e2e_steps):
-            h.step_host(acts_pin[k % pool])
-        barrier()
-        t_e2e = torch.tensor([time.perf_counter() - t0], device=h.device, dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
+
+        def host_rate(hh):
+            for k in range(3):
+                hh.step_host(acts_pin[k % pool])
+            barrier()
+            t0 = time.perf_counter()
+            for k in range(e2e_steps):
+                hh.step_host(acts_pin[k % pool])
+            barrier()
+            t_e2e = torch.tensor([time.perf_counter() - t0], device=hh.device, dtype=torch.float64)
+            if world > 1:
+                dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
+            return world * N * M * e2e_steps / float(t_e2e.item())
+
         isz = 4
-        e2e_out = {"value": world * N * M * e2e_steps / float(t_e2e.item()), "unit": "drone-steps/s",
-                   "h2d_bytes_per_step": N * M * h.A * isz, "d2h_bytes_per_step": N * M * h.O * isz + N * isz + 2 * N + N * M,
-                   "steps": e2e_steps}
+        d2h = lambda hh: N * M * hh.O * isz + N * isz + 2 * N + N * M   # noqa: E731
+        e2e_out = {"value": host_rate(h), "unit": "drone-steps/s",
+                   "h2d_bytes_per_step": N * M * h.A * isz, "d2h_bytes_per_step": d2h(h), "steps": e2e_steps}
+        if ctrl and h.A == 4:
+            # the same call for a caller who reads only the kinematic columns (adrp_config.obs_columns = 12; NOT the
+            # reference's 20-float row, so not the headline): 40 % less D2H on a link-bound path
+            h12 = _lib.Handle(make_cfg(wl, N, device=local, env_offset=rank * N, obs_columns=12))
+            if state0 is not None:
+                h12.set_state(state0)
+            e2e_out["kinematic_columns_only"] = {"value": host_rate(h12), "obs_columns": 12, "d2h_bytes_per_step": d2h(h12)}
+            h12.close()
+            restart()
 
     stats = torch.stack([h.obs[:, :, 2].double().mean(), h.reward.double().mean()])
     O, A = h.O, h.A
@@ -547,7 +562,8 @@ def measure(wl, N, args, *, rank=0, world=1, local=0, dist=None, steps=None, min
         "step_n": {"value": world * N * M * step_n_k / (n_med * 1e-3), "control_steps_per_launch": step_n_k,
                    "ms_per_step": n_med / step_n_k, "launches": reps_n, "substep_updates_per_s": world * N * M * step_n_k * S / (n_med * 1e-3),
                    "random_policy_value": None if rnd_med is None else world * N * M * step_n_k / (rnd_med * 1e-3)},
-        "config": {"workload": WORKLOADS[wl][7], "envs_per_gpu": N, "drones_per_env": M, "substeps_per_step": S,
+        "config": {"workload": WORKLOADS[wl][7] + (" [obs_columns=12: NOT the reference's row]" if O == 12 and ctrl else ""),
+                   "envs_per_gpu": N, "drones_per_env": M, "substeps_per_step": S,
                    "l2": "working set per step (state+action+obs) exceeds the 126 MB L2" if N * M * bpd > 126e6
                    else "working set fits L2 (small workload)", "action_pool": pool},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -569,6 +585,9 @@ def main():
                     help="weak: --envs-per-gpu (default: the workload's) on every GPU; strong: --total-drones split over the GPUs")
     ap.add_argument("--total-drones", type=int, default=1 << 20, help="strong scaling: drones of the whole job (SURVEY 8d: 2^20, 2^23)")
     ap.add_argument("--envs-per-gpu", type=int, default=0)
+    ap.add_argument("--obs-columns", type=int, default=0, choices=[0, 12, 20],
+                    help="diagnostic: CtrlAviary-kind workloads with adrp_config.obs_columns (12 = kinematic columns only; not the "
+                         "reference's row, so not a headline figure)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-workloads", action="store_true", help="skip the other configs (C1 .. C5M) of the default N = 1 run")
     args = ap.parse_args()

@@ -13,7 +13,7 @@ import math
 from .assets import DroneParams, drone_params
 from .utils.enums import ActionType, DroneModel, Physics, RaceMode
 
-ABI_VERSION = 5
+ABI_VERSION = 6
 MAX_DRONES, MAX_GATES, MAX_OBSTACLES, STATE_DIM = 32, 8, 8, 20
 
 F32, F64 = 0, 1
@@ -78,7 +78,7 @@ class ConfigC(C.Structure):
                 ("init_xyz", (d * 3) * MAX_DRONES), ("init_rpy", (d * 3) * MAX_DRONES),
                 ("init_vel", (d * 3) * MAX_DRONES), ("init_pqr", (d * 3) * MAX_DRONES),
                 ("target_pos", (d * 3) * MAX_DRONES), ("drone", DroneParamsC), ("dslpid_drone", DroneParamsC),
-                ("track", TrackC), ("rnd", RandomizationC)]
+                ("track", TrackC), ("rnd", RandomizationC), ("obs_columns", i32), ("reserved0", i32)]
 
 
 def drone_params_c(p: DroneParams, body: DroneParams | None = None) -> DroneParamsC:
@@ -106,7 +106,7 @@ def make_config(*, num_envs, num_drones=1, drone_model=DroneModel.CF2X, physics=
                 ctrl_freq=240, action_type=ACT_RPM_RAW, env_kind=ENV_CTRL, precision=F32, device=0,
                 initial_xyzs=None, initial_rpys=None, initial_vels=None, initial_pqrs=None, target_pos=None,
                 episode_len_sec=8.0, auto_reset=False, race_mode=RaceMode.COMPARE, seed=0, env_offset=0,
-                physics_mask=None, body_model=None, mel_mass=0.027) -> ConfigC:
+                physics_mask=None, body_model=None, mel_mass=0.027, obs_columns=0) -> ConfigC:
     if pyb_freq % ctrl_freq != 0:
         # same check and message as BaseAviary.__init__ (:79-80)
         raise ValueError('[ERROR] in BaseAviary.__init__(), pyb_freq is not divisible by env_freq.')
@@ -126,6 +126,7 @@ def make_config(*, num_envs, num_drones=1, drone_model=DroneModel.CF2X, physics=
     c.bug_compat = 0xFFFFFFFF
     c.g, c.episode_len_sec, c.mel_mass = 9.8, float(episode_len_sec), float(mel_mass)
     c.seed, c.env_offset = int(seed), int(env_offset)
+    c.obs_columns = int(obs_columns)
     xyz = default_init_xyz(p, num_drones) if initial_xyzs is None else initial_xyzs
     rpy = [[0.0] * 3] * num_drones if initial_rpys is None else initial_rpys
     vel = [[0.0] * 3] * num_drones if initial_vels is None else initial_vels

@@ -127,7 +127,7 @@ void derive_params(const adrp_config& c, KParams<T>& P)
     P.N = c.num_envs; P.M = c.drones_per_env; P.Mpad = next_pow2(c.drones_per_env);
     P.S = c.pyb_freq / c.ctrl_freq; P.A = action_dim(c.action_type);
     P.B = (c.env_kind == ADRP_ENV_HOVER || c.env_kind == ADRP_ENV_MULTIHOVER) ? c.ctrl_freq / 2 : 0;   // BaseRLAviary.py:66
-    P.O = c.env_kind == ADRP_ENV_CTRL ? 20 : 12 + P.B * P.A;
+    P.O = c.env_kind == ADRP_ENV_CTRL ? (c.obs_columns == 12 ? 12 : 20) : 12 + P.B * P.A;
     if (c.env_kind == ADRP_ENV_RACE)      // MultiRaceAviary._observationSpace (:291-343)
         P.O = 12 + 5 * c.track.num_gates + 4 * c.track.num_obstacles + 1 + (c.race_mode == ADRP_RACE_COMPETE ? 6 * (c.drones_per_env - 1) : 0);
     P.physics = c.physics; P.drone_model = c.drone_model; P.action_type = c.action_type; P.env_kind = c.env_kind;
@@ -408,6 +408,7 @@ int validate(const adrp_config* c)
     if (c->wrappers & ~(ADRP_WRAP_OBS | ADRP_WRAP_REWARD)) { g_create_error = "unknown bit in wrappers"; return ADRP_EINVAL; }
     if (c->wrappers && c->env_kind != ADRP_ENV_RACE) { g_create_error = "wrappers (utils/wrapper.py) apply to the race env"; return ADRP_EINVAL; }
     if (c->env_kind == ADRP_ENV_RACE && (c->track.num_gates < 0 || c->track.num_gates > ADRP_MAX_GATES || c->track.num_obstacles < 0 || c->track.num_obstacles > ADRP_MAX_OBSTACLES)) { g_create_error = "too many gates / obstacles"; return ADRP_EINVAL; }
+    if (c->obs_columns != 0 && !(c->env_kind == ADRP_ENV_CTRL && (c->obs_columns == 12 || c->obs_columns == 20))) { g_create_error = "obs_columns is 0, 12 or 20, and CtrlAviary-kind envs' only"; return ADRP_EINVAL; }
     if (c->env_kind == ADRP_ENV_HOVER && c->drones_per_env != 1) { g_create_error = "HoverAviary is single-drone"; return ADRP_EINVAL; }
     return ADRP_OK;
 }

@@ -38,6 +38,6 @@ template <int PHY> RaceStepFnF32 race_step_special_dense(int mpad, bool quiet, b
 // all-forces masks (DYN + GND + DRAG + DW = 15, Physics.PYB_GND_DRAG_DW = 30; adrp_step_f32_forces.cu), 1 / 2 / 4 / 8 lanes per env.
 using StepFnF32 = void (*)(KParams<float>, KBuffers<float>, const float*, float*, float*, uint8_t*, uint8_t*, uint8_t*);
 template <int PHY> StepFnF32 step_special(int mpad, bool ctrl);      // NULL: no such instance
-template <int PHY> StepFnF32 step_special_multi(int mpad, bool ctrl);   // adrp_step_n: K control steps per launch
+template <int PHY> StepFnF32 step_special_multi(int mpad, int envk);    // adrp_step_n: K control steps per launch (envk: adrp_step_special.cuh)
 
 }  // namespace adrp

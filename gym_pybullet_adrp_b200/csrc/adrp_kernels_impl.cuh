@@ -119,15 +119,17 @@ cudaError_t Launch<T>::step(const KParams<T>& P, const KBuffers<T>& b, const T* 
     // compiled in their own translation units (step_special)
     if constexpr (M<T>::fast) {
         static const bool generic = [] { const char* e = getenv("ADRP_STEP_GENERIC"); return e && e[0] == '1'; }();   // diagnostic
-        if (!pid && !generic && P.drone_model != ADRP_CF2P) {      // (the instances have the X prop layout compiled in)
+        // (the instances have the X prop layout compiled in; the CtrlAviary-kind n-step ones lack the in-kernel action draw)
+        if (!pid && !generic && P.drone_model != ADRP_CF2P && !(P.act_rng && P.env_kind == ADRP_ENV_CTRL)) {
             StepFnF32 f = nullptr;
             const bool ctrl = P.env_kind == ADRP_ENV_CTRL;
+            const int envk = ctrl ? (P.O == 12 ? 2 : 0) : 1;
             constexpr int ALL = ADRP_PHY_GND | ADRP_PHY_DRAG | ADRP_PHY_DW;
             switch (P.physics) {
-                case ADRP_PHY_DYN: f = multi ? step_special_multi<ADRP_PHY_DYN>(P.Mpad, ctrl) : step_special<ADRP_PHY_DYN>(P.Mpad, ctrl); break;
-                case ADRP_PHY_GROUND: f = multi ? step_special_multi<ADRP_PHY_GROUND>(P.Mpad, ctrl) : step_special<ADRP_PHY_GROUND>(P.Mpad, ctrl); break;
-                case ADRP_PHY_DYN | ALL: f = multi ? step_special_multi<ADRP_PHY_DYN | ALL>(P.Mpad, ctrl) : step_special<ADRP_PHY_DYN | ALL>(P.Mpad, ctrl); break;
-                case ADRP_PHY_GROUND | ALL: f = multi ? step_special_multi<ADRP_PHY_GROUND | ALL>(P.Mpad, ctrl) : step_special<ADRP_PHY_GROUND | ALL>(P.Mpad, ctrl); break;
+                case ADRP_PHY_DYN: f = multi ? step_special_multi<ADRP_PHY_DYN>(P.Mpad, envk) : step_special<ADRP_PHY_DYN>(P.Mpad, ctrl); break;
+                case ADRP_PHY_GROUND: f = multi ? step_special_multi<ADRP_PHY_GROUND>(P.Mpad, envk) : step_special<ADRP_PHY_GROUND>(P.Mpad, ctrl); break;
+                case ADRP_PHY_DYN | ALL: f = multi ? step_special_multi<ADRP_PHY_DYN | ALL>(P.Mpad, envk) : step_special<ADRP_PHY_DYN | ALL>(P.Mpad, ctrl); break;
+                case ADRP_PHY_GROUND | ALL: f = multi ? step_special_multi<ADRP_PHY_GROUND | ALL>(P.Mpad, envk) : step_special<ADRP_PHY_GROUND | ALL>(P.Mpad, ctrl); break;
                 default: break;
             }
             if (f) { launch_pdl(f, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl); return cudaGetLastError(); }

@@ -96,7 +96,8 @@ __device__ __forceinline__ int group_or(int v, int Mpad)
 
 // PHY_CT >= 0: physics mask known at compile time (specialised kernels); -1: read from the params.
 // ACTC: 0 = RPM-type actions, 1 = DSLPID-type actions.  MP: lanes per env (0 = read from the params).
-// ENVK: -1 = env kind read from the params; 0 = CtrlAviary-kind (20-float rows, no reward / action buffer) compiled in;
+// ENVK: -1 = env kind read from the params; 0 = CtrlAviary-kind (20-float rows, no reward / action buffer) compiled in
+// (2: the same with the 12-column row of adrp_config.obs_columns, n-step instances only);
 // 1 = an RL aviary (Hover / MultiHover, told apart at run time) compiled in.  The epilogues of the two families differ
 // a lot (5 stores vs. the action-buffer copy), and the registers of the larger one count for the whole kernel.
 // MULTI: adrp_step_n instances -- P.K control steps per launch (the single-step instances compile the loop away and are
@@ -120,7 +121,7 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
     const bool valid = env < P.env_end && i < P.M;
     const long long D = P.Dpad;
     const int phy = PHY_CT >= 0 ? PHY_CT : P.physics;
-    const bool is_ctrl = ENVK == 0 ? true : (ENVK == 1 ? false : P.env_kind == ADRP_ENV_CTRL);
+    const bool is_ctrl = (ENVK == 0 || ENVK == 2) ? true : (ENVK == 1 ? false : P.env_kind == ADRP_ENV_CTRL);
     constexpr int kRingBatch = ENVK == 1 ? 8 : kRingBatchGeneric;
     const long long od = valid ? env * P.M + i : 0;      // row of this drone in (N, M, .) tensors
     pdl_wait();
@@ -151,7 +152,10 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
     const T* a = action + (long long)kv * P.act_step + od * P.A;
     constexpr int AMAX = ACTC == 0 ? 4 : 12;             // RPM-type actions have at most 4 components
     T act_in[AMAX];
-    if (MULTI && P.act_rng) {                                 // a random policy's draw, made here (KParams::act_rng)
+    // a random policy's draw, made here (KParams::act_rng).  Not compiled into the CtrlAviary-kind instances (their actions are
+    // RPMs, not Box(-1, 1) samples; the draw's registers cost the C4 / C5 n-step instances 3 - 5 %): such a handle runs the
+    // generic instance for it (Launch::step)
+    if (MULTI && ENVK != 0 && ENVK != 2 && P.act_rng) {
         uint32_t o[4];
         philox4x32((uint32_t)(P.env_offset + (unsigned long long)env), (uint32_t)(192 + i), P.rng_step0 + (uint32_t)ks, 0u, P.rng_lo, P.rng_hi, o);
 #pragma unroll
@@ -274,14 +278,29 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
     // fp32 build: rows whose length is a multiple of 4 floats go out as 16-byte stores (a warp's scalar store of one
     // column touches 32 sectors for 128 useful bytes; the float4 form moves 4x the payload per sector access)
     const bool vec = M<T>::fast && P.obs_vec;
+    // (the run-time choice of the 12-column row is not compiled into the CtrlAviary-kind n-step instances: there it moves ptxas
+    // from 93 to 84 registers and C5's adrp_step_n rate from 1.468e10 to 1.432e10; ENVK = 2 are the n-step instances of that row)
+    constexpr bool kObs12 = !(MULTI && ENVK == 0);
+    const bool row12 = ENVK == 2 ? true : (kObs12 && P.O == 12);
     if (is_ctrl) {
         if (valid && vec) {
             float4* o4 = reinterpret_cast<float4*>(o);
-            o4[0] = make_float4((float)d.p.x, (float)d.p.y, (float)d.p.z, (float)d.q.x);
-            o4[1] = make_float4((float)d.q.y, (float)d.q.z, (float)d.q.w, (float)rpy.x);
-            o4[2] = make_float4((float)rpy.y, (float)rpy.z, (float)d.v.x, (float)d.v.y);
-            o4[3] = make_float4((float)d.v.z, (float)d.w.x, (float)d.w.y, (float)d.w.z);
-            o4[4] = make_float4((float)d.last_rpm[0], (float)d.last_rpm[1], (float)d.last_rpm[2], (float)d.last_rpm[3]);
+            const float4 kin1 = make_float4((float)rpy.y, (float)rpy.z, (float)d.v.x, (float)d.v.y);
+            const float4 kin2 = make_float4((float)d.v.z, (float)d.w.x, (float)d.w.y, (float)d.w.z);
+            if (row12) {                                       // adrp_config.obs_columns = 12: the kinematic columns only
+                o4[0] = make_float4((float)d.p.x, (float)d.p.y, (float)d.p.z, (float)rpy.x);
+                o4[1] = kin1;
+                o4[2] = kin2;
+            } else {
+                o4[0] = make_float4((float)d.p.x, (float)d.p.y, (float)d.p.z, (float)d.q.x);
+                o4[1] = make_float4((float)d.q.y, (float)d.q.z, (float)d.q.w, (float)rpy.x);
+                o4[2] = kin1;
+                o4[3] = kin2;
+                o4[4] = make_float4((float)d.last_rpm[0], (float)d.last_rpm[1], (float)d.last_rpm[2], (float)d.last_rpm[3]);
+            }
+        } else if (valid && row12) {
+            o[0] = d.p.x; o[1] = d.p.y; o[2] = d.p.z; o[3] = rpy.x; o[4] = rpy.y; o[5] = rpy.z;
+            o[6] = d.v.x; o[7] = d.v.y; o[8] = d.v.z; o[9] = d.w.x; o[10] = d.w.y; o[11] = d.w.z;
         } else if (valid) {
             o[0] = d.p.x; o[1] = d.p.y; o[2] = d.p.z; o[3] = d.q.x; o[4] = d.q.y; o[5] = d.q.z; o[6] = d.q.w;
             o[7] = rpy.x; o[8] = rpy.y; o[9] = rpy.z; o[10] = d.v.x; o[11] = d.v.y; o[12] = d.v.z;
@@ -430,7 +449,10 @@ __global__ void reset_kernel(const KParams<T> P, KBuffers<T> b, const uint8_t* _
     if (obs) {
         T* o = obs + (env * P.M + i) * P.O;
         const V3<T> rpy = euler_rpy(d.q);
-        if (P.env_kind == ADRP_ENV_CTRL) {
+        if (P.env_kind == ADRP_ENV_CTRL && P.O == 12) {        // adrp_config.obs_columns = 12
+            o[0] = d.p.x; o[1] = d.p.y; o[2] = d.p.z; o[3] = rpy.x; o[4] = rpy.y; o[5] = rpy.z;
+            o[6] = d.v.x; o[7] = d.v.y; o[8] = d.v.z; o[9] = d.w.x; o[10] = d.w.y; o[11] = d.w.z;
+        } else if (P.env_kind == ADRP_ENV_CTRL) {
             o[0] = d.p.x; o[1] = d.p.y; o[2] = d.p.z; o[3] = d.q.x; o[4] = d.q.y; o[5] = d.q.z; o[6] = d.q.w;
             o[7] = rpy.x; o[8] = rpy.y; o[9] = rpy.z; o[10] = d.v.x; o[11] = d.v.y; o[12] = d.v.z;
             o[13] = d.w.x; o[14] = d.w.y; o[15] = d.w.z; o[16] = o[17] = o[18] = o[19] = T(0);

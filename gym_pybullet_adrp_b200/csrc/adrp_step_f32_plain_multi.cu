@@ -1,5 +1,5 @@
 // fp32 product build of step_kernel, adrp_step_n instances (K control steps per launch) of the plain masks.
 #define ADRP_MULTI_TU
 #include "adrp_step_special.cuh"
-template adrp::StepFnF32 adrp::step_special_multi<1>(int, bool);
-template adrp::StepFnF32 adrp::step_special_multi<16>(int, bool);
+template adrp::StepFnF32 adrp::step_special_multi<1>(int, int);
+template adrp::StepFnF32 adrp::step_special_multi<16>(int, int);

@@ -30,7 +30,13 @@ StepFnF32 step_special_impl(int mpad, bool ctrl)
     return nullptr;
 }
 #ifdef ADRP_MULTI_TU
-template <int PHY> StepFnF32 step_special_multi(int mpad, bool ctrl) { return step_special_impl<PHY, true>(mpad, ctrl); }
+// envk: 0 = CtrlAviary-kind, 1 = RL aviary, 2 = CtrlAviary-kind with the 12-column observation row (adrp_config.obs_columns)
+// compiled in -- its own instances, because the run-time choice of the row moves the allocation of the 20-column ones (step_kernel)
+template <int PHY> StepFnF32 step_special_multi(int mpad, int envk)
+{
+    if (envk == 2) return step_special_mp<PHY, 2, true>(mpad);
+    return step_special_impl<PHY, true>(mpad, envk == 0);
+}
 #else
 template <int PHY> StepFnF32 step_special(int mpad, bool ctrl) { return step_special_impl<PHY, false>(mpad, ctrl); }
 #endif

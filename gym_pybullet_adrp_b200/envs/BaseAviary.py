@@ -27,7 +27,8 @@ class BaseAviary:
                  initial_xyzs=None, initial_rpys=None, physics: Physics = Physics.PYB, pyb_freq: int = 240,
                  ctrl_freq: int = 240, gui=False, record=False, obstacles=False, user_debug_gui=True,
                  vision_attributes=False, output_folder='results', *, num_envs: int = 1, device: int = 0,
-                 precision: str = "fp32", auto_reset: bool | None = None, seed: int = 0, env_offset: int = 0):
+                 precision: str = "fp32", auto_reset: bool | None = None, seed: int = 0, env_offset: int = 0,
+                 obs_columns: int = 0):
         if gui or record or vision_attributes:
             raise NotImplementedError("GUI / video / camera observations need a graphics stack: unavailable on this box")
         #### Constants (BaseAviary.py:74-128) ######################
@@ -72,6 +73,7 @@ class BaseAviary:
         self.PRECISION = {"fp32": _abi.F32, "fp64": _abi.F64}[precision]
         self._auto_reset = (self.NUM_ENVS > 1) if auto_reset is None else bool(auto_reset)
         self._seed, self._env_offset = int(seed), int(env_offset)
+        self._obs_columns = int(obs_columns)               # CtrlAviary-kind: 12 = the kinematic columns only (adrp_config.obs_columns)
         self._single = self.NUM_ENVS == 1
         self._handle = None
         self.CLIENT = -1                                   # there is no PyBullet client
@@ -87,7 +89,8 @@ class BaseAviary:
                                 action_type=self.ACTION_TYPE, env_kind=self.ENV_KIND, precision=self.PRECISION,
                                 device=self.DEVICE, initial_xyzs=self.INIT_XYZS.tolist(), initial_rpys=self.INIT_RPYS.tolist(),
                                 target_pos=self._target_pos(), episode_len_sec=getattr(self, "EPISODE_LEN_SEC", 8.0),
-                                auto_reset=self._auto_reset, seed=self._seed, env_offset=self._env_offset)
+                                auto_reset=self._auto_reset, seed=self._seed, env_offset=self._env_offset,
+                                obs_columns=self._obs_columns)
 
     def _target_pos(self):
         return None

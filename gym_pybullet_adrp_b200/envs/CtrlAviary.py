@@ -33,4 +33,7 @@ class CtrlAviary(BaseAviary):
         hi = np.array([[np.inf, np.inf, np.inf, 1., 1., 1., 1., np.pi, np.pi, np.pi, np.inf, np.inf, np.inf,
                         np.inf, np.inf, np.inf, self.MAX_RPM, self.MAX_RPM, self.MAX_RPM, self.MAX_RPM]
                        for _ in range(self.NUM_DRONES)])
+        if self._obs_columns == 12:                        # [pos3, rpy3, vel3, ang_vel3] (not in the reference: obs_columns=12)
+            keep = [0, 1, 2, 7, 8, 9, 10, 11, 12, 13, 14, 15]
+            lo, hi = lo[:, keep], hi[:, keep]
         return Box(low=lo, high=hi, dtype=np.float64 if self.PRECISION == _abi.F64 else np.float32)

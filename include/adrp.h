@@ -18,7 +18,7 @@
 extern "C" {
 #endif
 
-#define ADRP_ABI_VERSION 5
+#define ADRP_ABI_VERSION 6
 #define ADRP_MAX_DRONES 32      /* drones per env: one env lives inside one warp */
 #define ADRP_MAX_GATES 8
 #define ADRP_MAX_OBSTACLES 8
@@ -154,6 +154,12 @@ typedef struct adrp_config {
     adrp_drone_params dslpid_drone;        /* URDF constants the DSLPID controller reads (BaseControl.py:35-39) */
     adrp_track track;
     adrp_randomization rnd;
+    /* CtrlAviary-kind envs: 0 or 20 = the reference's 20-float row of _getDroneStateVector (envs/CtrlAviary.py:106-117,
+     * BaseAviary.py:545-565); 12 = only its kinematic columns [pos3, rpy3, vel3, ang_vel3] -- the twelve that
+     * BaseRLAviary._computeObs picks from it (:310-317) -- for callers who do not read quaternion and last RPM: 40 % less
+     * observation traffic to HBM and over PCIe.  Other env kinds: must be 0. */
+    int32_t obs_columns;
+    int32_t reserved0;            /* 0 */
 } adrp_config;
 
 typedef struct adrp_handle adrp_handle;

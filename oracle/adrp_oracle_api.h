@@ -10,7 +10,7 @@ static FN(orc)* FN(create)(const adrp_config* c)
     h->N = c->num_envs; h->M = c->drones_per_env; h->S = c->pyb_freq / c->ctrl_freq;
     h->A = FN(action_dim)(c->action_type);
     h->B = c->env_kind == ADRP_ENV_HOVER || c->env_kind == ADRP_ENV_MULTIHOVER ? c->ctrl_freq / 2 : 0;   /* BaseRLAviary.py:66 */
-    if (c->env_kind == ADRP_ENV_CTRL) h->O = 20;
+    if (c->env_kind == ADRP_ENV_CTRL) h->O = c->obs_columns == 12 ? 12 : 20;
     else if (c->env_kind == ADRP_ENV_RACE) h->O = 49 + (c->race_mode == ADRP_RACE_COMPETE ? 6 * (h->M - 1) : 0);
     else h->O = 12 + h->B * h->A;
     size_t D = (size_t)h->N * h->M;

@@ -332,3 +332,61 @@ def test_auto_reset_and_truncation():
     assert truncations >= 8                              # 0.5 s episodes at 30 Hz: every env is truncated at least twice
     np.testing.assert_allclose(h.get_state().cpu().numpy(), o.get_state(), atol=1e-5)
     h.close(); o.close()
+
+
+KIN12 = [0, 1, 2, 7, 8, 9, 10, 11, 12, 13, 14, 15]
+
+
+@pytest.mark.parametrize("precision", [_abi.F64, _abi.F32])
+@pytest.mark.parametrize("physics,M", [(Physics.DYN_GND_DRAG_DW, 8), (Physics.PYB_GND_DRAG_DW, 3), (Physics.PYB, 1)])
+def test_obs_columns_12(physics, M, precision):
+    """adrp_config.obs_columns = 12 (CtrlAviary-kind): the kernel writes only [pos3, rpy3, vel3, ang_vel3] -- exactly the
+    twelve columns of the 20-float row that a twin handle writes (bit for bit, both builds: the same instance runs both), the
+    same through adrp_step_host, adrp_step_n and adrp_reset, and the oracle's 12-column row within the usual bounds."""
+    import torch
+    N = 130
+    rng = np.random.default_rng(M)
+    xyz = [[1.2 * (k % 3), 1.2 * (k // 3), 0.5 + 0.25 * (k % 4)] for k in range(M)]
+    mk = lambda cols: _abi.make_config(num_envs=N, num_drones=M, physics=physics, pyb_freq=240, ctrl_freq=30,   # noqa: E731
+                                       action_type=_abi.ACT_RPM_RAW, env_kind=_abi.ENV_CTRL, precision=precision,
+                                       initial_xyzs=xyz, obs_columns=cols)
+    full, kin, host, multi, o = _handle(mk(0)), _handle(mk(12)), _handle(mk(12)), _handle(mk(12)), OracleEnv(mk(12))
+    assert full.O == 20 and kin.O == 12
+    assert torch.equal(full.reset()[..., KIN12], kin.reset())
+    o.reset()
+    hover = float(np.sqrt(9.8 * 0.03454 / (4 * 3.16e-10)))
+    acts = hover * (1 + 0.005 * rng.uniform(-1, 1, (10, N, M, 4)))
+    for k in range(10):
+        of = [t.clone() for t in full.step(acts[k])]
+        ok = [t.clone() for t in kin.step(acts[k])]
+        assert torch.equal(of[0][..., KIN12], ok[0])
+        for x, y in zip(of[1:], ok[1:]):
+            assert torch.equal(x, y)
+        oh = host.step_host(acts[k].astype(host.np_dtype))
+        np.testing.assert_array_equal(oh[0], ok[0].cpu().numpy())
+        oc = o.step(acts[k], nthreads=4)[0]
+        if precision == _abi.F64:
+            assert gc.rel_err(ok[0].cpu().numpy(), oc) < 1e-9
+        else:
+            assert np.abs(ok[0].cpu().numpy() - oc).max() < 1e-4
+    om = multi.step_n(acts, keep_outputs=True)[0]
+    assert tuple(om.shape) == (10, N, M, 12)
+    if precision == _abi.F64:
+        assert torch.equal(om[-1], kin.obs)
+    else:
+        assert (om[-1] - kin.obs).abs().max().item() < 2e-5
+    for h in (full, kin, host, multi):
+        h.close()
+    o.close()
+
+
+def test_obs_columns_is_ctrl_aviary_only():
+    from gym_pybullet_adrp_b200 import _lib
+    cfg = _abi.make_config(num_envs=4, num_drones=1, physics=Physics.PYB, pyb_freq=240, ctrl_freq=30, action_type=_abi.ACT_RPM,
+                           env_kind=_abi.ENV_HOVER, precision=_abi.F32, obs_columns=12)
+    with pytest.raises(Exception, match="obs_columns"):
+        _lib.Handle(cfg)
+    cfg = _abi.make_config(num_envs=4, num_drones=1, physics=Physics.PYB, pyb_freq=240, ctrl_freq=30,
+                           action_type=_abi.ACT_RPM_RAW, env_kind=_abi.ENV_CTRL, precision=_abi.F32, obs_columns=13)
+    with pytest.raises(Exception, match="obs_columns"):
+        _lib.Handle(cfg)

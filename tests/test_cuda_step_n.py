@@ -191,18 +191,20 @@ def _random_policy_cfg(case, precision, N, env_offset=0):
         return _abi.make_race_config(rc, num_envs=N, num_drones=2, physics=Physics.PYB, racemode=RaceMode.COMPETE,
                                      precision=precision, seed=0x1234567812345, auto_reset=True, env_offset=env_offset), 2, 4
     kind, M, act, A = {"hover_rpm": (_abi.ENV_HOVER, 1, _abi.ACT_RPM, 4), "multihover_one_d": (_abi.ENV_MULTIHOVER, 3, _abi.ACT_ONE_D_RPM, 1),
-                       "hover_pid": (_abi.ENV_HOVER, 1, _abi.ACT_PID, 3), "multihover_vel": (_abi.ENV_MULTIHOVER, 2, _abi.ACT_VEL, 4)}[case]
+                       "hover_pid": (_abi.ENV_HOVER, 1, _abi.ACT_PID, 3), "multihover_vel": (_abi.ENV_MULTIHOVER, 2, _abi.ACT_VEL, 4),
+                       "ctrl_vel": (_abi.ENV_CTRL, 2, _abi.ACT_VEL, 4), "ctrl_rpm": (_abi.ENV_CTRL, 2, _abi.ACT_RPM, 4)}[case]
     return _abi.make_config(num_envs=N, num_drones=M, physics=Physics.PYB, pyb_freq=240, ctrl_freq=30, action_type=act, env_kind=kind,
                             precision=precision, auto_reset=True, episode_len_sec=0.4, seed=0x1234567812345, env_offset=env_offset), M, A
 
 
 @pytest.mark.parametrize("precision", [_abi.F32, _abi.F64])
-@pytest.mark.parametrize("case", ["hover_rpm", "multihover_one_d", "hover_pid", "multihover_vel", "race"])
+@pytest.mark.parametrize("case", ["hover_rpm", "multihover_one_d", "hover_pid", "multihover_vel", "race", "ctrl_vel", "ctrl_rpm"])
 def test_random_policy_drawn_in_the_kernel(case, precision):
     """ADRP_ACTIONS_PHILOX (step_n(None, K)): the launch that draws its own U[-1, 1) actions equals, bit for bit in both builds
     (the same kernel instance runs both), the launch that is handed those actions -- computed here by the NumPy Philox of
     tests/philox_np.py (pinned to Random123's known answers on the CPU side); two calls in a row continue the counter, a
-    shard draws the rows of the whole batch, and set_rollout_step replays."""
+    shard draws the rows of the whole batch, and set_rollout_step replays.  (ctrl_rpm, fp32: a CtrlAviary-kind handle draws on
+    the generic instance -- its specialised ones do not carry the draw -- so that one comparison is to rounding, 2e-5.)"""
     import torch
     from tests.philox_np import random_policy_actions
     N, K1, K2, off = 96, 7, 5, 1000
@@ -210,15 +212,23 @@ def test_random_policy_drawn_in_the_kernel(case, precision):
     a, b = _handle(cfg), _handle(cfg)
     a.reset(); b.reset()
     want_actions = random_policy_actions(cfg.seed, off, N, M, A, 0, K1 + K2)
+    loose = case == "ctrl_rpm" and precision == _abi.F32
+
+    def same(x, y):
+        if loose and x.is_floating_point():
+            assert ((x - y).abs() / x.abs().clamp(min=1.0)).max().item() < 2e-5
+        else:
+            assert torch.equal(x, y), (x != y).nonzero()[:4]
+
     got = a.step_n(None, n_steps=K1, keep_outputs=True)
     want = b.step_n(want_actions[:K1], keep_outputs=True)
     for x, y in zip(got, want):
-        assert torch.equal(x, y), (x != y).nonzero()[:4]
+        same(x, y)
     got = a.step_n(None, n_steps=K2, keep_outputs=True)           # continues at rollout step K1
     want = b.step_n(want_actions[K1:], keep_outputs=True)
     for x, y in zip(got, want):
-        assert torch.equal(x, y)
-    assert torch.equal(a.get_state(), b.get_state())
+        same(x, y)
+    same(a.get_state(), b.get_state())
     # a shard of the batch (env_offset = global index of its first env) reproduces those rows
     lo, hi = 32, 64
     cfg_s, _, _ = _random_policy_cfg(case, precision, hi - lo, off + lo)
@@ -235,7 +245,7 @@ def test_random_policy_drawn_in_the_kernel(case, precision):
     r1.reset(); r2.reset()
     r1.set_rollout_step(5)
     for x, y in zip(r1.step_n(None, n_steps=3), r2.step_n(want_actions[5:8])):
-        assert torch.equal(x, y)
+        same(x, y)
     r1.step_n(None, n_steps=1)                                    # K = 1, no action buffer at all
     r1.close(); r2.close()
     for h in (a, b, s, w):

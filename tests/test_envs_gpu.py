@@ -121,6 +121,25 @@ def test_env_step_n_reproduces_the_golden_run_in_one_launch_and_draws_a_random_p
     env.close(); other.close()
 
 
+def test_ctrl_aviary_kinematic_columns_only():
+    """CtrlAviary(obs_columns=12): (NUM_DRONES, 12) rows [pos, rpy, vel, ang_vel] = those columns of the reference's 20."""
+    from gym_pybullet_adrp_b200.envs import CtrlAviary
+    xyz = np.array([[0.0, 0.0, 0.5], [0.6, 0.0, 0.7]])
+    full = CtrlAviary(num_drones=2, physics=Physics.PYB_GND_DRAG_DW, pyb_freq=240, ctrl_freq=48, initial_xyzs=xyz, precision="fp64")
+    kin = CtrlAviary(num_drones=2, physics=Physics.PYB_GND_DRAG_DW, pyb_freq=240, ctrl_freq=48, initial_xyzs=xyz, precision="fp64",
+                     obs_columns=12)
+    assert kin.observation_space.shape == (2, 12) and full.observation_space.shape == (2, 20)
+    keep = [0, 1, 2, 7, 8, 9, 10, 11, 12, 13, 14, 15]
+    of, _ = full.reset()
+    ok, _ = kin.reset()
+    assert ok.shape == (2, 12) and np.array_equal(of[:, keep], ok)
+    for k in range(10):
+        a = np.full((2, 4), 14500.0 + 30 * k)
+        of, ok = full.step(a)[0], kin.step(a)[0]
+        assert np.array_equal(of[:, keep], ok)
+    full.close(); kin.close()
+
+
 def test_multi_race_aviary_matches_reference_run():
     """scripts/sim.py-style loop on the reference's own race run (level3, COMPARE), draws and disturbances injected."""
     meta, z = gc.load("race_pyb_compare_level3")

@@ -241,3 +241,28 @@ def test_flop_table_is_the_mechanical_count():
         got = (r["per_substep_update"]["flops"], r["per_substep_update"]["sfu"], r["per_control_step"]["flops"], r["per_control_step"]["sfu"])
         for g, w in zip(got, (sub_f, sub_s, step_f, step_s)):
             assert abs(g - w) <= 0.01 * max(abs(w), 10.0), (wl, got)
+
+
+KIN12 = [0, 1, 2, 7, 8, 9, 10, 11, 12, 13, 14, 15]
+
+
+@pytest.mark.parametrize("precision", [_abi.F32, _abi.F64])
+def test_obs_columns_12_is_the_kinematic_part_of_the_reference_row(precision):
+    """adrp_config.obs_columns = 12 (CtrlAviary-kind; no counterpart in the reference): columns [pos3, rpy3, vel3, ang_vel3] of
+    the 20-float _getDroneStateVector row (BaseAviary.py:545-565), in that order -- the oracle's two rows side by side."""
+    from gym_pybullet_adrp_b200.utils.enums import Physics
+    rng = np.random.default_rng(12)
+    N, M = 3, 4
+    xyz = [[0.8 * k, 0.3 * k, 0.4 + 0.2 * k] for k in range(M)]
+    mk = lambda cols: OracleEnv(_abi.make_config(num_envs=N, num_drones=M, physics=Physics.PYB_GND_DRAG_DW, pyb_freq=240,   # noqa: E731
+                                                 ctrl_freq=48, action_type=_abi.ACT_RPM_RAW, env_kind=_abi.ENV_CTRL,
+                                                 precision=precision, initial_xyzs=xyz, obs_columns=cols))
+    full, kin = mk(0), mk(12)
+    assert full.O == 20 and kin.O == 12 and mk(20).O == 20
+    assert np.array_equal(full.reset()[..., KIN12], kin.reset())
+    for _ in range(12):
+        a = 14468.0 * (1 + 0.05 * rng.uniform(-1, 1, (N, M, 4)))
+        of, ok = full.step(a), kin.step(a)
+        assert np.array_equal(of[0][..., KIN12], ok[0])
+        for x, y in zip(of[1:], ok[1:]):
+            assert np.array_equal(x, y)
