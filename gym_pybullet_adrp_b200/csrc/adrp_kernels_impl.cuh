@@ -239,7 +239,7 @@ cudaError_t Launch<T>::race_step(const KParams<T>& P, const RaceParams<T>& RP, c
     static const int force_dense = [] { const char* e = getenv("ADRP_RACE_DENSE"); return e ? (e[0] == '0' ? 0 : 1) : -1; }();
     const bool quiet_launch = !noise && !RP.disturbances;
     const bool dense = force_dense >= 0 ? force_dense == 1 : quiet_launch;
-    launch_pdl(race_step_fn<T>(P.Mpad, P.action_type, !noise && !RP.disturbances, P.physics, P.K > 1 || P.act_rng, dense),
+    launch_pdl(race_step_fn<T>(P.Mpad, P.action_type, quiet_launch, noise ? -1 : P.physics, P.K > 1 || P.act_rng, dense),
                threads, kRaceBlock,
                race_smem_bytes(P, RP, kRaceBlock), s, P, RP, b, rb, action, noise, obs, reward, te, tr, fl);
     return cudaGetLastError();
