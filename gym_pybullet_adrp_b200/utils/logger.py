@@ -46,5 +46,24 @@ class Logger:
             np.savez(out_file, timestamps=self.timestamps, states=self.states, controls=self.controls)
         return path
 
+    def save_as_csv(self, comment: str = ""):
+        """logger.py:131-201: a folder ``save-flight-<comment>-<date>`` with one two-column (time, value) CSV per logged
+        quantity and drone -- x y z, r p ya (+ their finite-difference rates rr pr yar), vx vy vz, wx wy wz, rpm0-3, pwm0-3."""
+        csv_dir = os.path.join(self.OUTPUT_FOLDER, "save-flight-" + comment + "-" + datetime.now().strftime("%m.%d.%Y_%H.%M.%S"))
+        os.makedirs(csv_dir, exist_ok=True)
+        t = np.arange(0, self.timestamps.shape[1] / self.LOGGING_FREQ_HZ, 1 / self.LOGGING_FREQ_HZ)[:self.timestamps.shape[1]]
+        rows = {"x": 0, "y": 1, "z": 2, "r": 6, "p": 7, "ya": 8, "vx": 3, "vy": 4, "vz": 5, "wx": 9, "wy": 10, "wz": 11}
+        for i in range(self.NUM_DRONES):
+            cols = {name + str(i): self.states[i, k, :] for name, k in rows.items()}
+            for name, k in (("rr", 6), ("pr", 7), ("yar", 8)):             # rates of the logged angles (:161-169)
+                cols[name + str(i)] = np.hstack([0, np.diff(self.states[i, k, :]) * self.LOGGING_FREQ_HZ])
+            for m in range(4):
+                cols[f"rpm{m}-{i}"] = self.states[i, 12 + m, :]
+                cols[f"pwm{m}-{i}"] = (self.states[i, 12 + m, :] - 4070.3) / 0.2685
+            for name, v in cols.items():
+                with open(os.path.join(csv_dir, name + ".csv"), "wb") as out_file:
+                    np.savetxt(out_file, np.transpose(np.vstack([t, v])), delimiter=",")
+        return csv_dir
+
     def plot(self, pwm=False):
         raise NotImplementedError("Logger.plot needs matplotlib and a display: unavailable on this box")

@@ -36,3 +36,15 @@ def load_controller(path, class_name: str = None):
     spec.loader.exec_module(module)
     assert hasattr(module, class_name), f"{path} does not define {class_name}"
     return getattr(module, class_name)
+
+
+def str2bool(val):
+    """utils/utils.py:70-91: argparse helper, the strings the reference's example scripts accept for a Boolean."""
+    if isinstance(val, bool):
+        return val
+    if str(val).lower() in ("yes", "true", "t", "y", "1"):
+        return True
+    if str(val).lower() in ("no", "false", "f", "n", "0"):
+        return False
+    import argparse
+    raise argparse.ArgumentTypeError("[ERROR] in str2bool(), a Boolean value is expected")
