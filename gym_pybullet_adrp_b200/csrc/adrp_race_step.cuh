@@ -186,12 +186,13 @@ race_step_kernel(const __grid_constant__ KParams<T> P, const __grid_constant__ R
     if (restage) {
         const long long env0 = (long long)P.env_begin + (long long)blockIdx.x * EPB;
         const int total = RP.TF * EPB;
+        const int epb_log2 = 31 - __clz(EPB);
         for (int base = threadIdx.x; base < total; base += 6 * nthr) {
             T v[6];
 #pragma unroll
             for (int u = 0; u < 6; ++u) {
                 const int idx = base + u * nthr;
-                const int f = idx / EPB, el = idx - f * EPB;
+                const int f = idx >> epb_log2, el = idx & (EPB - 1);              // (EPB: block size / lanes per env, powers of two)
                 v[u] = (idx < total && env0 + el < P.N) ? rb.track[(long long)f * P.N + env0 + el] : T(0);
             }
 #pragma unroll
