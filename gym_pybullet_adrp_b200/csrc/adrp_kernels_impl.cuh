@@ -19,14 +19,21 @@ static_assert(kBlock == 128, "adrp_api.cu cuts host-path chunks in units of 128-
 // 7 per SM at most (448 threads); C3's 32 768 threads are 4 x 64 vs 7 x 32.  The kernels index with blockDim.x.
 // ADRP_BLOCK=<n> forces a size (diagnostic).
 // Programmatic stream serialisation (see pdl_wait in adrp_step.cuh) when the grid is longer than one wave: the next
-// step's blocks then fill the slots the last wave frees (C4 +13 %, C5 +2 %).  A grid that fits one wave launches plainly:
-// its dependents would be placed into whatever slots the running grid leaves, unevenly over the SMs (measured: C2 -17 %,
-// C3 -13 %).  ADRP_PDL=0 in the environment switches it off altogether.
+// step's blocks then fill the slots the last wave frees (C4 +13 %, C5 +2 %).  A grid that fits one wave, launched that way as
+// it is, has its dependents placed into whatever slots the running grid leaves, unevenly over the SMs (measured: C2 -17 %,
+// C3 -13 %).  Single-step launches of such a grid are therefore padded with dynamic shared memory until an SM holds exactly
+// ceil(blocks / SMs) blocks: the dependents can only take the slots of blocks that exit, spread like them, and wait at
+// griddepcontrol.wait already resident when the grid before them drains -- the launch gap is gone (C2 4.56e9 -> 5.65e9, C3
+// +3 %, C1 +2 %).  The padding takes L1 capacity, which the long n-step launches (no gap to hide) would only pay for
+// (C2 adrp_step_n -1.7 %): they launch plainly.  ADRP_PDL_ONEWAVE=0 switches this off, ADRP_PDL=0 every programmatic launch.
+constexpr size_t kPadBudget = 200 * 1024;   // dynamic shared memory per SM handed out as padding (of 227 KB usable)
 template <typename... KArgs, typename... Args>
-inline void launch_pdl(void (*kernel)(KArgs...), long long threads, unsigned block_max, size_t smem_at_max, cudaStream_t s, Args... args)
+inline void launch_pdl(void (*kernel)(KArgs...), long long threads, unsigned block_max, size_t smem_at_max, cudaStream_t s, bool single_step,
+                       Args... args)
 {
     static const bool enabled = [] { const char* e = getenv("ADRP_PDL"); return !e || e[0] != '0'; }();
     static const int forced = [] { const char* e = getenv("ADRP_BLOCK"); return e ? atoi(e) : 0; }();
+    static const bool onewave_pdl = [] { const char* e = getenv("ADRP_PDL_ONEWAVE"); return !e || e[0] != '0'; }();
     static std::mutex mu;
     struct Info { long long wave; int sms; };
     static std::map<std::pair<const void*, int>, Info> cache;     // (kernel, device) -> resident blocks at block_max, SMs
@@ -40,6 +47,7 @@ inline void launch_pdl(void (*kernel)(KArgs...), long long threads, unsigned blo
         if (it == cache.end()) {
             int per_sm = 0, sms = 0;
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, (int)block_max, smem_at_max);
+            cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPadBudget);   // (the padding below)
             cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
             it = cache.emplace(key, Info{(long long)per_sm * sms, sms}).first;
         }
@@ -62,11 +70,17 @@ inline void launch_pdl(void (*kernel)(KArgs...), long long threads, unsigned blo
     cfg.blockDim = dim3(block, 1, 1);
     cfg.dynamicSmemBytes = smem_at_max * block / block_max;
     cfg.stream = s;
+    bool pdl = enabled && !one_wave;
+    if (enabled && one_wave && onewave_pdl && single_step && info.sms > 0) {
+        const long long per_sm = (cfg.gridDim.x + info.sms - 1) / info.sms;
+        const size_t pad = (kPadBudget / (size_t)per_sm) & ~(size_t)1023;
+        if (pad > cfg.dynamicSmemBytes) { cfg.dynamicSmemBytes = pad; pdl = true; }
+    }
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = (enabled && !one_wave) ? 1 : 0;
+    cfg.numAttrs = pdl ? 1 : 0;
     cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
 
@@ -132,14 +146,14 @@ cudaError_t Launch<T>::step(const KParams<T>& P, const KBuffers<T>& b, const T* 
                 case ADRP_PHY_GROUND | ALL: f = multi ? step_special_multi<ADRP_PHY_GROUND | ALL>(P.Mpad, envk) : step_special<ADRP_PHY_GROUND | ALL>(P.Mpad, ctrl); break;
                 default: break;
             }
-            if (f) { launch_pdl(f, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl); return cudaGetLastError(); }
+            if (f) { launch_pdl(f, grid, kStepBlock, 0, s, !multi, P, b, action, obs, reward, te, tr, fl); return cudaGetLastError(); }
         }
     }
-#define ADRP_LAUNCH_STEP(MP) launch_pdl(step_kernel<T, -1, 0, MP>, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl)
+#define ADRP_LAUNCH_STEP(MP) launch_pdl(step_kernel<T, -1, 0, MP>, grid, kStepBlock, 0, s, true, P, b, action, obs, reward, te, tr, fl)
     if (multi) {                                              // generic instances with the control-step loop
-        if (pid) launch_pdl(step_kernel<T, -1, 1, 0, -1, true>, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl);
-        else launch_pdl(step_kernel<T, -1, 0, 0, -1, true>, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl);
-    } else if (pid) launch_pdl(step_kernel<T, -1, 1, 0>, grid, kStepBlock, 0, s, P, b, action, obs, reward, te, tr, fl);
+        if (pid) launch_pdl(step_kernel<T, -1, 1, 0, -1, true>, grid, kStepBlock, 0, s, false, P, b, action, obs, reward, te, tr, fl);
+        else launch_pdl(step_kernel<T, -1, 0, 0, -1, true>, grid, kStepBlock, 0, s, false, P, b, action, obs, reward, te, tr, fl);
+    } else if (pid) launch_pdl(step_kernel<T, -1, 1, 0>, grid, kStepBlock, 0, s, true, P, b, action, obs, reward, te, tr, fl);
     else switch (P.Mpad) {
         case 1: ADRP_LAUNCH_STEP(1); break;
         case 2: ADRP_LAUNCH_STEP(2); break;
@@ -241,7 +255,7 @@ cudaError_t Launch<T>::race_step(const KParams<T>& P, const RaceParams<T>& RP, c
     const bool dense = force_dense >= 0 ? force_dense == 1 : quiet_launch;
     launch_pdl(race_step_fn<T>(P.Mpad, P.action_type, quiet_launch, noise ? -1 : P.physics, P.K > 1 || P.act_rng, dense),
                threads, kRaceBlock,
-               race_smem_bytes(P, RP, kRaceBlock), s, P, RP, b, rb, action, noise, obs, reward, te, tr, fl);
+               race_smem_bytes(P, RP, kRaceBlock), s, !(P.K > 1 || P.act_rng), P, RP, b, rb, action, noise, obs, reward, te, tr, fl);
     return cudaGetLastError();
 }
 

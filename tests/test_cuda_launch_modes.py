@@ -2,6 +2,8 @@
 
 * Programmatic dependent launch (grids longer than one wave) against plain launches (`ADRP_PDL=0`): bit-identical --
   back-to-back control steps where step n+1's blocks are scheduled while step n drains must still see all of step n.
+* The same for grids that fit one wave, whose single-step launches are padded to a whole number of blocks per SM and launched
+  programmatically too (`ADRP_PDL_ONEWAVE=0`: plain).
 * The physics-mask / env-family instances of the step kernel against the generic instance (`ADRP_STEP_GENERIC=1`):
   same formulas, but the compiler may contract multiply-adds differently, so the comparison is at 1e-5.
 
@@ -61,6 +63,17 @@ def test_programmatic_launch_is_bit_identical(wl, n):
     a = _run(wl, n, 12, ADRP_PDL="1")
     b = _run(wl, n, 12, ADRP_PDL="0")
     assert a["finite"] and a["obs_sha"] == b["obs_sha"] and a["state_sha"] == b["state_sha"]
+
+
+@pytest.mark.parametrize("wl,n", [("c2", 65536), ("c3", 16384), ("c4", 600), ("c1", 1), ("c5m", 37)])
+def test_one_wave_programmatic_launch_is_bit_identical(wl, n):
+    """Grids that fit one wave: single-step launches are padded with dynamic shared memory to ceil(blocks / SMs) blocks per SM
+    and launched programmatically (`ADRP_PDL_ONEWAVE`, default on) -- 25 control steps enqueued back to back (with C3's
+    in-kernel resets and re-staged tracks) against plain launches."""
+    a = _run(wl, n, 25)
+    b = _run(wl, n, 25, ADRP_PDL_ONEWAVE="0")
+    c = _run(wl, n, 25, ADRP_PDL="0")
+    assert a["finite"] and a["obs_sha"] == b["obs_sha"] == c["obs_sha"] and a["state_sha"] == b["state_sha"] == c["state_sha"]
 
 
 @pytest.mark.parametrize("wl,n", [("c4", 4096), ("c2", 4096)])
