@@ -119,12 +119,58 @@ __device__ __forceinline__ void downwash_pair_sym(const KParams<T>& P, T dx, T d
     theirs = dz < T(0) ? term : T(0);
 }
 
-template <typename T, int MP>
+#ifndef ADRP_PACKED_DW
+#define ADRP_PACKED_DW 1
+#endif
+// Two evaluations of downwash_pair_sym at once in the packed fp32 forms of sm_100 (FFMA2 / FMUL2 / FADD2: two results per
+// issue slot; the FMA pipe is as busy as before, but the step kernel is bound by instruction issue, not by that pipe).
+// dx, dy, dz: the two partners' offsets; mine / theirs as in downwash_pair_sym, per partner.
+__device__ __forceinline__ void downwash_pair_sym2(const KParams<float>& P, float2 dx, float2 dy, float2 dz, float2& mine, float2& theirs)
+{
+    const float2 dxy2 = __ffma2_rn(dy, dy, __fmul2_rn(dx, dx));
+    const float2 az = make_float2(fabsf(dz.x), fabsf(dz.y));
+    const float2 den = __ffma2_rn(make_float2(P.dwf_a, P.dwf_a), az, make_float2(P.dwf_b, P.dwf_b));
+    const float2 rz = make_float2(M<float>::rcp(az.x), M<float>::rcp(az.y));
+    const float2 ib = make_float2(M<float>::rcp(den.x), M<float>::rcp(den.y));
+    const float2 u = __fmul2_rn(dxy2, ib);
+    const float2 arg = __ffma2_rn(make_float2(-u.x, -u.y), ib, make_float2(P.dwf_l2c, P.dwf_l2c));
+    const float2 e = make_float2(M<float>::fexp2(arg.x), M<float>::fexp2(arg.y));
+    const float2 t = __fmul2_rn(__fmul2_rn(e, rz), rz);
+    const float tx = dxy2.x < 100.0f ? t.x : 0.0f, ty = dxy2.y < 100.0f ? t.y : 0.0f;
+    mine = make_float2(dz.x > 0.0f ? tx : 0.0f, dz.y > 0.0f ? ty : 0.0f);
+    theirs = make_float2(dz.x < 0.0f ? tx : 0.0f, dz.y < 0.0f ? ty : 0.0f);
+}
+
+// PACKED: the caller's choice per kernel instance (measured, profiles/r02zm_*): it pays in the n-step instances (C5 +4.2 %, C4
+// +2.8 %) and in C5's single-step one (+0.8 %), not in C4's single-step one (-0.6 %) nor under the race kernel's register cap
+// (C5M -1.2 %).
+template <typename T, int MP, bool PACKED = false>
 __device__ __forceinline__ T downwash(const KParams<T>& P, const V3<T>& p, int lane_base, bool valid)
 {
     T fz = T(0);
     const T pz_pub = valid ? p.z : T(-1e30);          // padding lanes never count as "above"
     const int mpad = MP > 0 ? MP : P.Mpad;
+    if constexpr (M<T>::fast && MP == 8 && PACKED && ADRP_PACKED_DW) {
+        // the four partners of the all-pairs scheme below (k = 1, 2, 3 and the antipodal k = 4), two per packed evaluation
+        const int i = (threadIdx.x & 31) - lane_base;
+        float2 ox[2], oy[2], oz[2];
+#pragma unroll
+        for (int k = 1; k <= 4; ++k) {
+            const int fwd = lane_base + ((i + k) & 7);
+            const float x = __shfl_sync(0xffffffffu, p.x, fwd), y = __shfl_sync(0xffffffffu, p.y, fwd), z = __shfl_sync(0xffffffffu, pz_pub, fwd);
+            if ((k - 1) & 1) { ox[(k - 1) >> 1].y = x; oy[(k - 1) >> 1].y = y; oz[(k - 1) >> 1].y = z; }
+            else { ox[(k - 1) >> 1].x = x; oy[(k - 1) >> 1].x = y; oz[(k - 1) >> 1].x = z; }
+        }
+        const float2 npx = make_float2(-p.x, -p.x), npy = make_float2(-p.y, -p.y), npz = make_float2(-pz_pub, -pz_pub);
+        float2 m0, t0, m1, t1;
+        downwash_pair_sym2(P, __fadd2_rn(ox[0], npx), __fadd2_rn(oy[0], npy), __fadd2_rn(oz[0], npz), m0, t0);
+        downwash_pair_sym2(P, __fadd2_rn(ox[1], npx), __fadd2_rn(oy[1], npy), __fadd2_rn(oz[1], npz), m1, t1);
+        fz -= m0.x; fz -= __shfl_sync(0xffffffffu, t0.x, lane_base + ((i - 1) & 7));
+        fz -= m0.y; fz -= __shfl_sync(0xffffffffu, t0.y, lane_base + ((i - 2) & 7));
+        fz -= m1.x; fz -= __shfl_sync(0xffffffffu, t1.x, lane_base + ((i - 3) & 7));
+        fz -= m1.y;                                        // antipodal pair: evaluated from both ends, nothing handed back
+        return fz;
+    }
     if (M<T>::fast && MP >= 4) {
         // every unordered pair once: lane i evaluates (i, i+k mod MP) for k = 1 .. MP/2-1 and hands the partner's
         // share back over one more shuffle; the antipodal pairs (k = MP/2) are evaluated from both ends

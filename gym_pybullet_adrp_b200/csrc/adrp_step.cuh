@@ -244,7 +244,7 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
             else fext = drag_force(P, d);
         }
         T dw = T(0);
-        if (phy & ADRP_PHY_DW) dw = downwash<T, MP>(P, d.p, lane_base, valid);
+        if (phy & ADRP_PHY_DW) dw = downwash<T, MP, (MULTI || (PHY_CT >= 0 && (PHY_CT & ADRP_PHY_DYN) != 0))>(P, d.p, lane_base, valid);
         if (dyn_fast) {
             dyn_substep_fast<T, DM>(P, d, R, f, tq, dw, axy, az, s == P.S - 1);
             axy = axy_cur; az = az_cur;
