@@ -66,6 +66,25 @@ __device__ __forceinline__ void ground_effect_total(const KParams<T>& P, const D
     }
 }
 
+// The same for props (0, 1) and (2, 3) at once in the packed fp32 forms (see downwash_pair_sym2): 20 scalar FP instructions -> 10.
+__device__ __forceinline__ void ground_effect_total2(const KParams<float>& P, const Drone<float>& d, const Mat3<float>& R,
+                                                     const float rpm2kf[4], float out[4])
+{
+    const bool on = R.m22 > 0.0f && fabsf(R.m20) < 0.99999f;
+    const float c = on ? P.gnd_eff_coeff * P.qr4 * P.qr4 : 0.0f;
+    const float2 r20 = make_float2(R.m20, R.m20), r21 = make_float2(R.m21, R.m21), pz = make_float2(d.p.z, d.p.z);
+    const float2 c2 = make_float2(c, c), one = make_float2(1.0f, 1.0f);
+#pragma unroll
+    for (int i = 0; i < 4; i += 2) {
+        float2 h = __ffma2_rn(r21, make_float2(P.prop_y[i], P.prop_y[i + 1]), __ffma2_rn(r20, make_float2(P.prop_x[i], P.prop_x[i + 1]), pz));
+        h = make_float2(fmaxf(h.x, P.gnd_eff_h_clip), fmaxf(h.y, P.gnd_eff_h_clip));
+        const float2 hh = __fmul2_rn(h, h);
+        const float2 g = __ffma2_rn(c2, make_float2(M<float>::rcp(hh.x), M<float>::rcp(hh.y)), one);
+        const float2 o = __fmul2_rn(make_float2(rpm2kf[i], rpm2kf[i + 1]), g);
+        out[i] = o.x; out[i + 1] = o.y;
+    }
+}
+
 // World-frame drag force (:761-788): R^T (c o v) applied in LINK_FRAME == c o v.
 template <typename T>
 __device__ __forceinline__ V3<T> drag_force(const KParams<T>& P, const Drone<T>& d)

@@ -7,6 +7,9 @@
 #include "adrp_dslpid.cuh"
 #include "adrp_physics.cuh"
 
+#ifndef ADRP_PACKED_GND
+#define ADRP_PACKED_GND 1
+#endif
 namespace adrp {
 
 constexpr int kBlock = 128;
@@ -225,11 +228,17 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
             axy_cur = T(1) - P.k_drag_xy * sc; az_cur = T(1) - P.k_drag_z * sc;
         }
     }
+    // the packed fp32 forms of the force models (adrp_physics.cuh): in the n-step instances and the DYN single-step ones
+    // (measured per instance, profiles/r02zm_* / r02zo_*: the ground effect's packed form costs C4's n-step instance 2.6 %)
+    constexpr bool kPacked = MULTI || (PHY_CT >= 0 && (PHY_CT & ADRP_PHY_DYN) != 0);
+    constexpr bool kPackedGnd = PHY_CT >= 0 && (PHY_CT & ADRP_PHY_DYN) != 0;
     for (int s = 0; s < P.S; ++s) {
         const Mat3<T> R = M<T>::fast ? rotmat_unit(d.q) : rotmat_loop(d.q);
         T f[4] = {f0[0], f0[1], f0[2], f0[3]};
         if (phy & ADRP_PHY_GND) {
-            if (M<T>::fast) {
+            if constexpr (M<T>::fast && kPackedGnd && ADRP_PACKED_GND) {
+                ground_effect_total2(P, d, R, f0, f);
+            } else if (M<T>::fast) {
                 ground_effect_total(P, d, R, f0, f);
             } else {
                 T gnd[4];
@@ -244,7 +253,7 @@ step_kernel(const __grid_constant__ KParams<T> P, const KBuffers<T> b, const T* 
             else fext = drag_force(P, d);
         }
         T dw = T(0);
-        if (phy & ADRP_PHY_DW) dw = downwash<T, MP, (MULTI || (PHY_CT >= 0 && (PHY_CT & ADRP_PHY_DYN) != 0))>(P, d.p, lane_base, valid);
+        if (phy & ADRP_PHY_DW) dw = downwash<T, MP, kPacked>(P, d.p, lane_base, valid);
         if (dyn_fast) {
             dyn_substep_fast<T, DM>(P, d, R, f, tq, dw, axy, az, s == P.S - 1);
             axy = axy_cur; az = az_cur;
