@@ -345,6 +345,8 @@ __device__ __forceinline__ void dyn_substep_fast(const KParams<T>& P, Drone<T>& 
         M<T>::sincos_small(wn * P.half_dt, &s, &c);
         k = s * M<T>::rcp(wn);
     }
+    // (the four rows as two packed pairs -- 20 FP instructions -> 10 -- measured slower: C5 adrp_step_n 1.569e10 -> 1.529e10; this update is
+    // on the substep's dependency chain, where the packed forms' latency counts: profiles/r02zq_packed_quaternion_ab.txt)
     d.q = {c * q.x + k * (nz * q.y - ny * q.z + nx * q.w), c * q.y + k * (-nz * q.x + nx * q.z + ny * q.w),
            c * q.z + k * (ny * q.x - nx * q.y + nz * q.w), c * q.w + k * (-nx * q.x - ny * q.y - nz * q.z)};
     if (last) {                                            // world rates: R of the pose BEFORE this update (:875-879)
