@@ -35,7 +35,7 @@ inline void launch_pdl(void (*kernel)(KArgs...), long long threads, unsigned blo
     static const int forced = [] { const char* e = getenv("ADRP_BLOCK"); return e ? atoi(e) : 0; }();
     static const bool onewave_pdl = [] { const char* e = getenv("ADRP_PDL_ONEWAVE"); return !e || e[0] != '0'; }();
     static std::mutex mu;
-    struct Info { long long wave; int sms; };
+    struct Info { long long wave; int sms; bool pad_ok; };
     static std::map<std::pair<const void*, int>, Info> cache;     // (kernel, device) -> resident blocks at block_max, SMs
     Info info;
     {
@@ -47,9 +47,11 @@ inline void launch_pdl(void (*kernel)(KArgs...), long long threads, unsigned blo
         if (it == cache.end()) {
             int per_sm = 0, sms = 0;
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, (int)block_max, smem_at_max);
-            cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPadBudget);   // (the padding below)
+            // (the padding below; a device that cannot give a block that much shared memory launches one-wave grids plainly)
+            const bool pad_ok = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPadBudget) == cudaSuccess;
+            if (!pad_ok) cudaGetLastError();
             cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-            it = cache.emplace(key, Info{(long long)per_sm * sms, sms}).first;
+            it = cache.emplace(key, Info{(long long)per_sm * sms, sms, pad_ok}).first;
         }
         info = it->second;
     }
@@ -71,7 +73,7 @@ inline void launch_pdl(void (*kernel)(KArgs...), long long threads, unsigned blo
     cfg.dynamicSmemBytes = smem_at_max * block / block_max;
     cfg.stream = s;
     bool pdl = enabled && !one_wave;
-    if (enabled && one_wave && onewave_pdl && single_step && info.sms > 0) {
+    if (enabled && one_wave && onewave_pdl && single_step && info.pad_ok && info.sms > 0) {
         const long long per_sm = (cfg.gridDim.x + info.sms - 1) / info.sms;
         const size_t pad = (kPadBudget / (size_t)per_sm) & ~(size_t)1023;
         if (pad > cfg.dynamicSmemBytes) { cfg.dynamicSmemBytes = pad; pdl = true; }
@@ -226,7 +228,8 @@ cudaError_t Launch<T>::race_prepare(const RaceParams<T>& RP, const KParams<T>& P
     if (bytes <= 48 * 1024) return cudaSuccess;
     cudaError_t e = cudaSuccess;
     for (int v = 0; v < 8 && e == cudaSuccess; ++v)
-        e = cudaFuncSetAttribute(race_step_fn<T>(P.Mpad, P.action_type, (v & 1) != 0, P.physics, (v & 2) != 0, (v & 4) != 0), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)race_smem_bytes(P, RP, kRaceBlock));
+        e = cudaFuncSetAttribute(race_step_fn<T>(P.Mpad, P.action_type, (v & 1) != 0, P.physics, (v & 2) != 0, (v & 4) != 0), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)(race_smem_bytes(P, RP, kRaceBlock) > kPadBudget ? race_smem_bytes(P, RP, kRaceBlock) : kPadBudget));   // (never below launch_pdl's padding)
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(race_reset_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
 }
