@@ -15,6 +15,9 @@
 #include "adrp_math.cuh"
 #include "adrp_params.cuh"
 
+#ifndef ADRP_PACKED_PWM
+#define ADRP_PACKED_PWM 1
+#endif
 namespace adrp {
 
 // libm float functions of the firmware.  Parity build (T = double): correctly rounded via the
@@ -291,6 +294,18 @@ __device__ __forceinline__ void mellinger_tick(const RaceParams<T>& RP, const ui
         if (stop) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) rp[k] = RPM_LO;                          // zero PWM, clamped to 20000 (:246)
+        } else if constexpr (ADRP_PACKED_PWM && sizeof(T) == 4) {
+            // motors (0, 1) and (2, 3) in the packed fp32 forms (two results per issue slot; clamps stay scalar)
+#pragma unroll
+            for (int k = 0; k < 4; k += 2) {
+                const float2 x = __fmul2_rn(make_float2(fminf(fmaxf((float)th[k], 0.0f), 65535.0f), fminf(fmaxf((float)th[k + 1], 0.0f), 65535.0f)),
+                                            make_float2((float)(60.0 / 65535.0), (float)(60.0 / 65535.0)));
+                const float2 v = __fmul2_rn(x, __ffma2_rn(make_float2((float)A, (float)A), x, make_float2((float)B, (float)B)));
+                const float2 r = __ffma2_rn(make_float2((float)SCALE, (float)SCALE),
+                                            make_float2(fminf(fmaxf(v.x, 20000.0f), 65535.0f), fminf(fmaxf(v.y, 20000.0f), 65535.0f)),
+                                            make_float2((float)CONST, (float)CONST));
+                rp[k] = (T)r.x; rp[k + 1] = (T)r.y;
+            }
         } else {
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
